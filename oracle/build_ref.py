@@ -1,0 +1,74 @@
+"""Build the UNMODIFIED reference rasterizer (Oracle A) into oracle/_ref/.
+
+TEST INFRASTRUCTURE ONLY. The reference CUDA extension
+(/root/reference/submodules/diff-gaussian-rasterization, setup.py:6-38) is
+compiled from the sources where they lie, with the reference's exact nvcc
+flags (-O3 --use_fast_math -std=c++17 --extended-lambda
+--expt-relaxed-constexpr, setup.py:22-33) for sm_100.  Only build outputs
+land in the repo, under the git-ignored oracle/_ref/:
+
+    oracle/_ref/ref_dgr/_C.so        the compiled extension (pybind module "_C")
+    oracle/_ref/ref_dgr/__init__.py  the reference's Python wrapper (an install
+                                     artefact, like `pip install --target`)
+
+The package is importable as `ref_dgr` (see oracle/ref_loader.py) so it can
+live beside the drop-in `diff_gaussian_rasterization` in one process.
+Needs /root/reference; on the GPU box only the prebuilt files are used.
+"""
+import os
+import shutil
+import sys
+
+REF = "/root/reference/submodules/diff-gaussian-rasterization"
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, "_ref", "ref_dgr")
+BUILD = os.environ.get("GGS_REF_BUILD_DIR", "/tmp/ggs_ref_build")
+
+
+def build(force: bool = False) -> str:
+    so = os.path.join(OUT, "_C.so")
+    if os.path.exists(so) and not force:
+        return so
+    if not os.path.isdir(REF):
+        raise RuntimeError("reference sources not present at " + REF)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0")
+    os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
+    from torch.utils.cpp_extension import load
+
+    os.makedirs(BUILD, exist_ok=True)
+    srcs = [
+        "cuda_rasterizer/rasterizer_impl.cu",
+        "cuda_rasterizer/render_forward.cu",
+        "cuda_rasterizer/render_backward.cu",
+        "cuda_rasterizer/sample_forward.cu",
+        "cuda_rasterizer/sample_backward.cu",
+        "rasterize_points.cu",
+        "ext.cpp",
+    ]
+    load(
+        name="_C",
+        sources=[os.path.join(REF, s) for s in srcs],
+        extra_cuda_cflags=[
+            "-O3",
+            "--use_fast_math",
+            "-std=c++17",
+            "--extended-lambda",
+            "--expt-relaxed-constexpr",
+            "-I" + os.path.join(REF, "third_party/glm/"),
+        ],
+        extra_include_paths=[REF],
+        build_directory=BUILD,
+        is_python_module=False,
+        verbose=True,
+    )
+    os.makedirs(OUT, exist_ok=True)
+    shutil.copyfile(os.path.join(BUILD, "_C.so"), so)
+    shutil.copyfile(
+        os.path.join(REF, "diff_gaussian_rasterization", "__init__.py"),
+        os.path.join(OUT, "__init__.py"),
+    )
+    return so
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv))
