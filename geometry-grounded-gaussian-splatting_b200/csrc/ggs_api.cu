@@ -1,0 +1,450 @@
+// C ABI of the rasterizer (include/ggs_rasterizer.h): argument checking, workspace carving and the
+// stage sequence.  Host orchestration follows CudaRasterizer::Rasterizer::forward / backward /
+// evaluateTransmittance (DGR/cuda_rasterizer/rasterizer_impl.cu:285-448, :452-592, :594-815).
+#include <algorithm>
+#include <cstdio>
+#include <string>
+
+#include "../../include/ggs_rasterizer.h"
+#include "ggs_kernels.cuh"
+
+using namespace ggs;
+
+namespace {
+
+thread_local std::string g_error;
+thread_local uint32_t* g_pinned = nullptr;
+
+int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+
+#define GGS_CUDA(expr)                                                                           \
+    do {                                                                                         \
+        cudaError_t e__ = (expr);                                                                \
+        if (e__ != cudaSuccess)                                                                  \
+            return fail(GGS_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));      \
+    } while (0)
+
+#define GGS_STAGE(name, debug, stream)                                                           \
+    do {                                                                                         \
+        cudaError_t e__ = cudaGetLastError();                                                    \
+        if (e__ == cudaSuccess && (debug)) e__ = cudaStreamSynchronize(stream);                  \
+        if (e__ != cudaSuccess)                                                                  \
+            return fail(GGS_ERR_CUDA, std::string("stage ") + name + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+uint32_t* pinned_word() {
+    if (!g_pinned) {
+        if (cudaMallocHost(&g_pinned, 64) != cudaSuccess) g_pinned = nullptr;
+    }
+    return g_pinned;
+}
+
+int sort_end_bit(int tiles) { return 32 + (int)higher_msb((uint32_t)tiles); }
+int sort_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS; }
+
+int make_frame(const GgsFrame* f, const GgsGaussians* g, FrameParams& fp, GaussianInputs& in) {
+    if (!f || !g) return fail(GGS_ERR_INVALID_ARGUMENT, "null frame or gaussians");
+    if (f->image_width <= 0 || f->image_height <= 0)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "image size must be positive");
+    if (g->count < 0 || g->count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad Gaussian count");
+    if (!f->viewmatrix || !f->projmatrix || !f->campos || !f->background)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "camera tensors must be device pointers");
+    if (g->count > 0 && (!g->means3D || !g->opacities))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "means3D and opacities are required");
+    if (g->count > 0 && (!g->scales || !g->rotations))
+        return fail(GGS_ERR_UNSUPPORTED,
+                    "scale/rotation pair required: precomputed 3D covariance is not supported (the reference "
+                    "kernel cannot consume it either, render_forward.cu:344-345)");
+    fp.P = (int)g->count;
+    fp.W = f->image_width;
+    fp.H = f->image_height;
+    fp.gx = (fp.W + TILE_X - 1) / TILE_X;
+    fp.gy = (fp.H + TILE_Y - 1) / TILE_Y;
+    if (fp.gx >= 65536 || fp.gy >= 65536) return fail(GGS_ERR_INVALID_ARGUMENT, "image too large");
+    fp.SHD = f->sh_degree;
+    fp.SHM = g->shs ? g->sh_coeffs : 0;
+    fp.SGD = f->sg_degree;
+    fp.SGM = g->sg_color ? g->sg_lobes : 0;
+    if (fp.SHD < 0 || fp.SHD > 3) return fail(GGS_ERR_INVALID_ARGUMENT, "sh_degree must be in 0..3");
+    if (g->shs && (fp.SHD + 1) * (fp.SHD + 1) > fp.SHM)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "sh_coeffs smaller than (sh_degree+1)^2");
+    if (fp.SGD < 0 || fp.SGD > fp.SGM) return fail(GGS_ERR_INVALID_ARGUMENT, "sg_degree exceeds allocated lobes");
+    fp.tanfovx = f->tanfovx;
+    fp.tanfovy = f->tanfovy;
+    // rasterizer_impl.cu:318-319
+    fp.focal_y = fp.H / (2.0f * fp.tanfovy);
+    fp.focal_x = fp.W / (2.0f * fp.tanfovx);
+    fp.kernel_size = f->kernel_size;
+    fp.scale_modifier = f->scale_modifier;
+    fp.view.view = f->viewmatrix;
+    fp.view.proj = f->projmatrix;
+    fp.view.campos = f->campos;
+    fp.view.bg = f->background;
+    in.means3D = g->means3D;
+    in.opacities = g->opacities;
+    in.scales = g->scales;
+    in.rotations = g->rotations;
+    in.shs = g->shs;
+    in.sg_axis = fp.SGM ? g->sg_axis : nullptr;
+    in.sg_sharpness = fp.SGM ? g->sg_sharpness : nullptr;
+    in.sg_color = fp.SGM ? g->sg_color : nullptr;
+    in.colors_precomp = g->colors_precomp;
+    return GGS_OK;
+}
+
+template <typename T>
+T* at(void* base, size_t off) {
+    return reinterpret_cast<T*>(static_cast<char*>(base) + off);
+}
+
+// Bins the visible Gaussians of a frame: preprocess, scan, (sync), duplicate, sort, ranges.
+// On return *D holds the number of (tile, Gaussian) pairs and *bin the binning workspace.
+int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_color, int* radii, void* geom,
+                  uint2* ranges, GgsAllocFn alloc, void* user, void** bin, int64_t* D_out, bool debug,
+                  cudaStream_t stream) {
+    const GeomLayout GL = geom_layout(fp.P);
+    launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
+                      at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
+                      at<uint8_t>(geom, GL.clamped), radii, stream);
+    GGS_STAGE("preprocess", debug, stream);
+    launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
+                at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter),
+                at<uint32_t>(geom, GL.total), stream);
+    GGS_STAGE("scan", debug, stream);
+    uint32_t* host = pinned_word();
+    if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
+    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(geom, GL.total), 4, cudaMemcpyDeviceToHost, stream));
+    GGS_CUDA(cudaStreamSynchronize(stream));
+    const uint32_t D = *host;
+    if (D >= (1u << 30)) return fail(GGS_ERR_UNSUPPORTED, "more than 2^30 (tile, Gaussian) pairs");
+    *D_out = D;
+
+    const int tiles = fp.gx * fp.gy;
+    const int end_bit = sort_end_bit(tiles);
+    const int passes = sort_passes(0, end_bit);
+    const BinLayout BL = bin_layout(D, passes);
+    void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
+    if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
+    *bin = b;
+    launch_duplicate_keys(fp.P, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
+                          at<float>(geom, GL.depths), fp.gx, at<uint64_t>(b, BL.keys_a), at<uint32_t>(b, BL.vals_a),
+                          D, stream);
+    GGS_STAGE("duplicate_keys", debug, stream);
+    const int where = launch_radix_sort(at<uint64_t>(b, BL.keys_a), at<uint64_t>(b, BL.keys_b),
+                                        at<uint32_t>(b, BL.vals_a), at<uint32_t>(b, BL.vals_b), D, 0, end_bit,
+                                        at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), BL.status_bytes,
+                                        at<uint32_t>(b, BL.counters), stream);
+    GGS_STAGE("radix_sort", debug, stream);
+    const uint64_t* sorted_keys = where ? at<uint64_t>(b, BL.keys_b) : at<uint64_t>(b, BL.keys_a);
+    launch_tile_ranges(sorted_keys, D, ranges, tiles, stream);
+    GGS_STAGE("tile_ranges", debug, stream);
+    return GGS_OK;
+}
+
+const uint32_t* sorted_list(void* bin, int64_t D, int tiles) {
+    const int passes = sort_passes(0, sort_end_bit(tiles));
+    const BinLayout BL = bin_layout((size_t)D, passes);
+    return (passes & 1) ? at<uint32_t>(bin, BL.vals_b) : at<uint32_t>(bin, BL.vals_a);
+}
+
+}  // namespace
+
+extern "C" {
+
+int ggs_abi_version(void) { return GGS_ABI_VERSION; }
+
+const char* ggs_last_error(void) { return g_error.c_str(); }
+
+int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user,
+                              const GgsForwardOutputs* out, GgsForwardState* state, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (!alloc || !out || !state) return fail(GGS_ERR_INVALID_ARGUMENT, "null alloc/out/state");
+    if (!out->color || !out->alpha || !out->normal || !out->mdepth || (fp.P > 0 && !out->radii))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null output tensor");
+    if (fp.P > 0 && ((in.shs == nullptr) == (in.colors_precomp == nullptr)))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "provide exactly one of shs / colors_precomp");
+    const bool debug = frame->debug != 0;
+    const size_t npix = (size_t)fp.W * fp.H;
+    const int tiles = fp.gx * fp.gy;
+    state->geometry = state->binning = state->image = state->tile = nullptr;
+    state->num_rendered = 0;
+
+    if (fp.P == 0) {
+        // rasterize_points.cu:95: nothing is launched, the zero-filled outputs are returned
+        GGS_CUDA(cudaMemsetAsync(out->color, 0, 3 * npix * 4, stream));
+        GGS_CUDA(cudaMemsetAsync(out->alpha, 0, npix * 4, stream));
+        GGS_CUDA(cudaMemsetAsync(out->normal, 0, 3 * npix * 4, stream));
+        GGS_CUDA(cudaMemsetAsync(out->mdepth, 0, npix * 4, stream));
+        return 0;
+    }
+
+    const GeomLayout GL = geom_layout(fp.P);
+    const TileLayout TL = tile_layout(tiles);
+    const ImgLayout IL = img_layout(npix);
+    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
+    void* tile = alloc(GGS_SLOT_TILE, TL.bytes, user);
+    void* img = alloc(GGS_SLOT_IMAGE, IL.bytes, user);
+    if (!geom || !tile || !img) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
+    state->geometry = geom;
+    state->tile = tile;
+    state->image = img;
+
+    int64_t D = 0;
+    void* bin = nullptr;
+    rc = bin_gaussians(fp, in, true, out->radii, geom, at<uint2>(tile, TL.ranges), alloc, user, &bin, &D, debug,
+                       stream);
+    if (rc) return rc;
+    state->binning = bin;
+    state->num_rendered = D;
+
+    if (!frame->require_depth) {
+        GGS_CUDA(cudaMemsetAsync(out->normal, 0, 3 * npix * 4, stream));
+        GGS_CUDA(cudaMemsetAsync(out->mdepth, 0, npix * 4, stream));
+    }
+    RenderOut ro;
+    ro.color = out->color;
+    ro.alpha = out->alpha;
+    ro.normal = out->normal;
+    ro.mdepth = out->mdepth;
+    ro.n_contrib = at<uint32_t>(img, IL.n_contrib);
+    ro.max_contributor = at<uint32_t>(tile, TL.max_contributor);
+    launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, D, tiles),
+                          at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
+    GGS_STAGE("render_forward", debug, stream);
+    return D;
+}
+
+int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                           const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                           void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (!state || !bi || !alloc || !grads) return fail(GGS_ERR_INVALID_ARGUMENT, "null state/inputs/alloc/grads");
+    if (fp.P == 0) return GGS_OK;
+    if (!state->geometry || !state->binning || !state->image || !state->tile)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "forward state is incomplete");
+    if (!grads->dL_dmeans3D || !grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity ||
+        !grads->dL_dscales || !grads->dL_drotations)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
+    if (in.shs && !grads->dL_dsh) return fail(GGS_ERR_INVALID_ARGUMENT, "dL_dsh required with shs");
+    if (in.shs && fp.SGM && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");
+    const bool debug = frame->debug != 0;
+    const size_t npix = (size_t)fp.W * fp.H;
+    const int tiles = fp.gx * fp.gy;
+    const GeomLayout GL = geom_layout(fp.P);
+    const TileLayout TL = tile_layout(tiles);
+    const ImgLayout IL = img_layout(npix);
+    (void)IL;
+
+    const size_t acc_bytes = (size_t)fp.P * GRAD_STRIDE * 4;
+    float* acc = static_cast<float*>(alloc(GGS_SLOT_BACKWARD, acc_bytes, user));
+    if (!acc) return fail(GGS_ERR_ALLOC, "backward workspace allocation failed");
+    GGS_CUDA(cudaMemsetAsync(acc, 0, acc_bytes, stream));
+
+    RenderBwdIn ri;
+    ri.alpha = bi->alpha;
+    ri.normal = bi->normal;
+    ri.mdepth = bi->mdepth;
+    ri.n_contrib = at<uint32_t>(state->image, 0);
+    ri.max_contributor = at<uint32_t>(state->tile, TL.max_contributor);
+    ri.dL_dcolor = bi->dL_dcolor;
+    ri.dL_dmdepth = bi->dL_dmdepth;
+    ri.dL_dalpha = bi->dL_dalpha;
+    ri.dL_dnormal = bi->dL_dnormal;
+    launch_render_backward(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state->num_rendered, tiles),
+                           at<SplatRecord>(state->geometry, GL.records), ri, acc, frame->require_depth != 0, stream);
+    GGS_STAGE("render_backward", debug, stream);
+
+    GaussianGrads gg;
+    gg.dL_dmeans3D = grads->dL_dmeans3D;
+    gg.dL_dmeans2D = grads->dL_dmeans2D;
+    gg.dL_dcolors = grads->dL_dcolors;
+    gg.dL_dopacity = grads->dL_dopacity;
+    gg.dL_dscales = grads->dL_dscales;
+    gg.dL_drotations = grads->dL_drotations;
+    gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
+    const bool sg = in.shs && fp.SGM;
+    gg.dL_dsg_axis = sg ? grads->dL_dsg_axis : nullptr;
+    gg.dL_dsg_sharpness = sg ? grads->dL_dsg_sharpness : nullptr;
+    gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
+    launch_gaussian_backward(fp, in, bi->radii, at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
+    GGS_STAGE("gaussian_backward", debug, stream);
+    return GGS_OK;
+}
+
+int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                             int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
+                             uint8_t* inside, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
+    if (fp.P == 0 || num_points == 0) return 0;  // rasterize_points.cu:335
+    if (!points3D || !out_transmittance || !inside || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    const bool debug = frame->debug != 0;
+    const int PN = (int)num_points;
+    const int tiles = fp.gx * fp.gy;
+    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;  // rasterizer_impl.cu:638: geometry only
+    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
+
+    const GeomLayout GL = geom_layout(fp.P);
+    // tile workspace: gaussian ranges, point ranges, rounds, offsets, scan scratch
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t a = o;
+        o = align_up(o + bytes, 256);
+        return a;
+    };
+    const size_t t_granges = take((size_t)tiles * 8), t_pranges = take((size_t)tiles * 8),
+                 t_rounds = take((size_t)tiles * 4), t_offsets = take((size_t)tiles * 4),
+                 t_status = take(((size_t)tiles / SCAN_TILE + 2) * 8), t_counter = take(256), t_total = take(256);
+    const size_t tile_bytes = o;
+    // point workspace
+    o = 0;
+    const size_t p_xy = take((size_t)PN * 8), p_depth = take((size_t)PN * 4), p_touched = take((size_t)PN * 4),
+                 p_offsets = take((size_t)PN * 4), p_status = take(((size_t)PN / SCAN_TILE + 2) * 8),
+                 p_counter = take(256), p_total = take(256), p_radii = take((size_t)fp.P * 4);
+    const size_t point_bytes = o;
+
+    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
+    void* tile = alloc(GGS_SLOT_TILE, tile_bytes, user);
+    void* pts = alloc(GGS_SLOT_POINT, point_bytes, user);
+    if (!geom || !tile || !pts) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
+
+    int64_t D = 0;
+    void* bin = nullptr;
+    rc = bin_gaussians(fp, in, false, at<int>(pts, p_radii), geom, at<uint2>(tile, t_granges), alloc, user, &bin, &D,
+                       debug, stream);
+    if (rc) return rc;
+
+    launch_preprocess_points(fp, PN, points3D, at<float2>(pts, p_xy), at<float>(pts, p_depth),
+                             at<uint32_t>(pts, p_touched), nullptr, stream);
+    launch_scan(at<uint32_t>(pts, p_touched), at<uint32_t>(pts, p_offsets), PN, at<uint64_t>(pts, p_status),
+                at<uint32_t>(pts, p_counter), at<uint32_t>(pts, p_total), stream);
+    GGS_STAGE("preprocess_points", debug, stream);
+    uint32_t* host = pinned_word();
+    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(pts, p_total), 4, cudaMemcpyDeviceToHost, stream));
+    GGS_CUDA(cudaStreamSynchronize(stream));
+    const uint32_t E = *host;
+
+    const int bit = (int)higher_msb((uint32_t)tiles);
+    const int ppasses = sort_passes(32, 32 + bit);
+    const BinLayout PL = bin_layout(E, ppasses);
+    void* pbin = alloc(GGS_SLOT_POINT_BINNING, PL.bytes, user);
+    if (!pbin) return fail(GGS_ERR_ALLOC, "point binning workspace allocation failed");
+    launch_point_keys(PN, at<uint32_t>(pts, p_offsets), at<uint32_t>(pts, p_touched), at<float2>(pts, p_xy), fp.gx,
+                      fp.gy, at<uint64_t>(pbin, PL.keys_a), at<uint32_t>(pbin, PL.vals_a), stream);
+    const int where = launch_radix_sort(at<uint64_t>(pbin, PL.keys_a), at<uint64_t>(pbin, PL.keys_b),
+                                        at<uint32_t>(pbin, PL.vals_a), at<uint32_t>(pbin, PL.vals_b), E, 32, 32 + bit,
+                                        at<uint32_t>(pbin, PL.hist), at<uint32_t>(pbin, PL.status), PL.status_bytes,
+                                        at<uint32_t>(pbin, PL.counters), stream);
+    const uint64_t* pkeys = where ? at<uint64_t>(pbin, PL.keys_b) : at<uint64_t>(pbin, PL.keys_a);
+    const uint32_t* plist = where ? at<uint32_t>(pbin, PL.vals_b) : at<uint32_t>(pbin, PL.vals_a);
+    launch_tile_ranges(pkeys, E, at<uint2>(tile, t_pranges), tiles, stream);
+    launch_point_blocks(tiles, at<uint2>(tile, t_pranges), at<uint32_t>(tile, t_rounds), stream);
+    launch_scan(at<uint32_t>(tile, t_rounds), at<uint32_t>(tile, t_offsets), tiles, at<uint64_t>(tile, t_status),
+                at<uint32_t>(tile, t_counter), at<uint32_t>(tile, t_total), stream);
+    GGS_STAGE("point_binning", debug, stream);
+
+    constexpr uint32_t PER_ROUND = TILE_PIXELS * POINT_BATCH;
+    const uint32_t max_blocks = E ? (uint32_t)std::min<uint64_t>((uint64_t)tiles + E / PER_ROUND, (uint64_t)E) : 0;
+    launch_integrate(tiles, max_blocks, at<uint32_t>(tile, t_offsets), at<uint2>(tile, t_granges),
+                     at<uint2>(tile, t_pranges), sorted_list(bin, D, tiles), plist, at<SplatRecord>(geom, GL.records),
+                     at<float2>(pts, p_xy), at<float>(pts, p_depth), out_transmittance, inside, stream);
+    GGS_STAGE("integrate", debug, stream);
+    return D;
+}
+
+int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream_) {
+    (void)projmatrix;
+    if (count < 0 || count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad count");
+    if (count == 0) return GGS_OK;
+    if (!means3D || !viewmatrix || !present) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_mark_visible((int)count, means3D, viewmatrix, present, stream);
+    GGS_STAGE("mark_visible", false, stream);
+    return GGS_OK;
+}
+
+int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_rendered, GgsLayout* L) {
+    if (!L || P < 0 || width <= 0 || height <= 0 || num_rendered < 0)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad layout query");
+    const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
+    const int tiles = gx * gy;
+    const GeomLayout GL = geom_layout((size_t)P);
+    L->geometry_bytes = GL.bytes;
+    L->records = GL.records;
+    L->depths = GL.depths;
+    L->tiles_touched = GL.tiles_touched;
+    L->point_offsets = GL.point_offsets;
+    L->clamped = GL.clamped;
+    L->rects = GL.rects;
+    const int end_bit = sort_end_bit(tiles);
+    const int passes = sort_passes(0, end_bit);
+    const BinLayout BL = bin_layout((size_t)num_rendered, passes);
+    L->binning_bytes = BL.bytes;
+    const bool in_b = passes & 1;
+    L->sorted_keys = in_b ? BL.keys_b : BL.keys_a;
+    L->point_list = in_b ? BL.vals_b : BL.vals_a;
+    L->unsorted_keys = in_b ? BL.keys_a : BL.keys_b;
+    L->unsorted_list = in_b ? BL.vals_a : BL.vals_b;
+    const TileLayout TL = tile_layout(tiles);
+    L->tile_bytes = TL.bytes;
+    L->ranges = TL.ranges;
+    L->max_contributor = TL.max_contributor;
+    const ImgLayout IL = img_layout((size_t)width * height);
+    L->image_bytes = IL.bytes;
+    L->n_contrib = IL.n_contrib;
+    L->sort_bits = (uint32_t)end_bit;
+    L->sort_passes = (uint32_t)passes;
+    return GGS_OK;
+}
+
+size_t ggs_sort_scratch_bytes(int64_t n, int32_t begin_bit, int32_t end_bit) {
+    if (n < 0 || end_bit <= begin_bit) return 0;
+    const BinLayout BL = bin_layout((size_t)n, sort_passes(begin_bit, end_bit));
+    return BL.bytes;
+}
+
+int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   int64_t n, int32_t begin_bit, int32_t end_bit, void* scratch, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n < 0 || n >= (1LL << 30)) return fail(GGS_ERR_INVALID_ARGUMENT, "n out of range");
+    if (begin_bit < 0 || end_bit > 64 || end_bit <= begin_bit || sort_passes(begin_bit, end_bit) > MAX_PASSES)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad bit range");
+    if (n == 0) return GGS_OK;
+    if (!keys_in || !vals_in || !keys_out || !vals_out || !scratch)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    const int passes = sort_passes(begin_bit, end_bit);
+    const BinLayout BL = bin_layout((size_t)n, passes);
+    GGS_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
+    GGS_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    const int where = launch_radix_sort(keys_out, at<uint64_t>(scratch, BL.keys_b), vals_out,
+                                        at<uint32_t>(scratch, BL.vals_b), (uint32_t)n, begin_bit, end_bit,
+                                        at<uint32_t>(scratch, BL.hist), at<uint32_t>(scratch, BL.status),
+                                        BL.status_bytes, at<uint32_t>(scratch, BL.counters), stream);
+    if (where) {
+        GGS_CUDA(cudaMemcpyAsync(keys_out, at<uint64_t>(scratch, BL.keys_b), (size_t)n * 8, cudaMemcpyDeviceToDevice,
+                                 stream));
+        GGS_CUDA(cudaMemcpyAsync(vals_out, at<uint32_t>(scratch, BL.vals_b), (size_t)n * 4, cudaMemcpyDeviceToDevice,
+                                 stream));
+    }
+    GGS_STAGE("sort_pairs", false, stream);
+    return GGS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,227 @@
+// Stage 2 of the forward: prefix sum of tile counts, key duplication, tile ranges.
+// Hand-written replacements for the reference's cub::DeviceScan::InclusiveSum
+// (rasterizer_impl.cu:380), duplicateWithKeys (:70-107), createWithKeys (:109-137) and
+// identifyTileRanges (:142-161).  The radix sort lives in ggs_sort.cu.
+#include "ggs_kernels.cuh"
+
+namespace ggs {
+
+// ------------------------------------------------------------------------------------------------
+// Single-pass inclusive scan with decoupled look-back.  Descriptor: bits 63..62 = state
+// (0 invalid, 1 aggregate, 2 inclusive prefix), low 32 bits = value.
+// ------------------------------------------------------------------------------------------------
+constexpr uint64_t ST_AGG = 1ull << 62;
+constexpr uint64_t ST_PREFIX = 2ull << 62;
+
+__device__ __forceinline__ uint64_t ld_relaxed(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __restrict__ in,
+                                                            uint32_t* __restrict__ out, int n,
+                                                            uint64_t* __restrict__ status,
+                                                            uint32_t* __restrict__ counter,
+                                                            uint32_t* __restrict__ total) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+    __shared__ uint32_t s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+
+    uint32_t v[SCAN_ITEMS];
+    if (base + SCAN_ITEMS <= n) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? __ldg(in + base + i) : 0u;
+    }
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        sum += v[i];
+        v[i] = sum;
+    }
+    // warp inclusive scan of the per-thread sums
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; w++)
+        if (w < warp) warp_off += s_warp[w];
+    const uint32_t thread_excl = warp_off + incl - sum;
+
+    if (threadIdx.x == SCAN_THREADS - 1) {
+        const uint32_t aggregate = warp_off + incl;
+        uint32_t prefix = 0;
+        if (tile == 0) {
+            st_relaxed(status, ST_PREFIX | aggregate);
+        } else {
+            st_relaxed(status + tile, ST_AGG | aggregate);
+            int look = (int)tile - 1;
+            while (true) {
+                const uint64_t d = ld_relaxed(status + look);
+                if (d & ST_PREFIX) {
+                    prefix += (uint32_t)d;
+                    break;
+                }
+                if (d & ST_AGG) {
+                    prefix += (uint32_t)d;
+                    look--;
+                }
+            }
+            st_relaxed(status + tile, ST_PREFIX | (uint64_t)(prefix + aggregate));
+        }
+        s_prefix = prefix;
+        if ((int)(tile + 1) * SCAN_TILE >= n) *total = prefix + aggregate;
+    }
+    __syncthreads();
+    const uint32_t off = s_prefix + thread_excl;
+    if (base + SCAN_ITEMS <= n) {
+        uint4 a = {v[0] + off, v[1] + off, v[2] + off, v[3] + off};
+        uint4 b = {v[4] + off, v[5] + off, v[6] + off, v[7] + off};
+        reinterpret_cast<uint4*>(out + base)[0] = a;
+        reinterpret_cast<uint4*>(out + base)[1] = b;
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++)
+            if (base + i < n) out[base + i] = v[i] + off;
+    }
+}
+
+void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
+                 cudaStream_t stream) {
+    const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    cudaMemsetAsync(status, 0, (size_t)(tiles + 1) * 8, stream);
+    cudaMemsetAsync(counter, 0, 4, stream);
+    cudaMemsetAsync(total, 0, 4, stream);
+    if (n == 0) return;
+    scan_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(in, out, n, status, counter, total);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Key duplication, output-parallel: each block owns 256 consecutive Gaussians and walks the
+// contiguous slice of the key array they expand into; every output slot finds its Gaussian by
+// a binary search over the block's 257 offsets held in shared memory.  Writes are fully
+// coalesced and perfectly balanced (the reference loops over a splat's tiles in one thread).
+// Key = (tile << 32) | f32 bits of depth, value = Gaussian index; slot order inside one
+// Gaussian is y-major then x (rasterizer_impl.cu:96-104).
+// ------------------------------------------------------------------------------------------------
+constexpr int DUP_THREADS = 256;
+
+__global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, const uint32_t* __restrict__ offsets,
+                                                                     const uint2* __restrict__ rects,
+                                                                     const float* __restrict__ depths, int gx,
+                                                                     uint64_t* __restrict__ keys,
+                                                                     uint32_t* __restrict__ vals) {
+    __shared__ uint32_t s_off[DUP_THREADS + 1];
+    const int g0 = blockIdx.x * DUP_THREADS;
+    const int tid = threadIdx.x;
+    const int gi = g0 + tid;
+    if (tid == 0) s_off[0] = (g0 == 0) ? 0u : __ldg(offsets + g0 - 1);
+    s_off[tid + 1] = (gi < P) ? __ldg(offsets + gi) : 0xffffffffu;
+    __syncthreads();
+    const uint32_t begin = s_off[0];
+    const int last = min(DUP_THREADS, P - g0);
+    const uint32_t end = s_off[last];
+    for (uint32_t o = begin + tid; o < end; o += DUP_THREADS) {
+        // largest j in [0,last) with s_off[j] <= o
+        int lo = 0, hi = last;
+#pragma unroll
+        for (int s = 0; s < 9; s++) {
+            const int mid = (lo + hi) >> 1;
+            if (lo + 1 < hi) {
+                if (s_off[mid] <= o)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+        }
+        const int g = g0 + lo;
+        const uint32_t local = o - s_off[lo];
+        const uint2 rc = __ldg(rects + g);
+        const uint32_t minx = rc.x & 0xffffu, miny = rc.x >> 16;
+        const uint32_t w = (rc.y & 0xffffu) - minx;
+        const uint32_t ty = miny + local / w;
+        const uint32_t tx = minx + local % w;
+        uint64_t key = (uint64_t)(ty * (uint32_t)gx + tx);
+        key <<= 32;
+        key |= (uint64_t)__float_as_uint(__ldg(depths + g));
+        keys[o] = key;
+        vals[o] = (uint32_t)g;
+    }
+}
+
+void launch_duplicate_keys(int P, const uint32_t* offsets, const uint2* rects, const float* depths, int gx,
+                           uint64_t* keys, uint32_t* vals, uint32_t D, cudaStream_t stream) {
+    if (P == 0 || D == 0) return;
+    duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(P, offsets, rects, depths,
+                                                                                          gx, keys, vals);
+}
+
+// Points fall into exactly one tile (rasterizer_impl.cu:109-137).
+__global__ void point_keys_kernel(int PN, const uint32_t* __restrict__ offsets,
+                                  const uint32_t* __restrict__ touched, const float2* __restrict__ points2D, int gx,
+                                  int gy, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)PN) return;
+    if (touched[idx] > 0) {
+        const uint32_t off = (idx == 0) ? 0 : offsets[idx - 1];
+        const float2 p = points2D[idx];
+        const int x = min(gx - 1, max((int)0, (int)((p.x + 0.5f) / TILE_X)));
+        const int y = min(gy - 1, max((int)0, (int)((p.y + 0.5f) / TILE_Y)));
+        uint64_t key = (uint64_t)(uint32_t)(y * gx + x);
+        key <<= 32;
+        keys[off] = key;
+        vals[off] = (uint32_t)idx;
+    }
+}
+
+void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,
+                       int gy, uint64_t* keys, uint32_t* vals, cudaStream_t stream) {
+    if (PN == 0) return;
+    point_keys_kernel<<<(PN + 255) / 256, 256, 0, stream>>>(PN, offsets, touched, points2D, gx, gy, keys, vals);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tile ranges from the sorted keys (rasterizer_impl.cu:142-161); untouched tiles stay (0,0).
+// ------------------------------------------------------------------------------------------------
+__global__ void tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n, uint2* __restrict__ ranges) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    const uint32_t cur = (uint32_t)(__ldg(keys + idx) >> 32);
+    if (idx == 0) {
+        ranges[cur].x = 0;
+    } else {
+        const uint32_t prev = (uint32_t)(__ldg(keys + idx - 1) >> 32);
+        if (cur != prev) {
+            ranges[prev].y = idx;
+            ranges[cur].x = idx;
+        }
+    }
+    if (idx == n - 1) ranges[cur].y = n;
+}
+
+void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream) {
+    cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
+    if (n == 0) return;
+    tile_ranges_kernel<<<(n + 255) / 256, 256, 0, stream>>>(sorted_keys, n, ranges);
+}
+
+}  // namespace ggs

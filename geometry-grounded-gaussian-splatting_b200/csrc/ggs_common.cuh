@@ -1,0 +1,170 @@
+// Shared definitions of the B200-native Gaussian rasterizer kernels (sm_100a).
+//
+// Compile-time configuration mirrors the reference's shipped configuration
+// (DGR/cuda_rasterizer/config.h:15-39): MEDIAN_DEPTH_INIT, TRAINING=1, 16x16 tiles.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ggs {
+
+constexpr int TILE_X = 16;
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIXELS = TILE_X * TILE_Y;
+constexpr float MIN_TRANSMITTANCE = 0.45f;  // config.h:31
+constexpr int SPLIT = 8;                    // config.h:32
+constexpr float SAMPLE_RANGE = 0.4f;        // config.h:34 (TRAINING)
+constexpr int SPLIT_ITERATIONS = 5;         // config.h:35 (TRAINING)
+constexpr int POINT_BATCH = 2;              // config.h:27 SAMPLE_BATCH_SIZE
+
+// Per-Gaussian record consumed by the tile kernels: 16 floats = one 64-byte, 64-byte aligned
+// gather unit (two full 32-byte sectors, no wasted bytes).
+//   q0 = (mean2D.x, mean2D.y, conic.x, conic.y)
+//   q1 = (conic.z, opacity*coef, ray_plane.x, ray_plane.y)
+//   q2 = (ray_plane.z, ray_plane.w, r, g)
+//   q3 = (b, normal.x, normal.y, normal.z)
+struct __align__(16) SplatRecord {
+    float4 q0, q1, q2, q3;
+};
+static_assert(sizeof(SplatRecord) == 64, "record must be 64 bytes");
+
+// Per-Gaussian gradient accumulator written by the tile backward with warp-aggregated
+// reductions: 17 live floats, padded to 20 (80 bytes, 16-byte aligned).
+//   [0..2]  dL/dmean2D (x, y, |x|+|y|)
+//   [3..6]  dL/dconic (x, y, z), dL/d(opacity*coef)
+//   [7..9]  dL/dcolor
+//   [10..12] dL/dnormal
+//   [13..16] dL/dray_plane (x, y, tc, rsigma)
+constexpr int GRAD_STRIDE = 20;
+constexpr int GRAD_LIVE = 17;
+
+// Camera tensors stay in device memory (as in the reference, which takes raw device pointers);
+// nothing here forces a host round trip.
+struct View {
+    const float* view;    // [16] transposed world->view (reference layout, scene/cameras.py:70)
+    const float* proj;    // [16] transposed full projection
+    const float* campos;  // [3]
+    const float* bg;      // [3]
+};
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Reference host helper (rasterizer_impl.cu:37-50): NOT ceil(log2(n)).
+inline uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4;
+    uint32_t step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb)
+            msb += step;
+        else
+            msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+// ---- workspace layouts (private to this library; offsets exported for tests) -------------
+
+struct GeomLayout {
+    size_t records;        // SplatRecord[P]
+    size_t depths;         // f32[P]
+    size_t tiles_touched;  // u32[P]
+    size_t point_offsets;  // u32[P]
+    size_t clamped;        // u8[P]  (bit c set when colour channel c was clamped)
+    size_t rects;          // uint2[P]: (min.x | min.y<<16, max.x | max.y<<16) tile rectangle
+    size_t scan_status;    // u64[scan tiles + 1]
+    size_t scan_counter;   // u32
+    size_t total;          // u32 D mirror
+    size_t bytes;
+};
+
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_TILE = SCAN_ITEMS * SCAN_THREADS;
+
+inline GeomLayout geom_layout(size_t P) {
+    GeomLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t at = o;
+        o = align_up(o + bytes, 256);
+        return at;
+    };
+    L.records = take(P * sizeof(SplatRecord));
+    L.depths = take(P * 4);
+    L.tiles_touched = take(P * 4);
+    L.point_offsets = take(P * 4);
+    L.clamped = take(P);
+    L.rects = take(P * 8);
+    size_t tiles = (P + SCAN_TILE - 1) / SCAN_TILE + 1;
+    L.scan_status = take(tiles * 8);
+    L.scan_counter = take(256);
+    L.total = take(256);
+    L.bytes = o;
+    return L;
+}
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_PASSES = 8;
+
+struct BinLayout {
+    size_t keys_a, keys_b;  // u64[D]
+    size_t vals_a, vals_b;  // u32[D]
+    size_t hist;            // u32[MAX_PASSES][RADIX]  (global digit histograms -> exclusive offsets)
+    size_t status;          // u32[passes][tiles][RADIX] decoupled look-back descriptors
+    size_t counters;        // u32[MAX_PASSES] dynamic tile ids
+    size_t bytes;
+    size_t status_bytes;
+};
+
+inline BinLayout bin_layout(size_t D, int passes) {
+    BinLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t at = o;
+        o = align_up(o + bytes, 256);
+        return at;
+    };
+    L.keys_a = take(D * 8);
+    L.keys_b = take(D * 8);
+    L.vals_a = take(D * 4);
+    L.vals_b = take(D * 4);
+    L.hist = take(MAX_PASSES * RADIX * 4);
+    size_t tiles = (D + SORT_TILE - 1) / SORT_TILE;
+    L.status_bytes = (size_t)passes * tiles * RADIX * 4;
+    L.status = take(L.status_bytes);
+    L.counters = take(MAX_PASSES * 4);
+    L.bytes = o;
+    return L;
+}
+
+struct TileLayout {
+    size_t ranges;           // uint2[tiles]
+    size_t max_contributor;  // u32[tiles]
+    size_t bytes;
+};
+inline TileLayout tile_layout(size_t tiles) {
+    TileLayout L;
+    L.ranges = 0;
+    L.max_contributor = align_up(tiles * 8, 256);
+    L.bytes = L.max_contributor + align_up(tiles * 4, 256);
+    return L;
+}
+
+struct ImgLayout {
+    size_t n_contrib;  // u32[W*H]
+    size_t bytes;
+};
+inline ImgLayout img_layout(size_t npix) {
+    ImgLayout L;
+    L.n_contrib = 0;
+    L.bytes = align_up(npix * 4, 256);
+    return L;
+}
+
+}  // namespace ggs

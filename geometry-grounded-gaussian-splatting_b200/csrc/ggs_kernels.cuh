@@ -1,0 +1,108 @@
+// Launch entry points of the individual stages (internal C++ interface; the public boundary is
+// the C ABI in include/ggs_rasterizer.h).
+#pragma once
+#include "ggs_common.cuh"
+
+namespace ggs {
+
+struct FrameParams {
+    int P, W, H;
+    int gx, gy;  // tile grid
+    int SHD, SHM, SGD, SGM;
+    float tanfovx, tanfovy, focal_x, focal_y;
+    float kernel_size, scale_modifier;
+    View view;  // device pointers
+};
+
+struct GaussianInputs {
+    const float* means3D;         // [P,3]
+    const float* opacities;       // [P]
+    const float* scales;          // [P,3]
+    const float* rotations;       // [P,4] (r,x,y,z)
+    const float* shs;             // [P,SHM,3] or null
+    const float* sg_axis;         // [P,SGM,3] or null
+    const float* sg_sharpness;    // [P,SGM] or null
+    const float* sg_color;        // [P,SGM,3] or null
+    const float* colors_precomp;  // [P,3] or null
+};
+
+// ---- stage 1: per-Gaussian preprocess + scan -------------------------------------------------
+void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
+                       float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
+                       cudaStream_t stream);
+
+void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
+                 cudaStream_t stream);
+
+// ---- stage 2: key duplication, radix sort, tile ranges ----------------------------------------
+void launch_duplicate_keys(int P, const uint32_t* offsets, const uint2* rects, const float* depths, int gx,
+                           uint64_t* keys, uint32_t* vals, uint32_t D, cudaStream_t stream);
+
+// point variant (reference createWithKeys, rasterizer_impl.cu:109-137): key = tile<<32
+void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,
+                       int gy, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
+
+// Sorts (keys_a, vals_a) on bits [begin_bit, end_bit); returns 0 if the result is in *_a, 1 if in *_b.
+int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
+                      int begin_bit, int end_bit, uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
+                      cudaStream_t stream);
+
+void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream);
+
+// ---- stage 3: tile blend --------------------------------------------------------------------
+struct RenderOut {
+    float* color;   // [3,H,W]
+    float* alpha;   // [1,H,W]
+    float* normal;  // [3,H,W]
+    float* mdepth;  // [1,H,W]
+    uint32_t* n_contrib;
+    uint32_t* max_contributor;
+};
+void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
+                           const SplatRecord* records, const RenderOut& out, bool require_depth,
+                           cudaStream_t stream);
+
+// ---- backward --------------------------------------------------------------------------------
+struct RenderBwdIn {
+    const float* alpha;
+    const float* normal;
+    const float* mdepth;
+    const uint32_t* n_contrib;
+    const uint32_t* max_contributor;
+    const float* dL_dcolor;
+    const float* dL_dmdepth;
+    const float* dL_dalpha;
+    const float* dL_dnormal;
+};
+void launch_render_backward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
+                            const SplatRecord* records, const RenderBwdIn& in, float* grad_acc,
+                            bool require_depth, cudaStream_t stream);
+
+struct GaussianGrads {
+    float* dL_dmeans3D;       // [P,3]
+    float* dL_dmeans2D;       // [P,3]
+    float* dL_dcolors;        // [P,3]
+    float* dL_dopacity;       // [P]
+    float* dL_dscales;        // [P,3]
+    float* dL_drotations;     // [P,4]
+    float* dL_dsh;            // [P,SHM,3] or null
+    float* dL_dsg_axis;       // [P,SGM,3] or null
+    float* dL_dsg_sharpness;  // [P,SGM] or null
+    float* dL_dsg_color;      // [P,SGM,3] or null
+};
+void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
+                              const uint8_t* clamped, const float* grad_acc, const GaussianGrads& g,
+                              cudaStream_t stream);
+
+// ---- point queries (integrate) ----------------------------------------------------------------
+void launch_preprocess_points(const FrameParams& fp, int PN, const float* points3D, float2* points2D,
+                              float* depths, uint32_t* touched, uint8_t* inside, cudaStream_t stream);
+void launch_point_blocks(int tiles, const uint2* point_ranges, uint32_t* tile_rounds, cudaStream_t stream);
+void launch_integrate(int tiles, uint32_t max_blocks, const uint32_t* tile_offsets, const uint2* gaussian_ranges,
+                      const uint2* point_ranges, const uint32_t* gaussian_list, const uint32_t* point_list,
+                      const SplatRecord* records, const float2* points2D, const float* point_depths,
+                      float* out_transmittance, uint8_t* inside, cudaStream_t stream);
+
+void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
+
+}  // namespace ggs

@@ -1,0 +1,320 @@
+"""Drop-in replacement for the reference package `diff_gaussian_rasterization`
+(XiShuFan/Geometry-Grounded-Gaussian-Splatting, submodules/diff-gaussian-rasterization,
+DGR/diff_gaussian_rasterization/__init__.py).
+
+Same public names, argument order, return order and exceptions:
+
+    GaussianRasterizationSettings   NamedTuple, 15 fields            (reference :254-269)
+    GaussianRasterizer(settings)    nn.Module                        (reference :272-483)
+        .forward(means3D, means2D, opacities, shs, sg_axis, sg_sharpness, sg_color,
+                 colors_precomp, scales, rotations, cov3D_precomp)
+              -> (color [3,H,W], radii [P] int32, mdepth [1,H,W], alpha [1,H,W], normal [3,H,W])
+        .integrate(points3D, means3D, opacities, scales, rotations, ...) -> (1 - T [PN], inside [PN] bool)
+        .markVisible(positions) -> bool [P]
+
+so gaussian_renderer/__init__.py, train.py, render.py and mesh_extract*.py import it unchanged.
+All computation happens in hand-written sm_100a CUDA kernels behind the C ABI of
+include/ggs_rasterizer.h; this file only marshals tensors.  No CPU / PyTorch fallback exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _abi
+from ._abi import lib as _lib
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    kernel_size: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    sg_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    require_depth: bool
+    debug: bool
+
+
+def _dev_f32(t, device):
+    """Contiguous float32 tensor on `device` (the reference calls .contiguous() on everything)."""
+    if t is None:
+        return None
+    if t.device != device or t.dtype != torch.float32:
+        t = t.to(device=device, dtype=torch.float32)
+    return t.contiguous()
+
+
+def _present(t):
+    return t is not None and t.numel() != 0
+
+
+def _frame(rs: GaussianRasterizationSettings, device, keep: list, kernel_size=None) -> _abi.GgsFrame:
+    view = _dev_f32(rs.viewmatrix, device)
+    proj = _dev_f32(rs.projmatrix, device)
+    campos = _dev_f32(rs.campos, device)
+    bg = _dev_f32(rs.bg, device)
+    keep += [view, proj, campos, bg]
+    f = _abi.GgsFrame()
+    f.image_width = int(rs.image_width)
+    f.image_height = int(rs.image_height)
+    f.tanfovx = float(rs.tanfovx)
+    f.tanfovy = float(rs.tanfovy)
+    f.kernel_size = float(rs.kernel_size if kernel_size is None else kernel_size)
+    f.scale_modifier = float(rs.scale_modifier)
+    f.sh_degree = int(rs.sh_degree)
+    f.sg_degree = int(rs.sg_degree)
+    f.prefiltered = int(bool(rs.prefiltered))
+    f.require_depth = int(bool(rs.require_depth))
+    f.debug = int(bool(rs.debug))
+    f.viewmatrix = _abi.ptr(view)
+    f.projmatrix = _abi.ptr(proj)
+    f.campos = _abi.ptr(campos)
+    f.background = _abi.ptr(bg)
+    return f
+
+
+def _gaussians(means3D, opacities, scales, rotations, sh, sg_axis, sg_sharpness, sg_color, colors_precomp,
+               sg_degree) -> _abi.GgsGaussians:
+    g = _abi.GgsGaussians()
+    g.count = means3D.shape[0]
+    g.means3D = _abi.ptr(means3D)
+    g.opacities = _abi.ptr(opacities)
+    g.scales = _abi.ptr(scales)
+    g.rotations = _abi.ptr(rotations)
+    g.shs = _abi.ptr(sh)
+    g.sh_coeffs = sh.shape[1] if _present(sh) else 0
+    has_sg = _present(sg_color) and _present(sg_axis) and _present(sg_sharpness)
+    g.sg_axis = _abi.ptr(sg_axis) if has_sg else None
+    g.sg_sharpness = _abi.ptr(sg_sharpness) if has_sg else None
+    g.sg_color = _abi.ptr(sg_color) if has_sg else None
+    g.sg_lobes = sg_color.shape[1] if has_sg else 0
+    g.colors_precomp = _abi.ptr(colors_precomp)
+    if sg_degree > g.sg_lobes:
+        raise RuntimeError(f"sg_degree={sg_degree} but only {g.sg_lobes} spherical-Gaussian lobes were provided")
+    return g
+
+
+def _check_means(means3D):
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor: this rasterizer has no CPU path")
+
+
+def rasterize_gaussians(means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, colors_precomp, opacities, scales,
+                        rotations, cov3Ds_precomp, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, colors_precomp,
+                                     opacities, scales, rotations, cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    """Autograd node; argument and gradient order of the reference (:53-251)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, colors_precomp, opacities, scales,
+                rotations, cov3Ds_precomp, raster_settings):
+        rs = raster_settings
+        _check_means(means3D)
+        if _present(cov3Ds_precomp):
+            raise NotImplementedError(
+                "cov3D_precomp is not supported: the reference kernel itself cannot consume precomputed "
+                "covariances (render_forward.cu:344-345); pass scales and rotations")
+        device = means3D.device
+        P = means3D.shape[0]
+        H, W = int(rs.image_height), int(rs.image_width)
+        keep = []
+        tens = [_dev_f32(t, device) if _present(t) else None
+                for t in (means3D, opacities, scales, rotations, sh, sg_axis, sg_sharpness, sg_color, colors_precomp)]
+        m3, op, sc, ro, sh_, sa, ss, sgc, cp = tens
+        with torch.cuda.device(device):
+            frame = _frame(rs, device, keep)
+            g = _gaussians(m3, op, sc, ro, sh_, sa, ss, sgc, cp, int(rs.sg_degree))
+            color = torch.empty(3, H, W, dtype=torch.float32, device=device)
+            mdepth = torch.empty(1, H, W, dtype=torch.float32, device=device)
+            alpha = torch.empty(1, H, W, dtype=torch.float32, device=device)
+            normal = torch.empty(3, H, W, dtype=torch.float32, device=device)
+            radii = torch.empty(P, dtype=torch.int32, device=device)
+            out = _abi.GgsForwardOutputs(_abi.ptr(color), _abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth),
+                                         _abi.ptr(radii))
+            state = _abi.GgsForwardState()
+            arena = _abi.Arena(device)
+            n = _lib.ggs_rasterize_forward(C.byref(frame), C.byref(g), arena.fn, None, C.byref(out), C.byref(state),
+                                           _abi.stream_handle(device))
+            if n < 0:
+                if arena.error is not None:
+                    raise arena.error
+                _abi.check(n, "ggs_rasterize_forward")
+        ctx.raster_settings = rs
+        ctx.num_rendered = int(n)
+        ctx.arena = arena
+        ctx.had = [_present(t) for t in (sh, sg_axis, sg_sharpness, sg_color, colors_precomp)]
+        ctx.save_for_backward(m3, op, sc, ro, sh_, sa, ss, sgc, cp, alpha, normal, mdepth, radii)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, mdepth, alpha, normal
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_radii, grad_mdepth, grad_alpha, grad_normal):
+        rs = ctx.raster_settings
+        m3, op, sc, ro, sh_, sa, ss, sgc, cp, alpha, normal, mdepth, radii = ctx.saved_tensors
+        device = m3.device
+        P = m3.shape[0]
+        H, W = int(rs.image_height), int(rs.image_width)
+        keep = []
+
+        def g_or_zero(gr, c):
+            if gr is None:
+                return torch.zeros(c, H, W, dtype=torch.float32, device=device)
+            return _dev_f32(gr, device)
+
+        gc, gd, ga, gn = g_or_zero(grad_color, 3), g_or_zero(grad_mdepth, 1), g_or_zero(grad_alpha, 1), \
+            g_or_zero(grad_normal, 3)
+        opts = dict(dtype=torch.float32, device=device)
+        SHM = sh_.shape[1] if sh_ is not None else 0
+        SGM = sgc.shape[1] if (sgc is not None and sa is not None and ss is not None) else 0
+        d_means3D = torch.empty(P, 3, **opts)
+        d_means2D = torch.empty(P, 3, **opts)
+        d_colors = torch.empty(P, 3, **opts)
+        d_opacity = torch.empty(P, 1, **opts)
+        d_scales = torch.empty(P, 3, **opts)
+        d_rot = torch.empty(P, 4, **opts)
+        d_sh = torch.empty(P, SHM, 3, **opts)
+        d_sg_axis = torch.empty(P, SGM, 3, **opts)
+        d_sg_sharp = torch.empty(P, SGM, **opts)
+        d_sg_color = torch.empty(P, SGM, 3, **opts)
+        with torch.cuda.device(device):
+            frame = _frame(rs, device, keep)
+            g = _gaussians(m3, op, sc, ro, sh_, sa, ss, sgc, cp, int(rs.sg_degree))
+            fwd = ctx.arena.buffers
+            state = _abi.GgsForwardState(
+                _abi.ptr(fwd.get(_abi.SLOT_GEOMETRY)), _abi.ptr(fwd.get(_abi.SLOT_BINNING)),
+                _abi.ptr(fwd.get(_abi.SLOT_IMAGE)), _abi.ptr(fwd.get(_abi.SLOT_TILE)), ctx.num_rendered)
+            bi = _abi.GgsBackwardInputs(_abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth), _abi.ptr(radii),
+                                        _abi.ptr(gc), _abi.ptr(gd), _abi.ptr(ga), _abi.ptr(gn))
+            grads = _abi.GgsGradients(_abi.ptr(d_means3D), _abi.ptr(d_means2D), _abi.ptr(d_colors),
+                                      _abi.ptr(d_opacity), _abi.ptr(d_scales), _abi.ptr(d_rot), _abi.ptr(d_sh),
+                                      _abi.ptr(d_sg_axis), _abi.ptr(d_sg_sharp), _abi.ptr(d_sg_color))
+            arena = _abi.Arena(device)
+            rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn, None,
+                                             C.byref(grads), _abi.stream_handle(device))
+            if rc < 0:
+                if arena.error is not None:
+                    raise arena.error
+                _abi.check(rc, "ggs_rasterize_backward")
+        had_sh, had_sa, had_ss, had_sgc, had_cp = ctx.had
+        if SGM == 0:
+            # lobes absent or unused: gradients of whatever was passed are zero
+            d_sg_axis = torch.zeros_like(sa) if sa is not None else None
+            d_sg_sharp = torch.zeros_like(ss) if ss is not None else None
+            d_sg_color = torch.zeros_like(sgc) if sgc is not None else None
+        return (
+            d_means3D,
+            d_means2D,
+            d_sh if had_sh else None,
+            d_sg_axis if had_sa else None,
+            d_sg_sharp if had_ss else None,
+            d_sg_color if had_sgc else None,
+            d_colors if had_cp else None,
+            d_opacity,
+            d_scales,
+            d_rot,
+            None,
+            None,
+        )
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of points in front of the near plane (reference :277-283)."""
+        rs = self.raster_settings
+        with torch.no_grad():
+            device = positions.device
+            pos = _dev_f32(positions, device)
+            P = pos.shape[0]
+            present = torch.zeros(P, dtype=torch.bool, device=device)
+            keep = []
+            with torch.cuda.device(device):
+                view = _dev_f32(rs.viewmatrix, device)
+                proj = _dev_f32(rs.projmatrix, device)
+                keep += [view, proj]
+                _abi.check(_lib.ggs_mark_visible(_abi.ptr(pos), P, _abi.ptr(view), _abi.ptr(proj),
+                                                 _abi.ptr(present), _abi.stream_handle(device)), "ggs_mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, sg_axis=None, sg_sharpness=None, sg_color=None,
+                colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None):
+        rs = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception("Please provide excatly one of either SHs or precomputed colors!")
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        empty = torch.Tensor([])
+        shs = empty if shs is None else shs
+        colors_precomp = empty if colors_precomp is None else colors_precomp
+        scales = empty if scales is None else scales
+        rotations = empty if rotations is None else rotations
+        cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        return rasterize_gaussians(means3D, means2D, shs, sg_axis, sg_sharpness, sg_color, colors_precomp, opacities,
+                                   scales, rotations, cov3D_precomp, rs)
+
+    def integrate(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None,
+                  view2gaussian_precomp=None):
+        """Opacity (1 - transmittance) of query points seen from this camera (reference :338-402)."""
+        rs = self.raster_settings
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        if cov3D_precomp is not None and cov3D_precomp.numel():
+            raise NotImplementedError("cov3D_precomp is not supported; pass scales and rotations")
+        _check_means(means3D)
+        if points3D.dim() != 2 or points3D.shape[1] != 3:
+            raise RuntimeError("points3D must have dimensions (num_points, 3)")
+        device = means3D.device
+        with torch.no_grad():
+            pts = _dev_f32(points3D, device)
+            m3, op, sc, ro = (_dev_f32(t, device) for t in (means3D, opacities, scales, rotations))
+            PN = pts.shape[0]
+            transmittance = torch.zeros(PN, dtype=torch.float32, device=device)
+            inside = torch.zeros(PN, dtype=torch.bool, device=device)
+            keep = []
+            with torch.cuda.device(device):
+                frame = _frame(rs, device, keep, kernel_size=0.0)  # the reference passes 0.0 here (:382)
+                g = _gaussians(m3, op, sc, ro, None, None, None, None, None, 0)
+                arena = _abi.Arena(device)
+                n = _lib.ggs_integrate_points(C.byref(frame), C.byref(g), _abi.ptr(pts), PN, arena.fn, None,
+                                              _abi.ptr(transmittance), _abi.ptr(inside), _abi.stream_handle(device))
+                if n < 0:
+                    if arena.error is not None:
+                        raise arena.error
+                    _abi.check(n, "ggs_integrate_points")
+                # the arena's buffers are released when their last use on this stream has been enqueued;
+                # torch's caching allocator keeps them stream-ordered
+        return 1 - transmittance, inside
+
+    def evaluate_sdf(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None,
+                     view2gaussian_precomp=None):
+        raise NotImplementedError(
+            "evaluate_sdf is outside the accelerated hot path (no live caller in the reference: "
+            "mesh_extract_tetrahedra.py:90-102 is commented out); see DESIGN.md")
+
+    def sample_depth(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None):
+        raise NotImplementedError(
+            "sample_depth is the next row of the scope table (SURVEY.md 8(f) N1) and is not built yet; "
+            "see DESIGN.md")

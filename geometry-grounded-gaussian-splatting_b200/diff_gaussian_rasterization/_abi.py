@@ -1,0 +1,157 @@
+"""ctypes binding of libggs_rasterizer.so (C ABI declared in include/ggs_rasterizer.h).
+
+PyTorch is used for device memory and streams only; every kernel lives in the shared library.
+There is no fallback: if the library is missing or does not load, importing this module fails.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libggs_rasterizer.so")
+
+SLOT_GEOMETRY, SLOT_BINNING, SLOT_IMAGE, SLOT_TILE, SLOT_POINT, SLOT_POINT_BINNING, SLOT_BACKWARD = range(7)
+
+_f32p = C.c_void_p
+
+
+class GgsFrame(C.Structure):
+    _fields_ = [
+        ("image_width", C.c_int32), ("image_height", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float),
+        ("kernel_size", C.c_float), ("scale_modifier", C.c_float),
+        ("sh_degree", C.c_int32), ("sg_degree", C.c_int32),
+        ("prefiltered", C.c_int32), ("require_depth", C.c_int32), ("debug", C.c_int32),
+        ("viewmatrix", _f32p), ("projmatrix", _f32p), ("campos", _f32p), ("background", _f32p),
+    ]
+
+
+class GgsGaussians(C.Structure):
+    _fields_ = [
+        ("count", C.c_int64),
+        ("means3D", _f32p), ("opacities", _f32p), ("scales", _f32p), ("rotations", _f32p),
+        ("shs", _f32p), ("sh_coeffs", C.c_int32),
+        ("sg_axis", _f32p), ("sg_sharpness", _f32p), ("sg_color", _f32p), ("sg_lobes", C.c_int32),
+        ("colors_precomp", _f32p),
+    ]
+
+
+class GgsForwardOutputs(C.Structure):
+    _fields_ = [("color", _f32p), ("alpha", _f32p), ("normal", _f32p), ("mdepth", _f32p), ("radii", C.c_void_p)]
+
+
+class GgsForwardState(C.Structure):
+    _fields_ = [("geometry", C.c_void_p), ("binning", C.c_void_p), ("image", C.c_void_p), ("tile", C.c_void_p),
+                ("num_rendered", C.c_int64)]
+
+
+class GgsBackwardInputs(C.Structure):
+    _fields_ = [("alpha", _f32p), ("normal", _f32p), ("mdepth", _f32p), ("radii", C.c_void_p),
+                ("dL_dcolor", _f32p), ("dL_dmdepth", _f32p), ("dL_dalpha", _f32p), ("dL_dnormal", _f32p)]
+
+
+class GgsGradients(C.Structure):
+    _fields_ = [("dL_dmeans3D", _f32p), ("dL_dmeans2D", _f32p), ("dL_dcolors", _f32p), ("dL_dopacity", _f32p),
+                ("dL_dscales", _f32p), ("dL_drotations", _f32p), ("dL_dsh", _f32p), ("dL_dsg_axis", _f32p),
+                ("dL_dsg_sharpness", _f32p), ("dL_dsg_color", _f32p)]
+
+
+class GgsLayout(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "geometry_bytes", "records", "depths", "tiles_touched", "point_offsets", "clamped", "rects",
+        "binning_bytes", "sorted_keys", "point_list", "unsorted_keys", "unsorted_list",
+        "tile_bytes", "ranges", "max_contributor", "image_bytes", "n_contrib")] + [
+        ("sort_bits", C.c_uint32), ("sort_passes", C.c_uint32)]
+
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
+
+EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
+           "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
+           "ggs_sort_pairs")
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make -C geometry-grounded-gaussian-splatting_b200/csrc` "
+            "(or __graft_entry__.build()).  There is no CPU or PyTorch fallback for the rasterizer.")
+    lib = C.CDLL(LIB_PATH)
+    lib.ggs_abi_version.restype = C.c_int
+    lib.ggs_last_error.restype = C.c_char_p
+    lib.ggs_rasterize_forward.restype = C.c_int64
+    lib.ggs_rasterize_forward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), ALLOC_FN, C.c_void_p,
+                                          C.POINTER(GgsForwardOutputs), C.POINTER(GgsForwardState), C.c_void_p]
+    lib.ggs_rasterize_backward.restype = C.c_int
+    lib.ggs_rasterize_backward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.POINTER(GgsForwardState),
+                                           C.POINTER(GgsBackwardInputs), ALLOC_FN, C.c_void_p,
+                                           C.POINTER(GgsGradients), C.c_void_p]
+    lib.ggs_integrate_points.restype = C.c_int64
+    lib.ggs_integrate_points.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
+                                         ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_mark_visible.restype = C.c_int
+    lib.ggs_mark_visible.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_describe_layout.restype = C.c_int
+    lib.ggs_describe_layout.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.POINTER(GgsLayout)]
+    lib.ggs_sort_scratch_bytes.restype = C.c_size_t
+    lib.ggs_sort_scratch_bytes.argtypes = [C.c_int64, C.c_int32, C.c_int32]
+    lib.ggs_sort_pairs.restype = C.c_int
+    lib.ggs_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                   C.c_void_p, C.c_void_p]
+    if lib.ggs_abi_version() != 1:
+        raise ImportError("libggs_rasterizer.so has an unexpected ABI version")
+    return lib
+
+
+lib = _load()
+
+
+def last_error() -> str:
+    return (lib.ggs_last_error() or b"").decode()
+
+
+def check(rc: int, what: str) -> int:
+    if rc < 0:
+        raise RuntimeError(f"{what} failed ({rc}): {last_error()}")
+    return rc
+
+
+def ptr(t):
+    """Device pointer of a tensor, NULL for None / empty tensors."""
+    if t is None or t.numel() == 0:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+class Arena:
+    """Hands torch-owned device buffers to the library (the reference's resize lambdas,
+    rasterize_points.cu:27-37).  The tensors stay referenced here until the arena is dropped."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buffers = {}
+        self.error = None
+
+        def _alloc(slot, nbytes, _user):
+            try:
+                t = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
+                self.buffers[int(slot)] = t
+                return t.data_ptr()
+            except Exception as ex:  # surfaces as GGS_ERR_ALLOC
+                self.error = ex
+                return 0
+
+        self.fn = ALLOC_FN(_alloc)
+
+
+def stream_handle(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def describe_layout(P: int, W: int, H: int, num_rendered: int) -> GgsLayout:
+    L = GgsLayout()
+    check(lib.ggs_describe_layout(P, W, H, num_rendered, C.byref(L)), "ggs_describe_layout")
+    return L

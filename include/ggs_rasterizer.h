@@ -1,0 +1,194 @@
+/*
+ * ggs_rasterizer.h -- C ABI of the B200-native differentiable Gaussian rasterizer.
+ *
+ * This is the drop-in boundary for the hot path of XiShuFan/Geometry-Grounded-Gaussian-Splatting's
+ * submodules/diff-gaussian-rasterization ("DGR/").  Each entry point replaces one static method
+ * of CudaRasterizer::Rasterizer (DGR/cuda_rasterizer/rasterizer.h) that the reference's torch
+ * binding (DGR/rasterize_points.cu, exported by DGR/ext.cpp:15-23) calls:
+ *
+ *   ggs_rasterize_forward   <- Rasterizer::forward                (rasterizer.h:29,  rasterize_points.cu:39-139)
+ *   ggs_rasterize_backward  <- Rasterizer::backward               (rasterizer.h:63,  rasterize_points.cu:141-258)
+ *   ggs_integrate_points    <- Rasterizer::evaluateTransmittance  (rasterizer.h:111, rasterize_points.cu:279-366)
+ *   ggs_mark_visible        <- Rasterizer::markVisible            (rasterizer.h:22,  rasterize_points.cu:260-277)
+ *
+ * Conventions
+ *   - plain C: pointers, sizes and PODs only; no torch, STL or CUDA types in any signature;
+ *   - every data pointer is a DEVICE pointer on the current CUDA device unless marked "host";
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it.  The forward and the
+ *     point integration synchronise that stream once / twice to learn how many (tile, Gaussian)
+ *     pairs exist, exactly where the reference issues its blocking cudaMemcpy
+ *     (rasterizer_impl.cu:384, :676, :743);
+ *   - the caller owns all memory.  Where the reference takes std::function<char*(size_t)> resize
+ *     callbacks (rasterizer.h:30-33) this ABI takes ONE C callback, GgsAllocFn, tagged with the
+ *     buffer slot it is asked to provide.  Buffers handed out in the forward must be passed back
+ *     unchanged (same address, same contents) to the backward;
+ *   - functions return 0 (or a non-negative count) on success and a negative GgsStatus on error;
+ *     ggs_last_error() gives the message for the calling thread;
+ *   - tensors use the reference's layouts: means3D [P,3], scales [P,3], rotations [P,4] (r,x,y,z),
+ *     opacities [P], shs [P,sh_coeffs,3], sg_axis [P,sg_lobes,3], sg_sharpness [P,sg_lobes],
+ *     sg_color [P,sg_lobes,3], images channel-major [C,H,W]; viewmatrix / projmatrix are the
+ *     transposed 4x4 matrices the reference's cameras hold (scene/cameras.py:70-72).
+ *   - precomputed 3D covariances are not supported: the reference's own kernel cannot consume them
+ *     (render_forward.cu:344-345 dereferences scales+idx unconditionally).
+ */
+#ifndef GGS_RASTERIZER_H_
+#define GGS_RASTERIZER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGS_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define GGS_API __attribute__((visibility("default")))
+#else
+#define GGS_API
+#endif
+
+typedef enum GgsStatus {
+    GGS_OK = 0,
+    GGS_ERR_INVALID_ARGUMENT = -1,
+    GGS_ERR_CUDA = -2,
+    GGS_ERR_ALLOC = -3,
+    GGS_ERR_UNSUPPORTED = -4
+} GgsStatus;
+
+/* Workspace slots requested through GgsAllocFn (the reference's geometryBuffer, binningBuffer,
+ * imageBuffer, tileBuffer, pointBuffer, point_binningBuffer resize lambdas). */
+typedef enum GgsSlot {
+    GGS_SLOT_GEOMETRY = 0,
+    GGS_SLOT_BINNING = 1,
+    GGS_SLOT_IMAGE = 2,
+    GGS_SLOT_TILE = 3,
+    GGS_SLOT_POINT = 4,
+    GGS_SLOT_POINT_BINNING = 5,
+    GGS_SLOT_BACKWARD = 6
+} GgsSlot;
+
+/* Must return a device pointer to at least `bytes` bytes aligned to 256, or NULL on failure. */
+typedef void* (*GgsAllocFn)(int slot, size_t bytes, void* user);
+
+/* One camera / image (GaussianRasterizationSettings, DGR/diff_gaussian_rasterization/__init__.py:254-269). */
+typedef struct GgsFrame {
+    int32_t image_width;
+    int32_t image_height;
+    float tanfovx;
+    float tanfovy;
+    float kernel_size;
+    float scale_modifier;
+    int32_t sh_degree;     /* active SH degree, 0..3 */
+    int32_t sg_degree;     /* active spherical-Gaussian lobes */
+    int32_t prefiltered;   /* accepted for signature parity; culled Gaussians are simply skipped */
+    int32_t require_depth; /* 0: colour + alpha only, depth and normal outputs are left untouched */
+    int32_t debug;         /* 1: synchronise and report CUDA errors after every stage */
+    const float* viewmatrix; /* [16] */
+    const float* projmatrix; /* [16] */
+    const float* campos;     /* [3]  */
+    const float* background; /* [3]  */
+} GgsFrame;
+
+/* The Gaussian model as handed to GaussianRasterizer.forward. */
+typedef struct GgsGaussians {
+    int64_t count;               /* P */
+    const float* means3D;        /* [P,3] */
+    const float* opacities;      /* [P]   */
+    const float* scales;         /* [P,3] */
+    const float* rotations;      /* [P,4] */
+    const float* shs;            /* [P,sh_coeffs,3] or NULL */
+    int32_t sh_coeffs;           /* allocated coefficients per Gaussian (SHM) */
+    const float* sg_axis;        /* [P,sg_lobes,3] or NULL */
+    const float* sg_sharpness;   /* [P,sg_lobes]   or NULL */
+    const float* sg_color;       /* [P,sg_lobes,3] or NULL */
+    int32_t sg_lobes;            /* allocated lobes per Gaussian (SGM) */
+    const float* colors_precomp; /* [P,3] or NULL; exactly one of shs / colors_precomp */
+} GgsGaussians;
+
+typedef struct GgsForwardOutputs {
+    float* color;   /* [3,H,W] */
+    float* alpha;   /* [1,H,W] */
+    float* normal;  /* [3,H,W] written only when require_depth */
+    float* mdepth;  /* [1,H,W] written only when require_depth */
+    int32_t* radii; /* [P] */
+} GgsForwardOutputs;
+
+/* What the forward handed out and the backward needs again. */
+typedef struct GgsForwardState {
+    void* geometry;
+    void* binning;
+    void* image;
+    void* tile;
+    int64_t num_rendered;
+} GgsForwardState;
+
+typedef struct GgsBackwardInputs {
+    const float* alpha;      /* forward outputs */
+    const float* normal;
+    const float* mdepth;
+    const int32_t* radii;
+    const float* dL_dcolor;  /* [3,H,W] */
+    const float* dL_dmdepth; /* [1,H,W] */
+    const float* dL_dalpha;  /* [1,H,W] */
+    const float* dL_dnormal; /* [3,H,W] */
+} GgsBackwardInputs;
+
+/* Every row of every tensor is written (zeros for culled Gaussians); no pre-zeroing needed. */
+typedef struct GgsGradients {
+    float* dL_dmeans3D;      /* [P,3] */
+    float* dL_dmeans2D;      /* [P,3] (x, y, |x|+|y|) */
+    float* dL_dcolors;       /* [P,3] */
+    float* dL_dopacity;      /* [P]   */
+    float* dL_dscales;       /* [P,3] */
+    float* dL_drotations;    /* [P,4] */
+    float* dL_dsh;           /* [P,sh_coeffs,3] or NULL */
+    float* dL_dsg_axis;      /* [P,sg_lobes,3]  or NULL */
+    float* dL_dsg_sharpness; /* [P,sg_lobes]    or NULL */
+    float* dL_dsg_color;     /* [P,sg_lobes,3]  or NULL */
+} GgsGradients;
+
+GGS_API int ggs_abi_version(void);
+GGS_API const char* ggs_last_error(void);
+
+/* Forward.  Returns num_rendered (>= 0) or a negative GgsStatus.  `state` receives the buffers. */
+GGS_API int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user,
+                              const GgsForwardOutputs* out, GgsForwardState* state, void* stream);
+
+/* Backward of ggs_rasterize_forward; asks `alloc` for GGS_SLOT_BACKWARD scratch. */
+GGS_API int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                           const GgsBackwardInputs* in, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                           void* stream);
+
+/* Transmittance of query points seen from `frame` (integrate): out_transmittance [PN] and
+ * inside [PN] (uint8 0/1) must be zero-initialised by the caller.  Returns num_rendered. */
+GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                             int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
+                             uint8_t* inside, void* stream);
+
+/* present[i] = 1 iff Gaussian i passes the near-plane test. */
+GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* ---- introspection for tests: byte offsets of the arrays inside the opaque workspaces ---------- */
+typedef struct GgsLayout {
+    uint64_t geometry_bytes, records, depths, tiles_touched, point_offsets, clamped, rects;
+    uint64_t binning_bytes, sorted_keys, point_list, unsorted_keys, unsorted_list;
+    uint64_t tile_bytes, ranges, max_contributor;
+    uint64_t image_bytes, n_contrib;
+    uint32_t sort_bits, sort_passes;
+} GgsLayout;
+GGS_API int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_rendered, GgsLayout* layout);
+
+/* Stand-alone stable radix sort of (u64 key, u32 value) pairs on bits [begin_bit, end_bit) -- the
+ * replacement for cub::DeviceRadixSort::SortPairs at rasterizer_impl.cu:406-412.  `scratch` must
+ * hold ggs_sort_scratch_bytes(n, begin_bit, end_bit) bytes.  Results land in keys_out / vals_out. */
+GGS_API size_t ggs_sort_scratch_bytes(int64_t n, int32_t begin_bit, int32_t end_bit);
+GGS_API int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   int64_t n, int32_t begin_bit, int32_t end_bit, void* scratch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGS_RASTERIZER_H_ */
