@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""Forward+backward throughput of the Gaussian rasterizer hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3]
+
+One "step" = GaussianRasterizer.forward + autograd backward of one view (colour, median depth, alpha
+and normal all carry upstream gradients) on the workload BASELINE.json quotes the metric on:
+1 M Gaussians, 1237x822, SH degree 3, require_depth=True, synthetic seeded scene (scenes.py "c3").
+
+  value  fwd+bwd iters/s with every input resident in HBM (whole job: sum over ranks).
+  e2e    same step through the Python surface, plus per-step host<->device traffic of what changes
+         every training iteration: camera + background + the four upstream-gradient images (stand-in for
+         the ground-truth image of the loss) copied H2D from pinned memory, the rendered colour image
+         and a gradient checksum copied D2H.  The Gaussian parameters are the model and stay resident,
+         exactly as in the reference's train.py.
+  N > 1  one process per GPU; rank r renders view r of an N-view batch of the same scene and the
+         parameter gradients are summed with one NCCL all-reduce inside the timed region (weak scaling).
+  --impl reference   the UNMODIFIED reference CUDA rasterizer compiled into oracle/_ref (the reference
+         has no CPU implementation of this path); same scene, same step, same timing.  Under torchrun
+         rank 0 alone runs it.
+  cpu_baseline       the C restatement (oracle/, OpenMP) timed on the host cores on a bounded sample.
+
+Timing: CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks.  The
+working set (236 MB parameters + >500 MB binning buffers per step) exceeds the 126 MB L2, so no explicit
+flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "geometry-grounded-gaussian-splatting_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+import scenes  # noqa: E402
+
+METRIC = "fwd+bwd iters/s (1M Gaussians, 1237x822, SH3, depth+normal)"
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", d
+    return 6650.0, "fallback (B200_PROFILING.md)", {}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def make_view(workload, rank, world):
+    """View `rank` of a `world`-view batch; the Gaussians are identical on every rank."""
+    n_views = max(world, 1)
+    return scenes.make_scene(workload, view=rank, n_views=n_views if n_views > 1 else 1)
+
+
+class Step:
+    """One training-style iteration through a module with the reference's Python surface."""
+
+    def __init__(self, mod, sc, device, allreduce=False):
+        self.mod, self.sc, self.device, self.allreduce = mod, sc, device, allreduce
+        c = sc.cam
+        dev = device
+        self.params = {}
+        for k in ("means3D", "opacities", "scales", "rotations", "shs"):
+            self.params[k] = getattr(sc, k).to(dev).requires_grad_(True)
+        self.means2D = torch.zeros(sc.P, 3, device=dev, requires_grad=True)
+        # the reference binding needs tensors here even with sg_degree 0 (gaussian_renderer always passes them)
+        self.sg = [t.to(dev) for t in (sc.sg_axis, sc.sg_sharpness, sc.sg_color)]
+        self.cam_dev = dict(view=c.viewmatrix.to(dev), proj=c.projmatrix.to(dev), campos=c.campos.to(dev),
+                            bg=sc.bg.to(dev))
+        self.grads_dev = {k: v.to(dev) for k, v in sc.grads.items()}
+        # host staging for the end-to-end variant
+        self.cam_host = {k: v.cpu().pin_memory() for k, v in self.cam_dev.items()}
+        self.grads_host = {k: v.cpu().pin_memory() for k, v in sc.grads.items()}
+        self.color_host = torch.empty(3, c.H, c.W).pin_memory()
+        self.check_host = torch.empty(1).pin_memory()
+        self.h2d_bytes = sum(v.numel() * 4 for v in self.cam_host.values()) + \
+            sum(v.numel() * 4 for v in self.grads_host.values())
+        self.d2h_bytes = self.color_host.numel() * 4 + 4
+        self.flat = None
+
+    def _settings(self, cam):
+        c = self.sc.cam
+        return self.mod.GaussianRasterizationSettings(
+            image_height=c.H, image_width=c.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy,
+            kernel_size=self.sc.kernel_size, bg=cam["bg"], scale_modifier=1.0, viewmatrix=cam["view"],
+            projmatrix=cam["proj"], sh_degree=self.sc.sh_degree, sg_degree=0, campos=cam["campos"],
+            prefiltered=False, require_depth=True, debug=False)
+
+    def _fwd_bwd(self, cam, g):
+        p = self.params
+        for v in p.values():
+            v.grad = None
+        self.means2D.grad = None
+        rast = self.mod.GaussianRasterizer(self._settings(cam))
+        color, radii, mdepth, alpha, normal = rast(
+            means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"], sg_axis=self.sg[0],
+            sg_sharpness=self.sg[1], sg_color=self.sg[2], colors_precomp=None, scales=p["scales"], rotations=p["rotations"],
+            cov3D_precomp=None)
+        torch.autograd.backward([color, mdepth, alpha, normal], [g["color"], g["mdepth"], g["alpha"], g["normal"]])
+        if self.allreduce:
+            import torch.distributed as dist
+
+            grads = [p[k].grad.reshape(-1) for k in ("means3D", "opacities", "scales", "rotations", "shs")]
+            if self.flat is None:
+                self.flat = torch.empty(sum(x.numel() for x in grads), device=self.device)
+            torch.cat(grads, out=self.flat)
+            dist.all_reduce(self.flat)
+        return color
+
+    def resident(self):
+        self._fwd_bwd(self.cam_dev, self.grads_dev)
+
+    def end_to_end(self):
+        cam = {k: v.to(self.device, non_blocking=True) for k, v in self.cam_host.items()}
+        g = {k: v.to(self.device, non_blocking=True) for k, v in self.grads_host.items()}
+        color = self._fwd_bwd(cam, g)
+        self.color_host.copy_(color.detach(), non_blocking=True)
+        self.check_host.copy_(self.params["means3D"].grad.abs().sum().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+
+def timed(fn, steps, warmup, world, sampler=None):
+    import torch.distributed as dist
+
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms, clocks
+
+
+def algorithmic(sc_stats):
+    """Algorithmic bytes per launch of each stage; P, V, D, tiles, npix from the run."""
+    P, V, D, Tn, N = (sc_stats[k] for k in ("P", "visible", "num_rendered", "tiles", "npix"))
+    c, bits = 16, sc_stats["sort_bits"]
+    r = (bits + 7) // 8
+    return {
+        "preprocess": 12 * P + V * (32 + 12 * c) + 8 * P + 71 * V,
+        "scan": 8 * P,
+        "duplicate": 20 * V + 12 * D,
+        "sort": 8 * D + r * 24 * D,
+        "ranges": 8 * D + 8 * Tn,
+        "render_forward": 68 * D + 36 * N,
+        "render_backward": 68 * D + 56 * N + 68 * V,
+        "gaussian_backward": V * (32 + 12 * c + 68) + P * (12 + 12 + 12 + 4 + 12 + 16 + 12 * c),
+    }
+
+
+def cpu_baseline(seconds_budget=20.0):
+    """C restatement (oracle/) on the host cores: forward+backward of the c1 plumbing config."""
+    from oracle.oracle import Oracle, scene_kwargs
+
+    sc = scenes.make_scene("c1")
+    orc = Oracle()
+    g = sc.grads
+
+    def step():
+        orc.forward(**scene_kwargs(sc))
+        orc.backward(g["color"], g["mdepth"], g["alpha"], g["normal"])
+
+    step()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step()
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > seconds_budget or n >= 200:
+            break
+    its = n / dt
+    mpix = its * sc.cam.W * sc.cam.H / 1e6
+    return {"value": its, "unit": "iters/s", "mpix_per_s": mpix, "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{n} fwd+bwd iterations of config c1 (10k Gaussians, 256x256, SH3) through the C oracle "
+                      f"with OpenMP on {os.cpu_count()} host threads; the reference has no CPU path"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank, world, local = dist_env()
+    if args.impl == "reference" and rank != 0:
+        return 0
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    multi = world > 1 and args.impl == "ours"
+    if multi:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=device)
+
+    if args.impl == "ours":
+        import diff_gaussian_rasterization as mod
+        from diff_gaussian_rasterization import _abi
+    else:
+        from oracle import ref_loader
+
+        if not ref_loader.available():
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_dgr/_C.so not built "
+                              "(needs /root/reference at build time)"}))
+            return 0
+        mod = ref_loader.load()
+        _abi = None
+
+    sc = make_view(args.workload, rank if multi else 0, world if multi else 1)
+    step = Step(mod, sc, device, allreduce=multi)
+    c = sc.cam
+    npix = c.W * c.H
+
+    # ---- device-resident throughput, with per-stage event timing on our arm ----
+    if _abi is not None:
+        _abi.profile_enable(True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, clocks = timed(step.resident, args.steps, args.warmup, world if multi else 1, sampler)
+    stages = None
+    if _abi is not None:
+        # stage times of the last timed iteration plus a few more for an average
+        acc = {}
+        reps = 5
+        for _ in range(reps):
+            step.resident()
+            t = _abi.profile_read()
+            for k, v in t.items():
+                acc[k] = acc.get(k, 0.0) + float(v)
+        stages = {k[:-3]: acc[k] / reps for k in acc if k.endswith("_ms")}
+        _abi.profile_enable(False)
+    n_ranks = world if multi else 1
+    ms_per_step = ms / args.steps
+    value = n_ranks * 1000.0 / ms_per_step
+
+    # ---- end to end ----
+    ms_e2e, _ = timed(step.end_to_end, args.steps, args.warmup, world if multi else 1, None)
+    e2e_value = n_ranks * 1000.0 / (ms_e2e / args.steps)
+
+    if rank != 0:
+        if multi:
+            torch.distributed.destroy_process_group()
+        return 0
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "iters/s", "n_gpus": n_ranks, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "mpix_per_s": value * npix / 1e6,
+        "config": {"workload": f"{args.workload}: {sc.P} Gaussians, {c.W}x{c.H}, SH{sc.sh_degree}, "
+                               "require_depth=True, one view per rank",
+                   "views_per_step": n_ranks, "parallelism": f"view-parallel x{n_ranks}" if multi else "single GPU",
+                   "l2": "working set (>700 MB per step) exceeds the 126 MB L2; no explicit flush"},
+        "e2e": {"value": e2e_value, "unit": "iters/s", "h2d_bytes_per_step": step.h2d_bytes,
+                "d2h_bytes_per_step": step.d2h_bytes},
+        "clocks": clocks,
+    }
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["gpu_launches"] = 0
+        line["cpu_baseline"] = {"value": value, "unit": "iters/s", "cores": 0, "kind": "reference",
+                                "sample": "the reference CUDA rasterizer (oracle/_ref, unmodified sources, sm_100) "
+                                          "on one B200: it has no CPU implementation; same scene and step as ours"}
+    else:
+        hbm, how, _ = peaks()
+        # launches of OUR kernels per fwd+bwd step (counted from the stage sequence in ggs_api.cu):
+        # preprocess, scan, duplicate, histogram, offsets, 6 onesweep passes, ranges, render fwd, render bwd,
+        # gaussian bwd
+        outs, inter = None, None
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import helpers as H
+
+        outs, inter = H.ours_forward_raw(sc, str(device))
+        stats = {"P": sc.P, "visible": int((outs["radii"] > 0).sum()), "num_rendered": inter["num_rendered"],
+                 "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
+        passes = (stats["sort_bits"] + 7) // 8
+        line["gpu_launches"] = args.steps * (3 + 2 + passes + 1 + 1 + 2)
+        alg = algorithmic(stats)
+        per_stage = {}
+        for k, b in alg.items():
+            t = stages.get(k)
+            if t:
+                per_stage[k] = {"ms": t, "alg_bytes": b, "gbs": b / t / 1e6, "frac_hbm": b / t / 1e6 / hbm}
+        dom = max(per_stage, key=lambda k: per_stage[k]["ms"])
+        line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": per_stage[dom]["gbs"], "peak": hbm,
+                            "unit": "GB/s", "frac": per_stage[dom]["frac_hbm"], "traffic": None,
+                            "peak_source": how,
+                            "note": "render kernels are issue-bound (MUFU/FP32), not HBM-bound; see DESIGN.md "
+                                    "and profiles/ for pipe utilisation"}
+        line["stages"] = per_stage
+        line["scene"] = stats
+        if not args.no_cpu_baseline and not multi:
+            line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line))
+    if multi:
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

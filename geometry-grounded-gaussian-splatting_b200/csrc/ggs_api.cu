@@ -35,6 +35,25 @@ int fail(int code, const std::string& msg) {
             return fail(GGS_ERR_CUDA, std::string("stage ") + name + ": " + cudaGetErrorString(e__)); \
     } while (0)
 
+// ---- optional per-stage device timing (ggs_profile_enable / ggs_profile_read) -------------------
+enum { EV_F0, EV_PRE, EV_SCAN, EV_DUP0, EV_DUP, EV_SORT, EV_RANGES, EV_RENDER, EV_B0, EV_RBWD, EV_GBWD, EV_COUNT };
+struct Profiler {
+    bool on = false;
+    bool have_fwd = false, have_bwd = false;
+    cudaEvent_t ev[EV_COUNT] = {};
+    bool created = false;
+};
+thread_local Profiler g_prof;
+
+void prof_mark(cudaStream_t s, int which) {
+    if (!g_prof.on) return;
+    if (!g_prof.created) {
+        for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&g_prof.ev[i]);
+        g_prof.created = true;
+    }
+    cudaEventRecord(g_prof.ev[which], s);
+}
+
 uint32_t* pinned_word() {
     if (!g_pinned) {
         if (cudaMallocHost(&g_pinned, 64) != cudaSuccess) g_pinned = nullptr;
@@ -106,14 +125,17 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
                   uint2* ranges, GgsAllocFn alloc, void* user, void** bin, int64_t* D_out, bool debug,
                   cudaStream_t stream) {
     const GeomLayout GL = geom_layout(fp.P);
+    prof_mark(stream, EV_F0);
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
                       at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
                       at<uint8_t>(geom, GL.clamped), radii, stream);
     GGS_STAGE("preprocess", debug, stream);
+    prof_mark(stream, EV_PRE);
     launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
                 at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter),
                 at<uint32_t>(geom, GL.total), stream);
     GGS_STAGE("scan", debug, stream);
+    prof_mark(stream, EV_SCAN);
     uint32_t* host = pinned_word();
     if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
     GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(geom, GL.total), 4, cudaMemcpyDeviceToHost, stream));
@@ -129,18 +151,22 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
     if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
     *bin = b;
+    prof_mark(stream, EV_DUP0);
     launch_duplicate_keys(fp.P, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
                           at<float>(geom, GL.depths), fp.gx, at<uint64_t>(b, BL.keys_a), at<uint32_t>(b, BL.vals_a),
                           D, stream);
     GGS_STAGE("duplicate_keys", debug, stream);
+    prof_mark(stream, EV_DUP);
     const int where = launch_radix_sort(at<uint64_t>(b, BL.keys_a), at<uint64_t>(b, BL.keys_b),
                                         at<uint32_t>(b, BL.vals_a), at<uint32_t>(b, BL.vals_b), D, 0, end_bit,
                                         at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), BL.status_bytes,
                                         at<uint32_t>(b, BL.counters), stream);
     GGS_STAGE("radix_sort", debug, stream);
+    prof_mark(stream, EV_SORT);
     const uint64_t* sorted_keys = where ? at<uint64_t>(b, BL.keys_b) : at<uint64_t>(b, BL.keys_a);
     launch_tile_ranges(sorted_keys, D, ranges, tiles, stream);
     GGS_STAGE("tile_ranges", debug, stream);
+    prof_mark(stream, EV_RANGES);
     return GGS_OK;
 }
 
@@ -218,6 +244,8 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, D, tiles),
                           at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
     GGS_STAGE("render_forward", debug, stream);
+    prof_mark(stream, EV_RENDER);
+    g_prof.have_fwd = g_prof.on;
     return D;
 }
 
@@ -250,6 +278,7 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     const size_t acc_bytes = (size_t)fp.P * GRAD_STRIDE * 4;
     float* acc = static_cast<float*>(alloc(GGS_SLOT_BACKWARD, acc_bytes, user));
     if (!acc) return fail(GGS_ERR_ALLOC, "backward workspace allocation failed");
+    prof_mark(stream, EV_B0);
     GGS_CUDA(cudaMemsetAsync(acc, 0, acc_bytes, stream));
 
     RenderBwdIn ri;
@@ -265,6 +294,7 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     launch_render_backward(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state->num_rendered, tiles),
                            at<SplatRecord>(state->geometry, GL.records), ri, acc, frame->require_depth != 0, stream);
     GGS_STAGE("render_backward", debug, stream);
+    prof_mark(stream, EV_RBWD);
 
     GaussianGrads gg;
     gg.dL_dmeans3D = grads->dL_dmeans3D;
@@ -280,6 +310,8 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
     launch_gaussian_backward(fp, in, bi->radii, at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
     GGS_STAGE("gaussian_backward", debug, stream);
+    prof_mark(stream, EV_GBWD);
+    g_prof.have_bwd = g_prof.on;
     return GGS_OK;
 }
 
@@ -366,6 +398,38 @@ int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussian
                      at<float2>(pts, p_xy), at<float>(pts, p_depth), out_transmittance, inside, stream);
     GGS_STAGE("integrate", debug, stream);
     return D;
+}
+
+int ggs_profile_enable(int on) {
+    g_prof.on = on != 0;
+    g_prof.have_fwd = g_prof.have_bwd = false;
+    return GGS_OK;
+}
+
+int ggs_profile_read(GgsStageTimes* t) {
+    if (!t) return fail(GGS_ERR_INVALID_ARGUMENT, "null stage-time struct");
+    *t = GgsStageTimes{};
+    auto span = [&](int a, int b, float* out) -> int {
+        GGS_CUDA(cudaEventSynchronize(g_prof.ev[b]));
+        GGS_CUDA(cudaEventElapsedTime(out, g_prof.ev[a], g_prof.ev[b]));
+        return GGS_OK;
+    };
+    int rc = GGS_OK;
+    if (g_prof.have_fwd) {
+        if ((rc = span(EV_F0, EV_PRE, &t->preprocess_ms))) return rc;
+        if ((rc = span(EV_PRE, EV_SCAN, &t->scan_ms))) return rc;
+        if ((rc = span(EV_DUP0, EV_DUP, &t->duplicate_ms))) return rc;
+        if ((rc = span(EV_DUP, EV_SORT, &t->sort_ms))) return rc;
+        if ((rc = span(EV_SORT, EV_RANGES, &t->ranges_ms))) return rc;
+        if ((rc = span(EV_RANGES, EV_RENDER, &t->render_forward_ms))) return rc;
+        t->have_forward = 1;
+    }
+    if (g_prof.have_bwd) {
+        if ((rc = span(EV_B0, EV_RBWD, &t->render_backward_ms))) return rc;
+        if ((rc = span(EV_RBWD, EV_GBWD, &t->gaussian_backward_ms))) return rc;
+        t->have_backward = 1;
+    }
+    return GGS_OK;
 }
 
 int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,

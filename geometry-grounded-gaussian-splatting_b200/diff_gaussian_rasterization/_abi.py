@@ -67,11 +67,17 @@ class GgsLayout(C.Structure):
         ("sort_bits", C.c_uint32), ("sort_passes", C.c_uint32)]
 
 
+class GgsStageTimes(C.Structure):
+    _fields_ = [("have_forward", C.c_int32), ("have_backward", C.c_int32)] + [(n, C.c_float) for n in (
+        "preprocess_ms", "scan_ms", "duplicate_ms", "sort_ms", "ranges_ms", "render_forward_ms",
+        "render_backward_ms", "gaussian_backward_ms")]
+
+
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
-           "ggs_sort_pairs")
+           "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
 
 
 def _load():
@@ -101,6 +107,10 @@ def _load():
     lib.ggs_sort_pairs.restype = C.c_int
     lib.ggs_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                    C.c_void_p, C.c_void_p]
+    lib.ggs_profile_enable.restype = C.c_int
+    lib.ggs_profile_enable.argtypes = [C.c_int]
+    lib.ggs_profile_read.restype = C.c_int
+    lib.ggs_profile_read.argtypes = [C.POINTER(GgsStageTimes)]
     if lib.ggs_abi_version() != 1:
         raise ImportError("libggs_rasterizer.so has an unexpected ABI version")
     return lib
@@ -149,6 +159,16 @@ class Arena:
 
 def stream_handle(device) -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def profile_enable(on: bool) -> None:
+    check(lib.ggs_profile_enable(1 if on else 0), "ggs_profile_enable")
+
+
+def profile_read() -> dict:
+    t = GgsStageTimes()
+    check(lib.ggs_profile_read(C.byref(t)), "ggs_profile_read")
+    return {n: getattr(t, n) for n, _ in GgsStageTimes._fields_}
 
 
 def describe_layout(P: int, W: int, H: int, num_rendered: int) -> GgsLayout:

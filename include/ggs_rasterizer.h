@@ -171,6 +171,19 @@ GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* 
 GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
 
+/* ---- optional per-stage device timing ------------------------------------------------------------
+ * When enabled (per calling thread) the forward / backward record CUDA events on the caller's stream
+ * between stages; ggs_profile_read waits for the events of the most recent forward and backward and
+ * returns the stage durations in milliseconds.  The reference has no counterpart (its only timing is
+ * the torch.cuda.Event pair in train.py:63-64); bench.py uses this for the per-kernel roofline. */
+typedef struct GgsStageTimes {
+    int32_t have_forward, have_backward;
+    float preprocess_ms, scan_ms, duplicate_ms, sort_ms, ranges_ms, render_forward_ms;
+    float render_backward_ms, gaussian_backward_ms;
+} GgsStageTimes;
+GGS_API int ggs_profile_enable(int on);
+GGS_API int ggs_profile_read(GgsStageTimes* times);
+
 /* ---- introspection for tests: byte offsets of the arrays inside the opaque workspaces ---------- */
 typedef struct GgsLayout {
     uint64_t geometry_bytes, records, depths, tiles_touched, point_offsets, clamped, rects;

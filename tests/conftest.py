@@ -1,0 +1,47 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "geometry-grounded-gaussian-splatting_b200")
+for p in (ROOT, PKG, os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def _lib_built():
+    return os.path.exists(os.path.join(PKG, "diff_gaussian_rasterization", "libggs_rasterizer.so"))
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _native_built():
+    """The product has no fallback: build the library once if the tree is fresh."""
+    if not _lib_built():
+        import subprocess
+
+        subprocess.check_call(["make", "-C", os.path.join(PKG, "csrc"), "-j", "8"])
+    yield
+
+
+@pytest.fixture(scope="session")
+def device():
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return "cuda:0"
+
+
+@pytest.fixture(scope="session")
+def ref_module():
+    """The compiled reference rasterizer (Oracle A); None when oracle/_ref was not shipped."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        return None
+    return ref_loader.load()

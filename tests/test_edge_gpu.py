@@ -1,0 +1,142 @@
+"""Edge cases of the drop-in surface on the GPU: empty / fully culled inputs, require_depth=False,
+precomputed colours, ragged image sizes, markVisible, error behaviour."""
+import pytest
+import torch
+
+import helpers as H
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def _rast(sc, device, **kw):
+    import diff_gaussian_rasterization as ours
+
+    return ours, ours.GaussianRasterizer(H.settings_for(ours, sc, device, **kw))
+
+
+def test_empty_scene(device):
+    sc = scenes.make_scene("tiny", P=0)
+    sc.bg = torch.tensor([0.1, 0.2, 0.3])
+    ours, r = _rast(sc, device)
+    m = torch.zeros(0, 3, device=device, requires_grad=True)
+    color, radii, mdepth, alpha, normal = r(m, torch.zeros(0, 3, device=device), torch.zeros(0, 1, device=device),
+                                            shs=torch.zeros(0, 16, 3, device=device),
+                                            scales=torch.zeros(0, 3, device=device),
+                                            rotations=torch.zeros(0, 4, device=device))
+    assert radii.numel() == 0 and color.shape == (3, sc.cam.H, sc.cam.W)
+    # rasterize_points.cu:95: with P == 0 nothing runs and the zero-initialised outputs come back
+    assert float(color.abs().max()) == 0 and float(alpha.abs().max()) == 0 and float(mdepth.abs().max()) == 0
+
+
+def test_everything_culled(device):
+    sc = scenes.make_scene("tiny", P=500)
+    sc.means3D[:, 2] = -10.0
+    sc.bg = torch.tensor([0.25, 0.5, 0.75])
+    import diff_gaussian_rasterization as ours
+
+    out, g = H.run_module(ours, sc, device)
+    assert int(out["radii"].abs().sum()) == 0
+    assert torch.allclose(out["color"][2], torch.full_like(out["color"][2], 0.75))
+    assert float(out["alpha"].abs().max()) == 0 and float(out["normal"].abs().max()) == 0
+    for k in ("means3D", "opacities", "scales", "rotations", "shs", "means2D"):
+        assert float(g[k].abs().max()) == 0, k
+
+
+def test_require_depth_false_leaves_geometry_zero(device):
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("c1")
+    a, _ = H.run_module(ours, sc, device, require_depth=False)
+    b, _ = H.run_module(ours, sc, device, require_depth=True)
+    assert float(a["mdepth"].abs().max()) == 0 and float(a["normal"].abs().max()) == 0
+    assert torch.equal(a["color"], b["color"]) and torch.equal(a["alpha"], b["alpha"])
+    assert torch.equal(a["radii"], b["radii"])
+
+
+def test_colors_precomp_path(device, ref_module):
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("tiny")
+    cols = torch.rand(sc.P, 3, generator=torch.Generator().manual_seed(3))
+
+    def run(mod):
+        rs = H.settings_for(mod, sc, device)
+        x = H.leaf_inputs(sc, device)
+        cp = cols.to(device).requires_grad_(True)
+        r = mod.GaussianRasterizer(rs)
+        color, radii, mdepth, alpha, normal = r(
+            means3D=x["means3D"], means2D=x["means2D"], opacities=x["opacities"], shs=None, sg_axis=x["sg_axis"],
+            sg_sharpness=x["sg_sharpness"], sg_color=x["sg_color"], colors_precomp=cp, scales=x["scales"],
+            rotations=x["rotations"], cov3D_precomp=None)
+        g = {k: v.to(device) for k, v in sc.grads.items()}
+        ((color * g["color"]).sum() + (alpha * g["alpha"]).sum() + (mdepth * g["mdepth"]).sum()).backward()
+        return color.detach(), cp.grad.detach(), x["means3D"].grad.detach()
+
+    c, gc, gm = run(ours)
+    assert float(gc.abs().max()) > 0
+    if ref_module is not None:
+        c2, gc2, gm2 = run(ref_module)
+        assert H.image_rel_err(c, c2)[0] <= H.IMG_TOL
+        assert H.grad_rel_err(gc, gc2) <= H.GRAD_TOL and H.grad_rel_err(gm, gm2) <= H.GRAD_TOL
+
+
+@pytest.mark.parametrize("wh", [(1, 1), (17, 5), (16, 16), (33, 47)])
+def test_ragged_image_sizes(wh, device, ref_module):
+    import diff_gaussian_rasterization as ours
+
+    W, Hh = wh
+    sc = scenes.make_scene("tiny", W=W, H=Hh, scale_mult=6.0, seed=W * 100 + Hh)
+    o, g = H.run_module(ours, sc, device)
+    assert o["color"].shape == (3, Hh, W)
+    if ref_module is not None:
+        r, rg = H.run_module(ref_module, sc, device)
+        assert H.int_mismatch(o["radii"], r["radii"]) == 0
+        for k in ("color", "alpha", "mdepth", "normal"):
+            assert H.image_rel_err(o[k], r[k])[0] <= H.IMG_TOL, k
+        for k in H.GRAD_NAMES:
+            assert H.grad_rel_err(g[k], rg[k]) <= H.GRAD_TOL, k
+
+
+def test_mark_visible(device, ref_module):
+    sc = scenes.make_scene("c1")
+    ours, r = _rast(sc, device)
+    m = r.markVisible(sc.means3D.to(device))
+    view = sc.cam.viewmatrix
+    z = sc.means3D @ view[:3, 2] + view[3, 2]
+    assert m.dtype == torch.bool
+    # knife-edge points aside, identical to the z > 0.2 test
+    exp = z > 0.2
+    sure = (z - 0.2).abs() > 1e-5
+    assert torch.equal(m.cpu()[sure], exp[sure])
+    if ref_module is not None:
+        rr = ref_module.GaussianRasterizer(H.settings_for(ref_module, sc, device))
+        assert torch.equal(rr.markVisible(sc.means3D.to(device)), m)
+
+
+def test_unsupported_paths_are_loud(device):
+    sc = scenes.make_scene("tiny")
+    ours, r = _rast(sc, device)
+    x = H.leaf_inputs(sc, device)
+    with pytest.raises(NotImplementedError):
+        r(x["means3D"], x["means2D"], x["opacities"], shs=x["shs"], cov3D_precomp=torch.zeros(sc.P, 6, device=device))
+    with pytest.raises(RuntimeError, match="sg_degree"):
+        import diff_gaussian_rasterization as o2
+
+        rs = H.settings_for(o2, sc, device)._replace(sg_degree=3)
+        o2.GaussianRasterizer(rs)(x["means3D"], x["means2D"], x["opacities"], shs=x["shs"], sg_axis=x["sg_axis"],
+                                  sg_sharpness=x["sg_sharpness"], sg_color=x["sg_color"], scales=x["scales"],
+                                  rotations=x["rotations"])
+
+
+def test_non_default_stream_and_noncontiguous_grads(device):
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("tiny")
+    base, gbase = H.run_module(ours, sc, device)
+    s = torch.cuda.Stream(device=device)
+    with torch.cuda.stream(s):
+        out, g = H.run_module(ours, sc, device)
+    s.synchronize()
+    assert torch.equal(base["color"], out["color"])
+    assert H.grad_rel_err(g["means3D"], gbase["means3D"]) < 1e-5
