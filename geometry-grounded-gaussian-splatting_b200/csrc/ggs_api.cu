@@ -43,7 +43,7 @@ struct Profiler {
     cudaEvent_t ev[EV_COUNT] = {};
     bool created = false;
 };
-thread_local Profiler g_prof;
+Profiler g_prof;  // process-wide: autograd runs the backward on its own thread
 
 void prof_mark(cudaStream_t s, int which) {
     if (!g_prof.on) return;

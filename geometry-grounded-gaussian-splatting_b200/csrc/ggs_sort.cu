@@ -27,13 +27,16 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
 }
 
 __global__ void __launch_bounds__(256) histogram_kernel(const uint64_t* __restrict__ keys, uint32_t n,
-                                                        int begin_bit, int passes, uint32_t* __restrict__ hist) {
+                                                        int begin_bit, int end_bit, int passes, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_hist[MAX_PASSES][RADIX];
     for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += blockDim.x) (&s_hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint64_t k = __ldg(keys + i) >> begin_bit;
+        // only bits [begin_bit, end_bit) take part (the last digit may be narrower than 8 bits)
+        uint64_t k = __ldg(keys + i) >> begin_bit;
+        const int width = end_bit - begin_bit;
+        if (width < 64) k &= (1ull << width) - 1ull;
 #pragma unroll
         for (int p = 0; p < MAX_PASSES; p++) {
             if (p < passes) atomicAdd(&s_hist[p][(uint32_t)(k >> (RADIX_BITS * p)) & (RADIX - 1)], 1u);
@@ -73,6 +76,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
                                                                 uint64_t* __restrict__ keys_out,
                                                                 const uint32_t* __restrict__ vals_in,
                                                                 uint32_t* __restrict__ vals_out, uint32_t n, int shift,
+                                                                uint32_t digit_mask,
                                                                 const uint32_t* __restrict__ bin_offsets,
                                                                 uint32_t* __restrict__ status,
                                                                 uint32_t* __restrict__ counter) {
@@ -112,7 +116,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     const uint32_t lanemask_lt = (1u << lane) - 1;
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & (RADIX - 1);
+        const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     // ---- reorder through shared memory, then coalesced digit runs ------------------------------
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const uint32_t dg = (uint32_t)(key[i] >> shift) & (RADIX - 1);
+        const uint32_t dg = (uint32_t)(key[i] >> shift) & digit_mask;
         const uint32_t pos = s_bin_start[dg] + s_warp_hist[warp][dg] + rank[i];
         s_keys[pos] = key[i];
         s_vals[pos] = val[i];
@@ -187,7 +191,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     __syncthreads();
     for (uint32_t p = tid; p < count; p += SORT_THREADS) {
         const uint64_t k = s_keys[p];
-        const uint32_t dg = (uint32_t)(k >> shift) & (RADIX - 1);
+        const uint32_t dg = (uint32_t)(k >> shift) & digit_mask;
         const uint32_t out = s_global_base[dg] + p;
         keys_out[out] = k;
         vals_out[out] = s_vals[p];
@@ -204,14 +208,16 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
     cudaMemsetAsync(status, 0, status_bytes, stream);
     cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
     const int hist_blocks = (int)min((uint32_t)(148 * 8), (n + 255) / 256);
-    histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_a, n, begin_bit, passes, hist);
+    histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_a, n, begin_bit, end_bit, passes, hist);
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
     uint64_t* kin = keys_a;
     uint64_t* kout = keys_b;
     uint32_t* vin = vals_a;
     uint32_t* vout = vals_b;
     for (int p = 0; p < passes; p++) {
-        onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, begin_bit + RADIX_BITS * p,
+        const int shift = begin_bit + RADIX_BITS * p;
+        const int width = end_bit - shift < RADIX_BITS ? end_bit - shift : RADIX_BITS;
+        onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, shift, (1u << width) - 1u,
                                                             hist + p * RADIX, status + (size_t)p * tiles * RADIX,
                                                             counters + p);
         uint64_t* tk = kin;

@@ -172,7 +172,7 @@ GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* v
                      uint8_t* present, void* stream);
 
 /* ---- optional per-stage device timing ------------------------------------------------------------
- * When enabled (per calling thread) the forward / backward record CUDA events on the caller's stream
+ * When enabled (process-wide) the forward / backward record CUDA events on the caller's stream
  * between stages; ggs_profile_read waits for the events of the most recent forward and backward and
  * returns the stage durations in milliseconds.  The reference has no counterpart (its only timing is
  * the torch.cuda.Event pair in train.py:63-64); bench.py uses this for the per-kernel roofline. */
