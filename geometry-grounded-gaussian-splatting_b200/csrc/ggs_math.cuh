@@ -125,6 +125,37 @@ __device__ __forceinline__ float dot(const V3& a, const V3& b) {
 }
 __device__ __forceinline__ V3 normalize(const V3& v) { return v * rsqrtf(dot(v, v)); }
 
+// ---- explicitly rounded float steps --------------------------------------------------------------
+// The intrinsics below are never contracted, reassociated or re-fused by nvcc / ptxas, so an expression
+// written with them evaluates in exactly one way.  The per-Gaussian preprocess uses them to follow the
+// evaluation order of the reference binary (learned with tools/sassflow.py) and so reproduce its geometry
+// records bit for bit; plain `a * b + c` would leave the FMA contraction pattern to the compiler.
+__device__ __forceinline__ float MUL(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float ADD(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float FMA(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// a0*b0 + a1*b1 + a2*b2 as the compiler contracts a three-term dot product:
+// the middle product is rounded first, then two fused steps.
+__device__ __forceinline__ float sop3(float a0, float b0, float a1, float b1, float a2, float b2) {
+    return FMA(a2, b2, FMA(a0, b0, MUL(a1, b1)));
+}
+__device__ __forceinline__ float twice(float w) { return ADD(w, w); }
+__device__ __forceinline__ float one_minus_twice(float w) { return ADD(-ADD(w, w), 1.f); }
+
 // world/view transforms with the reference's term order (auxiliary.h:51-85)
 __device__ __forceinline__ float3 xform_point_4x3(const float3& p, const float* m) {
     return {m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],

@@ -93,85 +93,126 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, c
     const float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
 
     // ---- 2D covariance, ray plane, normal (render_forward.cu:81-243) --------------------------
-    const float focal_x = fp.focal_x, focal_y = fp.focal_y;
-    float3 t = xform_point_4x3(p_orig, viewmatrix);
-    const float tc = norm3df(t.x, t.y, t.z);
+    // Every float operation below is spelled out with an explicit rounding step (ggs_math.cuh: MUL / ADD /
+    // FMA / rcp_approx ...) in the evaluation order the reference binary uses, so conic, opacity, ray plane
+    // and normal come out bit-identical to the reference's geometry buffers (DESIGN.md "bit-exact records").
+    const float fx = fp.focal_x, fy = fp.focal_y;
+    const float v0 = viewmatrix[0], v1 = viewmatrix[1], v2 = viewmatrix[2], v4 = viewmatrix[4], v5 = viewmatrix[5],
+                v6 = viewmatrix[6], v8 = viewmatrix[8], v9 = viewmatrix[9], v10 = viewmatrix[10];
+    const float tx0 = p_view.x, ty0 = p_view.y, tz = p_view.z;
+    const float tc = norm3df(tx0, ty0, tz);  // also the depth key
 
-    const float limx = 1.3f * fp.tanfovx;
-    const float limy = 1.3f * fp.tanfovy;
-    float u = t.x / t.z;
-    float v = t.y / t.z;
-    t.x = fminf(limx, fmaxf(-limx, u)) * t.z;
-    t.y = fminf(limy, fmaxf(-limy, v)) * t.z;
-    u = t.x / t.z;
-    v = t.y / t.z;
+    const float rz = rcp_approx(tz);
+    const float limx = MUL(fp.tanfovx, 1.3f);
+    const float limy = MUL(fp.tanfovy, 1.3f);
+    const float tx = MUL(tz, fminf(limx, fmaxf(-limx, MUL(tx0, rz))));
+    const float ty = MUL(tz, fminf(limy, fmaxf(-limy, MUL(ty0, rz))));
+    const float u = MUL(tx, rz);
+    const float v = MUL(ty, rz);
+    const float r_tz2 = rcp_approx(MUL(tz, tz));
 
-    const M3 J = m3_cols(focal_x / t.z, 0.f, -(focal_x * t.x) / (t.z * t.z), 0.f, focal_y / t.z,
-                         -(focal_y * t.y) / (t.z * t.z), 0.f, 0.f, 0.f);
-    const M3 Wm = m3_cols(viewmatrix[0], viewmatrix[4], viewmatrix[8], viewmatrix[1], viewmatrix[5], viewmatrix[9],
-                          viewmatrix[2], viewmatrix[6], viewmatrix[10]);
-    const M3 T = Wm * J;
+    // J (two non-trivial columns) and T = W * J
+    const float J00 = MUL(rz, fx), J02 = MUL(MUL(tx, -fx), r_tz2);
+    const float J11 = MUL(rz, fy), J12 = MUL(MUL(ty, -fy), r_tz2);
+    const float T00 = FMA(v2, J02, FMA(v0, J00, MUL(0.f, v1)));
+    const float T01 = FMA(v6, J02, FMA(v4, J00, MUL(0.f, v5)));
+    const float T02 = FMA(v10, J02, FMA(v8, J00, MUL(0.f, v9)));
+    const float T10 = FMA(v2, J12, FMA(0.f, v0, MUL(v1, J11)));
+    const float T11 = FMA(v6, J12, FMA(0.f, v4, MUL(v5, J11)));
+    const float T12 = FMA(v10, J12, FMA(0.f, v8, MUL(v9, J11)));
 
     const float mod = fp.scale_modifier;
     const float3 sc = ld3(in.scales, idx);
-    const float scale_local[3] = {mod * sc.x, mod * sc.y, mod * sc.z};
-    const M3 S = m3_diag(scale_local[0], scale_local[1], scale_local[2]);
-    const M3 S_inv = m3_diag(__frcp_rn(scale_local[0]), __frcp_rn(scale_local[1]), __frcp_rn(scale_local[2]));
+    const float s0 = MUL(sc.x, mod), s1 = MUL(sc.y, mod), s2 = MUL(sc.z, mod);
+    const float i0 = __frcp_rn(s0), i1 = __frcp_rn(s1), i2 = __frcp_rn(s2);
 
     const float4 rot = __ldg(reinterpret_cast<const float4*>(in.rotations) + idx);
-    const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
-    const M3 R = m3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                         2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                         2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    const float qr = rot.x, qx = rot.y, qy = rot.z, qz = rot.w;
+    // rotation matrix, R<col><row>
+    const float R00 = one_minus_twice(ADD(MUL(qy, qy), MUL(qz, qz)));
+    const float R11 = one_minus_twice(FMA(qx, qx, MUL(qz, qz)));
+    const float R22 = one_minus_twice(FMA(qx, qx, MUL(qy, qy)));
+    const float R01 = twice(FMA(qx, qy, -MUL(qr, qz)));
+    const float R02 = twice(FMA(qr, qy, MUL(qx, qz)));
+    const float R10 = twice(FMA(qx, qy, MUL(qr, qz)));
+    const float R12 = twice(FMA(qy, qz, -MUL(qr, qx)));
+    const float R20 = twice(FMA(-qr, qy, MUL(qx, qz)));
+    const float R21 = twice(FMA(qy, qz, MUL(qr, qx)));
 
-    const M3 M = S * R * T;
-    const M3 cov = transpose(M) * M;
-    const M3 M_inv = S_inv * R * Wm;
-    const M3 cov_cam_inv = transpose(M_inv) * M_inv;
+    // M = (S R) T, only the two columns that reach the 2D covariance; cov = M^T M
+    const float B00 = MUL(s0, R00), B01 = MUL(s1, R01), B02 = MUL(s2, R02);
+    const float B10 = MUL(s0, R10), B11 = MUL(s1, R11), B12 = MUL(s2, R12);
+    const float B20 = MUL(s0, R20), B21 = MUL(s1, R21), B22 = MUL(s2, R22);
+    const float M00 = sop3(T00, B00, T01, B10, T02, B20);
+    const float M01 = sop3(T00, B01, T01, B11, T02, B21);
+    const float M02 = sop3(T00, B02, T01, B12, T02, B22);
+    const float M10 = sop3(T10, B00, T11, B10, T12, B20);
+    const float M11 = sop3(T10, B01, T11, B11, T12, B21);
+    const float M12 = sop3(T10, B02, T11, B12, T12, B22);
+    const float cov00 = sop3(M00, M00, M01, M01, M02, M02);
+    const float cov01 = sop3(M00, M10, M01, M11, M02, M12);
+    const float cov11 = sop3(M10, M10, M11, M11, M12, M12);
 
-    const float kernel_size = fp.kernel_size;
-    const float cov2D0 = float(cov.c[0][0] + kernel_size);
-    const float cov2D1 = float(cov.c[0][1]);
-    const float cov2D2 = float(cov.c[1][1] + kernel_size);
-    const float det_0 = fmaxf(1e-6f, cov.c[0][0] * cov.c[1][1] - cov.c[0][1] * cov.c[0][1]);
-    const float det_1 =
-        fmaxf(1e-6f, (cov.c[0][0] + kernel_size) * (cov.c[1][1] + kernel_size) - cov.c[0][1] * cov.c[0][1]);
-    const float coef = sqrtf(det_0 / det_1);
+    // camera-space inverse covariance  C = Minv^T Minv,  Minv = (S^-1 R) W
+    const float A00 = MUL(i0, R00), A01 = MUL(i1, R01), A02 = MUL(i2, R02);
+    const float A10 = MUL(i0, R10), A11 = MUL(i1, R11), A12 = MUL(i2, R12);
+    const float A20 = MUL(i0, R20), A21 = MUL(i1, R21), A22 = MUL(i2, R22);
+    const float N00 = sop3(v0, A00, v4, A10, v8, A20), N01 = sop3(v0, A01, v4, A11, v8, A21),
+                N02 = sop3(v0, A02, v4, A12, v8, A22);
+    const float N10 = sop3(v1, A00, v5, A10, v9, A20), N11 = sop3(v1, A01, v5, A11, v9, A21),
+                N12 = sop3(v1, A02, v5, A12, v9, A22);
+    const float N20 = sop3(v2, A00, v6, A10, v10, A20), N21 = sop3(v2, A01, v6, A11, v10, A21),
+                N22 = sop3(v2, A02, v6, A12, v10, A22);
+    const float C00 = sop3(N00, N00, N01, N01, N02, N02);
+    const float C10 = sop3(N00, N10, N01, N11, N02, N12);
+    const float C11 = sop3(N10, N10, N11, N11, N12, N12);
+    const float C20 = sop3(N00, N20, N01, N21, N02, N22);
+    const float C21 = sop3(N10, N20, N11, N21, N12, N22);
+    const float C22 = sop3(N20, N20, N21, N21, N22, N22);
 
-    const V3 uvh = {u, v, 1.f};
-    const V3 uvh_m = cov_cam_inv * uvh;
+    // Mip 2D filter
+    const float ks = fp.kernel_size;
+    const float ca = ADD(cov00, ks), cc = ADD(cov11, ks), cb = cov01;
+    const float cb2 = MUL(cb, cb);
+    const float det = FMA(ca, cc, -cb2);
+    const float det_0 = fmaxf(FMA(cov11, cov00, -cb2), 1e-6f);
+    const float det_1 = fmaxf(det, 1e-6f);
+    const float coef = sqrt_approx(MUL(det_0, rcp_approx(det_1)));
 
     float4 ray_plane;
     float3 normal;
     {
-        const float u2 = u * u, v2 = v * v, uv = u * v;
-        const float l = norm3df(t.x, t.y, t.z);
-        const M3 nJ_inv = m3_cols(v2 + 1, -uv, 0, -uv, u2 + 1, 0, -u, -v, 0);
-        const float vb = dot(uvh_m, uvh);
-        const float ray_len2 = u2 + v2 + 1;
-        const float factor_normal = l / ray_len2;
-        const V3 plane = nJ_inv * (uvh_m / vb);
-        const float rsigmat = sqrtf(vb / ray_len2);  // scale/rotation path is always "well conditioned"
-        ray_plane = {plane.x * factor_normal / focal_x, plane.y * factor_normal / focal_y, tc, rsigmat};
-        const V3 ray_normal_vector = {-plane.x * factor_normal, -plane.y * factor_normal, -1};
-        const M3 nJ = m3_cols(1 / t.z, 0.0f, -(t.x) / (t.z * t.z), 0.0f, 1 / t.z, -(t.y) / (t.z * t.z), t.x / l,
-                              t.y / l, t.z / l);
-        const V3 cam_normal_vector = nJ * ray_normal_vector;
-        const V3 nv = normalize(cam_normal_vector);
-        normal = {nv.x, nv.y, nv.z};
+        const float mx = ADD(FMA(u, C00, MUL(v, C10)), C20);
+        const float my = ADD(FMA(u, C10, MUL(v, C11)), C21);
+        const float mz = ADD(FMA(u, C20, MUL(v, C21)), C22);
+        const float vb = ADD(mz, FMA(u, mx, MUL(v, my)));
+        const float r_vb = rcp_approx(vb);
+        const float ax = MUL(mx, r_vb), ay = MUL(my, r_vb), az = MUL(mz, r_vb);
+        const float vv = MUL(v, v), uv = MUL(u, v);
+        const float plane_x = FMA(-u, az, FMA(ADD(vv, 1.f), ax, -MUL(uv, ay)));
+        const float plane_y = FMA(-v, az, FMA(FMA(u, u, 1.f), ay, -MUL(uv, ax)));
+        const float r_len2 = rcp_approx(ADD(FMA(u, u, vv), 1.f));
+        const float l = norm3df(tx, ty, tz);
+        const float factor = MUL(l, r_len2);
+        ray_plane = {MUL(MUL(factor, plane_x), rcp_approx(fx)), MUL(MUL(factor, plane_y), rcp_approx(fy)), tc,
+                     sqrt_approx(MUL(vb, r_len2))};
+        const float nx = MUL(factor, -plane_x), ny = MUL(factor, -plane_y);
+        const float rl = rcp_approx(l);
+        const float cx = FMA(-tx, rl, FMA(nx, rz, MUL(0.f, ny)));
+        const float cy = FMA(-ty, rl, FMA(0.f, nx, MUL(ny, rz)));
+        const float cz = FMA(-tz, rl, FMA(nx, MUL(tx, -r_tz2), MUL(ny, MUL(ty, -r_tz2))));
+        const float rs = rsqrt_approx(FMA(cz, cz, FMA(cx, cx, MUL(cy, cy))));
+        normal = {MUL(cx, rs), MUL(cy, rs), MUL(cz, rs)};
     }
 
     // ---- conic, radius, tile rectangle (render_forward.cu:347-368) ----------------------------
-    const float3 covv = {cov2D0, cov2D1, cov2D2};
-    const float det = (covv.x * covv.z - covv.y * covv.y);
     if (det == 0.0f) return;
-    const float det_inv = 1.f / det;
-    const float3 conic = {covv.z * det_inv, -covv.y * det_inv, covv.x * det_inv};
+    const float det_inv = rcp_approx(det);
+    const float3 conic = {MUL(cc, det_inv), MUL(det_inv, -cb), MUL(ca, det_inv)};
 
-    const float mid = 0.5f * (covv.x + covv.z);
-    const float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-    const float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
-    const float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+    const float mid = MUL(ADD(ca, cc), 0.5f);
+    const float sq = sqrt_approx(fmaxf(FMA(mid, mid, -det), 0.1f));
+    const float my_radius = ceilf(MUL(sqrt_approx(fmaxf(ADD(mid, sq), ADD(mid, -sq))), 3.f));
     const float2 point_image = {ndc_to_pix(p_proj.x, fp.W), ndc_to_pix(p_proj.y, fp.H)};
     uint2 rect_min, rect_max;
     tile_rect(point_image, my_radius, rect_min, rect_max, fp.gx, fp.gy);
@@ -187,13 +228,13 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, c
             rgb = eval_color(idx, fp, p_orig, in.shs, in.sg_axis, in.sg_sharpness, in.sg_color, mask);
     }
 
-    depths[idx] = norm3df(p_view.x, p_view.y, p_view.z);
+    depths[idx] = tc;
     radii[idx] = my_radius;
     clamped[idx] = mask;
     rects[idx] = {rect_min.x | (rect_min.y << 16), rect_max.x | (rect_max.y << 16)};
     tiles_touched[idx] = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
 
-    const float opac = __ldg(in.opacities + idx) * coef;
+    const float opac = MUL(coef, __ldg(in.opacities + idx));
     SplatRecord rec;
     rec.q0 = {point_image.x, point_image.y, conic.x, conic.y};
     rec.q1 = {conic.z, opac, ray_plane.x, ray_plane.y};

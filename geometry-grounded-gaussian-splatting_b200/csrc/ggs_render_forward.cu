@@ -6,7 +6,17 @@
 //   * mDepthinit is the ray depth of the last entry blended while T > 0.5 (MEDIAN_DEPTH_INIT);
 //   * bisection: bracket [d0-0.4, d0+0.4] clamped at 0, active iff T <= 0.45, 9 samples in the
 //     first iteration and 7 new ones afterwards, linear interpolation at the end.
-// One CTA per 16x16 tile; list entries are gathered as 64-byte SplatRecords into shared memory.
+//
+// Design (one CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel block):
+//   * list entries are gathered as 64-byte SplatRecords into shared memory, 256 per batch;
+//   * pass 1 leaves, per warp, a bitmask of the list positions that at least one of its pixels blended.
+//     The five bisection passes walk only those positions (about one third of the list), instead of
+//     re-testing every entry against every pixel as the reference does;
+//   * in a bisection pass a splat whose depth profile is more than 16 sigma away from the whole current
+//     bracket contributes exp() == 0 exactly (ex2.approx.ftz underflows), so its factor is exactly
+//     (1 - alpha) in front of the bracket and exactly 1 behind it: no exp / rsqrt is issued for it unless
+//     some pixel of the warp is close to it.  Brackets shrink 8x per iteration, so most splats are "far"
+//     in iterations 2-5.  Both shortcuts are exact: outputs are bit-identical to the plain evaluation.
 #include "ggs_kernels.cuh"
 
 namespace ggs {
@@ -19,6 +29,19 @@ struct RenderParams {
 
 constexpr int BATCH = TILE_PIXELS;
 
+constexpr int MASK_WORDS = 256;  // per warp: acceptance bits for the first 8192 list positions
+constexpr uint32_t FULL = 0xffffffffu;
+constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0
+
+// One depth sample of the vacancy-corrected transmittance product (render_forward.cu:603-621).
+__device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsigma, bool ball, float alpha) {
+    const float delta = (ts - t_peak) * rsigma;
+    const float g = ball ? expf(-0.5f * delta * delta) : 0.f;
+    const float one_minus_gaussian = 1.f - alpha * g;
+    const float rvacancy = rsqrtf(one_minus_gaussian);
+    return (ts > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
+}
+
 template <bool GEOMETRY>
 __global__ void __launch_bounds__(TILE_PIXELS)
     render_forward_kernel(const RenderParams rp, const uint2* __restrict__ ranges,
@@ -30,13 +53,16 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     __shared__ float4 s_q1[BATCH];
     __shared__ float4 s_q2[BATCH];
     __shared__ float4 s_q3[BATCH];
+    __shared__ uint32_t s_mask[GEOMETRY ? TILE_PIXELS / 32 : 1][GEOMETRY ? MASK_WORDS : 1];
     __shared__ uint32_t s_red[TILE_PIXELS / 32];
     __shared__ uint32_t s_block_max;
 
     const int W = rp.W, H = rp.H;
     const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
-    const uint32_t tid = threadIdx.y * TILE_X + threadIdx.x;
-    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
+    const uint32_t tid = threadIdx.x;
+    const uint32_t warp = tid >> 5, lane = tid & 31;
+    // warp w owns the 8x4 pixel block (w & 1, w >> 1) of the tile
+    const uint2 pix = {blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7), blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
     const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
@@ -56,6 +82,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     float C[3] = {0.f, 0.f, 0.f};
     float Normal[3] = {0.f, 0.f, 0.f};
     float mDepthinit = 0.f;
+    uint32_t mask_words = 0;  // words of s_mask[warp] that pass 1 produced (warp-uniform)
 
     for (int i = 0; i < rounds; i++, toDo -= BATCH) {
         const int block_done = __syncthreads_and(done);
@@ -73,42 +100,62 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         __syncthreads();
 
         const int lim = min(BATCH, toDo);
-        for (int j = 0; !done && j < lim; j++) {
-            contributor++;
-            const float4 q0 = s_q0[j];
-            const float4 q1 = s_q1[j];
-            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, q1.y * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1.f - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+        for (int w = 0; w * 32 < lim; w++) {
+            if (__all_sync(FULL, done)) break;
+            uint32_t bits = 0;
+            const int jend = min(32, lim - w * 32);
+            for (int jj = 0; jj < jend; jj++) {
+                const int j = w * 32 + jj;
+                bool blended = false;
+                if (!done) {
+                    contributor++;
+                    const float4 q0 = s_q0[j];
+                    const float4 q1 = s_q1[j];
+                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                    if (power <= 0.0f) {
+                        const float alpha = fminf(0.99f, q1.y * expf(power));
+                        if (alpha >= 1.0f / 255.0f) {
+                            const float test_T = T * (1.f - alpha);
+                            if (test_T < 0.0001f) {
+                                done = true;
+                            } else {
+                                const float aT = alpha * T;
+                                const float4 q2 = s_q2[j];
+                                const float4 q3 = s_q3[j];
+                                C[0] += q2.z * aT;
+                                C[1] += q2.w * aT;
+                                C[2] += q3.x * aT;
+                                if constexpr (GEOMETRY) {
+                                    const float t = q1.z * d.x + q1.w * d.y + q2.x;
+                                    Normal[0] += q3.y * aT;
+                                    Normal[1] += q3.z * aT;
+                                    Normal[2] += q3.w * aT;
+                                    mDepthinit = T > 0.5f ? t : mDepthinit;
+                                }
+                                T = test_T;
+                                last_contributor = contributor;
+                                blended = true;
+                            }
+                        }
+                    }
+                }
+                if constexpr (GEOMETRY) {
+                    if (__any_sync(FULL, blended)) bits |= 1u << jj;
+                }
             }
-            const float aT = alpha * T;
-            const float4 q2 = s_q2[j];
-            const float4 q3 = s_q3[j];
-            C[0] += q2.z * aT;
-            C[1] += q2.w * aT;
-            C[2] += q3.x * aT;
             if constexpr (GEOMETRY) {
-                const float t = q1.z * d.x + q1.w * d.y + q2.x;
-                Normal[0] += q3.y * aT;
-                Normal[1] += q3.z * aT;
-                Normal[2] += q3.w * aT;
-                mDepthinit = T > 0.5f ? t : mDepthinit;
+                const uint32_t gw = i * (BATCH / 32) + w;
+                if (lane == 0 && gw < MASK_WORDS) s_mask[warp][gw] = bits;
+                mask_words = gw + 1;
             }
-            T = test_T;
-            last_contributor = contributor;
         }
     }
 
     // block-wide max of last_contributor
     {
-        const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
-        if ((tid & 31) == 0) s_red[tid >> 5] = wmax;
+        const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+        if (lane == 0) s_red[warp] = wmax;
         __syncthreads();
         if (tid == 0) {
             uint32_t m = 0;
@@ -127,6 +174,12 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         float depth_min = fmaxf(mDepthinit - SAMPLE_RANGE, 0.f);
         float depth_max = fmaxf(mDepthinit + SAMPLE_RANGE, 0.f);
         bool in_range = T <= MIN_TRANSMITTANCE;
+        // rsqrt.approx(1.0): the vacancy factor of a splat whose Gaussian term underflowed
+        float c1;
+        {
+            const float one = 1.0f;
+            asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(c1) : "f"(one));
+        }
 
 #pragma unroll 1
         for (int it = 0; it < SPLIT_ITERATIONS; it++) {
@@ -139,10 +192,9 @@ __global__ void __launch_bounds__(TILE_PIXELS)
 #pragma unroll
             for (int s = 1; s < SPLIT; s++) T_p[s] = 1.f;
             const float interval = (depth_max - depth_min) * ONE_OVER_SPLIT;
-            bool bdone = !in_range;
-            int toDo2 = max_contributor;
-            contributor = 0;
-            for (int i = 0; i < rounds2; i++, toDo2 -= BATCH) {
+            // last list position any pixel of this warp still needs
+            const uint32_t warp_last = __reduce_max_sync(FULL, in_range ? last_contributor : 0u);
+            for (int i = 0; i < rounds2; i++) {
                 __syncthreads();
                 const uint32_t progress = i * BATCH + tid;
                 if (progress < max_contributor) {
@@ -153,40 +205,60 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                     s_q2[tid] = __ldg(src + 2);
                 }
                 __syncthreads();
-                const int lim = min(BATCH, toDo2);
-                for (int j = 0; !bdone && j < lim; j++) {
-                    contributor++;
-                    bdone = contributor >= last_contributor;
-                    const float4 q0 = s_q0[j];
-                    const float4 q1 = s_q1[j];
-                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                    if (power > 0.0f) continue;
-                    const float alpha = fminf(0.99f, q1.y * expf(power));
-                    if (alpha < 1.0f / 255.0f) continue;
-                    const float2 rp2 = *reinterpret_cast<const float2*>(&s_q2[j]);
-                    const float t_peak = q1.z * d.x + q1.w * d.y + rp2.x;
-                    const float rsigma = rp2.y;
-                    const bool ball = rsigma > 0;
-                    if (first) {
+                for (int w = 0; w < BATCH / 32; w++) {
+                    const uint32_t base = i * BATCH + w * 32;
+                    if (base >= warp_last) break;
+                    const uint32_t gw = i * (BATCH / 32) + w;
+                    uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
+                    while (bits) {
+                        const int jj = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        const uint32_t pos = base + jj + 1;  // 1-based list position == `contributor`
+                        if (pos > warp_last) break;
+                        const int j = w * 32 + jj;
+                        const float4 q0 = s_q0[j];
+                        const float4 q1 = s_q1[j];
+                        const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                        const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                        const float alpha = fminf(0.99f, q1.y * expf(power));
+                        const bool act = in_range && pos <= last_contributor && !(power > 0.0f) &&
+                                         !(alpha < 1.0f / 255.0f);
+                        if (!__any_sync(FULL, act)) continue;
+                        const float2 rp2 = *reinterpret_cast<const float2*>(&s_q2[j]);
+                        const float t_peak = q1.z * d.x + q1.w * d.y + rp2.x;
+                        const float rsigma = rp2.y;
+                        const bool ball = rsigma > 0;
+                        // exact shortcut: the whole bracket is > 16 sigma away from this splat's depth profile
+                        const float front = depth_min - t_peak;
+                        const float back = t_peak - depth_max;
+                        const float guard = 1e-5f * (depth_max + fabsf(t_peak));
+                        const bool far_front = ball && front * rsigma > FAR_SIGMAS && front > guard;
+                        const bool far_back = ball && back * rsigma > FAR_SIGMAS && back > guard;
+                        const bool near = act && !(far_front || far_back);
+                        if (__any_sync(FULL, near)) {
+                            if (act) {
+                                if (first) {
 #pragma unroll
-                        for (int s = 0; s < SPLIT + 1; s++) {
-                            const float ts = depth_min + interval * s;
-                            const float delta = (ts - t_peak) * rsigma;
-                            const float g = ball ? expf(-0.5f * delta * delta) : 0.f;
-                            const float one_minus_gaussian = 1.f - alpha * g;
-                            const float rvacancy = rsqrtf(one_minus_gaussian);
-                            T_p[s] *= (ts > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
-                        }
-                    } else {
+                                    for (int s = 0; s < SPLIT + 1; s++)
+                                        T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
+                                } else {
 #pragma unroll
-                        for (int s = 1; s < SPLIT; s++) {
-                            const float ts = depth_min + interval * s;
-                            const float delta = (ts - t_peak) * rsigma;
-                            const float g = ball ? expf(-0.5f * delta * delta) : 0.f;
-                            const float one_minus_gaussian = 1.f - alpha * g;
-                            const float rvacancy = rsqrtf(one_minus_gaussian);
-                            T_p[s] *= (ts > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
+                                    for (int s = 1; s < SPLIT; s++)
+                                        T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
+                                }
+                            }
+                        } else if (act) {
+                            // exp underflows to 0 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
+                            const float f = (far_front ? (1.f - alpha) : 1.0f) * c1;
+                            if (far_front || c1 != 1.0f) {
+                                if (first) {
+#pragma unroll
+                                    for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
+                                } else {
+#pragma unroll
+                                    for (int s = 1; s < SPLIT; s++) T_p[s] *= f;
+                                }
+                            }
                         }
                     }
                 }
@@ -239,7 +311,7 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     rp.focal_y = fp.focal_y;
     rp.bg = fp.view.bg;
     const dim3 grid(fp.gx, fp.gy, 1);
-    const dim3 block(TILE_X, TILE_Y, 1);
+    const dim3 block(TILE_PIXELS, 1, 1);
     if (require_depth)
         render_forward_kernel<true><<<grid, block, 0, stream>>>(rp, ranges, point_list, records, out.color, out.alpha,
                                                                out.normal, out.mdepth, out.n_contrib,

@@ -135,6 +135,17 @@ class _RasterizeGaussians(torch.autograd.Function):
         device = means3D.device
         P = means3D.shape[0]
         H, W = int(rs.image_height), int(rs.image_width)
+        if P == 0:
+            # rasterize_points.cu:95: nothing is launched, the zero-initialised outputs are returned
+            ctx.empty = True
+            ctx.in_shapes = [None if t is None else (t.shape, t.dtype, t.device) for t in
+                             (means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, colors_precomp, opacities, scales,
+                              rotations)]
+            z = lambda c: torch.zeros(c, H, W, dtype=torch.float32, device=device)  # noqa: E731
+            radii = torch.zeros(0, dtype=torch.int32, device=device)
+            ctx.mark_non_differentiable(radii)
+            return z(3), radii, z(1), z(1), z(3)
+        ctx.empty = False
         keep = []
         tens = [_dev_f32(t, device) if _present(t) else None
                 for t in (means3D, opacities, scales, rotations, sh, sg_axis, sg_sharpness, sg_color, colors_precomp)]
@@ -167,6 +178,10 @@ class _RasterizeGaussians(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_color, grad_radii, grad_mdepth, grad_alpha, grad_normal):
+        if ctx.empty:
+            gz = [None if (d is None or not ctx.needs_input_grad[i]) else torch.zeros(d[0], dtype=d[1], device=d[2])
+                  for i, d in enumerate(ctx.in_shapes)]
+            return (*gz, None, None)
         rs = ctx.raster_settings
         m3, op, sc, ro, sh_, sa, ss, sgc, cp, alpha, normal, mdepth, radii = ctx.saved_tensors
         device = m3.device

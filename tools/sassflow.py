@@ -110,7 +110,7 @@ def parse(path, kernel):
     return ins
 
 
-REG = re.compile(r"(-?)(\|?)(U?R\d+|U?P\d+)(\.reuse|\.64|\.H0_H0|\.H1_H1)*(\|?)")
+REG = re.compile(r"(-?)(\|?)(U?R\d+|U?P\d+)(\.reuse|\.64|\.H0_H0|\.H1_H1)*(\|?)(\.reuse)?")
 
 
 class Slicer:
@@ -187,7 +187,7 @@ class Slicer:
             return o
         m = REG.fullmatch(o)
         if m:
-            neg, a1, reg, _, a2 = m.groups()
+            neg, a1, reg, _, a2, _r = m.groups()
             v = self.value(reg, k)
             if a1:
                 v = f"|{v}|"
