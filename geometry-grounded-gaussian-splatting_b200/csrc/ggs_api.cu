@@ -147,7 +147,7 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     const int tiles = fp.gx * fp.gy;
     const int end_bit = sort_end_bit(tiles);
     const int passes = sort_passes(0, end_bit);
-    const BinLayout BL = bin_layout(D, passes);
+    const BinLayout BL = bin_layout(D, passes, tiles);
     void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
     if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
     *bin = b;
@@ -172,8 +172,13 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
 
 const uint32_t* sorted_list(void* bin, int64_t D, int tiles) {
     const int passes = sort_passes(0, sort_end_bit(tiles));
-    const BinLayout BL = bin_layout((size_t)D, passes);
+    const BinLayout BL = bin_layout((size_t)D, passes, tiles);
     return (passes & 1) ? at<uint32_t>(bin, BL.vals_b) : at<uint32_t>(bin, BL.vals_a);
+}
+
+uint32_t* accept_mask(void* bin, int64_t D, int tiles) {
+    const BinLayout BL = bin_layout((size_t)D, sort_passes(0, sort_end_bit(tiles)), tiles);
+    return at<uint32_t>(bin, BL.accept_mask);
 }
 
 }  // namespace
@@ -241,6 +246,8 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     ro.mdepth = out->mdepth;
     ro.n_contrib = at<uint32_t>(img, IL.n_contrib);
     ro.max_contributor = at<uint32_t>(tile, TL.max_contributor);
+    ro.accept_mask = accept_mask(bin, D, tiles);
+    ro.warp_words = at<uint32_t>(tile, TL.warp_words);
     launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, D, tiles),
                           at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
     GGS_STAGE("render_forward", debug, stream);
@@ -287,6 +294,8 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     ri.mdepth = bi->mdepth;
     ri.n_contrib = at<uint32_t>(state->image, 0);
     ri.max_contributor = at<uint32_t>(state->tile, TL.max_contributor);
+    ri.accept_mask = accept_mask(state->binning, state->num_rendered, tiles);
+    ri.warp_words = at<uint32_t>(state->tile, TL.warp_words);
     ri.dL_dcolor = bi->dL_dcolor;
     ri.dL_dmdepth = bi->dL_dmdepth;
     ri.dL_dalpha = bi->dL_dalpha;
@@ -459,7 +468,7 @@ int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_re
     L->rects = GL.rects;
     const int end_bit = sort_end_bit(tiles);
     const int passes = sort_passes(0, end_bit);
-    const BinLayout BL = bin_layout((size_t)num_rendered, passes);
+    const BinLayout BL = bin_layout((size_t)num_rendered, passes, tiles);
     L->binning_bytes = BL.bytes;
     const bool in_b = passes & 1;
     L->sorted_keys = in_b ? BL.keys_b : BL.keys_a;

@@ -118,11 +118,12 @@ struct BinLayout {
     size_t hist;            // u32[MAX_PASSES][RADIX]  (global digit histograms -> exclusive offsets)
     size_t status;          // u32[passes][tiles][RADIX] decoupled look-back descriptors
     size_t counters;        // u32[MAX_PASSES] dynamic tile ids
+    size_t accept_mask;     // u32[(D/32 + tiles) * 8]: per (tile, warp) bitmask of blended list positions
     size_t bytes;
     size_t status_bytes;
 };
 
-inline BinLayout bin_layout(size_t D, int passes) {
+inline BinLayout bin_layout(size_t D, int passes, size_t tiles_for_mask = 0) {
     BinLayout L;
     size_t o = 0;
     auto take = [&](size_t bytes) {
@@ -139,6 +140,7 @@ inline BinLayout bin_layout(size_t D, int passes) {
     L.status_bytes = (size_t)passes * tiles * RADIX * 4;
     L.status = take(L.status_bytes);
     L.counters = take(MAX_PASSES * 4);
+    L.accept_mask = take(tiles_for_mask ? (D / 32 + tiles_for_mask + 1) * 8 * 4 : 0);
     L.bytes = o;
     return L;
 }
@@ -146,13 +148,15 @@ inline BinLayout bin_layout(size_t D, int passes) {
 struct TileLayout {
     size_t ranges;           // uint2[tiles]
     size_t max_contributor;  // u32[tiles]
+    size_t warp_words;       // u32[tiles][8]: words of accept_mask each warp of the tile produced
     size_t bytes;
 };
 inline TileLayout tile_layout(size_t tiles) {
     TileLayout L;
     L.ranges = 0;
     L.max_contributor = align_up(tiles * 8, 256);
-    L.bytes = L.max_contributor + align_up(tiles * 4, 256);
+    L.warp_words = L.max_contributor + align_up(tiles * 4, 256);
+    L.bytes = L.warp_words + align_up(tiles * 32, 256);
     return L;
 }
 

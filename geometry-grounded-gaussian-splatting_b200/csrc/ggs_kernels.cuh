@@ -57,6 +57,8 @@ struct RenderOut {
     float* mdepth;  // [1,H,W]
     uint32_t* n_contrib;
     uint32_t* max_contributor;
+    uint32_t* accept_mask;  // see BinLayout::accept_mask
+    uint32_t* warp_words;   // see TileLayout::warp_words
 };
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
                            const SplatRecord* records, const RenderOut& out, bool require_depth,
@@ -69,6 +71,8 @@ struct RenderBwdIn {
     const float* mdepth;
     const uint32_t* n_contrib;
     const uint32_t* max_contributor;
+    const uint32_t* accept_mask;
+    const uint32_t* warp_words;
     const float* dL_dcolor;
     const float* dL_dmdepth;
     const float* dL_dalpha;

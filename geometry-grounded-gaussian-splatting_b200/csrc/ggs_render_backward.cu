@@ -3,7 +3,9 @@
 //           dL_dmt_dT_dtm = dL/dmdepth * rln / max(-dT/dt_m, 1e-7);
 //   pass B: back-to-front over [0, max_contributor), recomputing alpha, with the colour / normal
 //           "accumulated behind" recurrences, depth-term gradients and dL/dalpha.
-// Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
+// One CTA per 16x16 tile; warp w owns an 8x4 pixel block, as in the forward.  Both passes walk only the
+// list positions that the forward recorded as blended by at least one pixel of the warp (accept_mask):
+// about a third of the list.  Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
 // scalar atomics from one lane (the reference), the warp runs ONE transposing butterfly (20
 // shuffles) that leaves component c on its own lane, and those 17 lanes issue a single predicated
 // RED into the entry's contiguous 80-byte accumulator row.
@@ -18,6 +20,8 @@ struct RenderBwdParams {
 };
 
 constexpr int BATCH_B = TILE_PIXELS;
+constexpr int REC_QUADS_B = 5;  // 80-byte shared-memory stride (see ggs_render_forward.cu)
+constexpr uint32_t FULL_B = 0xffffffffu;
 
 // Butterfly reduce-scatter of 17 values (v[17] must be 0).  Returns the warp-wide sum of component
 // warp_component(lane) on lanes where that is >= 0.
@@ -84,21 +88,20 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                            const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
                            const float* __restrict__ alphas, const float* __restrict__ normalmap,
                            const float* __restrict__ mdepth, const uint32_t* __restrict__ n_contrib,
-                           const uint32_t* __restrict__ max_contributors, const float* __restrict__ dL_dpixels,
+                           const uint32_t* __restrict__ max_contributors, const uint32_t* __restrict__ accept_mask,
+                           const uint32_t* __restrict__ warp_words, const float* __restrict__ dL_dpixels,
                            const float* __restrict__ dL_dpixel_mdepths, const float* __restrict__ dL_dalphas,
                            const float* __restrict__ dL_dpixel_normals, float* __restrict__ grad_acc) {
     __shared__ uint32_t s_id[BATCH_B];
-    __shared__ float4 s_q0[BATCH_B];
-    __shared__ float4 s_q1[BATCH_B];
-    __shared__ float4 s_q2[BATCH_B];
-    __shared__ float4 s_q3[BATCH_B];
+    __shared__ float4 s_rec[BATCH_B * REC_QUADS_B];
 
     const int W = rp.W, H = rp.H;
     const size_t HW = (size_t)H * W;
     const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
-    const uint32_t tid = threadIdx.y * TILE_X + threadIdx.x;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t warp = tid >> 5;
     const int lane = tid & 31;
-    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
+    const uint2 pix = {blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7), blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
     const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
@@ -107,12 +110,16 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
     const uint2 range = ranges[tile_id];
     const uint32_t max_contributor = max_contributors[tile_id];
+    const uint32_t mask_base = range.x / 32 + tile_id;
+    const uint32_t mask_words = warp_words[tile_id * (TILE_PIXELS / 32) + warp];
+    const uint32_t* my_mask = accept_mask + (size_t)mask_base * 8 + warp;  // word gw at my_mask[gw * 8]
 
     const float w_final = inside ? alphas[pix_id] : 0.f;
     const float T_final = 1.f - w_final;
     float mDepth = 0.f;
     float T = T_final;
-    const int last_contributor = inside ? n_contrib[pix_id] : 0;
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+    const uint32_t warp_last = __reduce_max_sync(FULL_B, last_contributor);
 
     float accum_rec[3] = {0.f, 0.f, 0.f};
     float dL_dpixel[3] = {0.f, 0.f, 0.f};
@@ -147,48 +154,56 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const int rounds = (max_contributor + BATCH_B - 1) / BATCH_B;
 
     if constexpr (GEOMETRY) {
+        // ---- pass A: dT/dt_m at the stored median depth, front to back --------------------------------
         float dT_dtm = 0.f;
-        int toDo = max_contributor;
-        int contributor = 0;
-        bool done = (mDepth == 0) || (last_contributor == 0) || !inside;
-        for (int i = 0; i < rounds; i++, toDo -= BATCH_B) {
+        const bool live = !((mDepth == 0) || (last_contributor == 0) || !inside);
+        const uint32_t warp_last_a = __reduce_max_sync(FULL_B, live ? last_contributor : 0u);
+        for (int i = 0; i < rounds; i++) {
             __syncthreads();
             const uint32_t progress = i * BATCH_B + tid;
             if (progress < max_contributor) {
                 const uint32_t id = __ldg(point_list + range.x + progress);
                 const float4* src = reinterpret_cast<const float4*>(records + id);
-                s_q0[tid] = __ldg(src);
-                s_q1[tid] = __ldg(src + 1);
-                s_q2[tid] = __ldg(src + 2);
+                float4* dst = s_rec + tid * REC_QUADS_B;
+                dst[0] = __ldg(src);
+                dst[1] = __ldg(src + 1);
+                dst[2] = __ldg(src + 2);
             }
             __syncthreads();
-            const int lim = min(BATCH_B, toDo);
-            for (int j = 0; !done && j < lim; j++) {
-                contributor++;
-                done = contributor >= last_contributor;
-                const float4 q0 = s_q0[j];
-                const float4 q1 = s_q1[j];
-                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, q1.y * expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float2 rp2 = *reinterpret_cast<const float2*>(&s_q2[j]);
-                const float t_peak = q1.z * d.x + q1.w * d.y + rp2.x;
-                const float rsigma = rp2.y;
-                const float t_delta = (mDepth - t_peak) * rsigma;
-                const float G_exp = expf(-0.5f * t_delta * t_delta);
-                const float Gt = alpha * G_exp;
-                dT_dtm += -0.25f * Gt / (1.f - Gt) * fabsf(t_delta) * rsigma;
+            for (int w = 0; w < BATCH_B / 32; w++) {
+                const uint32_t base = i * BATCH_B + w * 32;
+                if (base >= warp_last_a) break;
+                const uint32_t gw = i * (BATCH_B / 32) + w;
+                uint32_t bits = gw < mask_words ? __ldg(my_mask + (size_t)gw * 8) : 0u;
+                while (bits) {
+                    const int jj = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const uint32_t pos = base + jj + 1;
+                    if (pos > warp_last_a) break;
+                    const float4* rec = s_rec + (w * 32 + jj) * REC_QUADS_B;
+                    const float4 q0 = rec[0];
+                    const float4 q1 = rec[1];
+                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                    const float alpha = fminf(0.99f, q1.y * expf(power));
+                    const bool act = live && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (!__any_sync(FULL_B, act)) continue;
+                    if (act) {
+                        const float4 q2 = rec[2];
+                        const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
+                        const float rsigma = q2.y;
+                        const float t_delta = (mDepth - t_peak) * rsigma;
+                        const float G_exp = expf(-0.5f * t_delta * t_delta);
+                        const float Gt = alpha * G_exp;
+                        dT_dtm += -0.25f * Gt / (1.f - Gt) * fabsf(t_delta) * rsigma;
+                    }
+                }
             }
         }
         dL_dmt_dT_dtm = dL_dpixel_mt / fmaxf(-dT_dtm, 1e-7f);
     }
 
-    const bool done = !inside;
-    int toDo = max_contributor;
-    uint32_t contributor = toDo;
-
+    // ---- pass B: back to front ----------------------------------------------------------------------
     float last_alpha = 0.f;
     float last_color[3] = {0.f, 0.f, 0.f};
     float last_normal[3] = {0.f, 0.f, 0.f};
@@ -197,114 +212,123 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const float ddely_dy = 0.5f * H;
     const int my_comp = warp_component(lane);
 
-    for (int i = 0; i < rounds; i++, toDo -= BATCH_B) {
+    for (int i = rounds - 1; i >= 0; i--) {
         __syncthreads();
         const uint32_t progress = i * BATCH_B + tid;
         if (progress < max_contributor) {
-            const uint32_t id = __ldg(point_list + range.x + max_contributor - progress - 1);
+            const uint32_t id = __ldg(point_list + range.x + progress);
             s_id[tid] = id;
             const float4* src = reinterpret_cast<const float4*>(records + id);
-            s_q0[tid] = __ldg(src);
-            s_q1[tid] = __ldg(src + 1);
-            s_q2[tid] = __ldg(src + 2);
-            s_q3[tid] = __ldg(src + 3);
+            float4* dst = s_rec + tid * REC_QUADS_B;
+            dst[0] = __ldg(src);
+            dst[1] = __ldg(src + 1);
+            dst[2] = __ldg(src + 2);
+            dst[3] = __ldg(src + 3);
         }
         __syncthreads();
 
-        const int lim = min(BATCH_B, toDo);
-        for (int j = 0; j < lim; j++) {
-            contributor--;
-            const float4 q0 = s_q0[j];
-            const float4 q1 = s_q1[j];
-            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-            const float4 con_o = {q0.z, q0.w, q1.x, q1.y};
-            const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-            const float G = expf(power);
-            const float alpha = fminf(0.99f, con_o.w * G);
-            const bool valid =
-                !(done || (contributor >= (uint32_t)last_contributor) || (power > 0.0f) || (alpha < 1.0f / 255.0f));
-            if (!__any_sync(0xffffffffu, valid)) continue;
+        for (int w = BATCH_B / 32 - 1; w >= 0; w--) {
+            const uint32_t base = i * BATCH_B + w * 32;
+            if (base >= warp_last) continue;
+            const uint32_t gw = i * (BATCH_B / 32) + w;
+            uint32_t bits = gw < mask_words ? __ldg(my_mask + (size_t)gw * 8) : 0u;
+            while (bits) {
+                const int jj = 31 - __clz(bits);
+                bits ^= 1u << jj;
+                const uint32_t idx = base + jj;  // 0-based list position == the reference's `contributor`
+                const int j = w * 32 + jj;
+                const float4* rec = s_rec + j * REC_QUADS_B;
+                const float4 q0 = rec[0];
+                const float4 q1 = rec[1];
+                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                const float4 con_o = {q0.z, q0.w, q1.x, q1.y};
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, con_o.w * G);
+                const bool valid = !((idx >= last_contributor) || (power > 0.0f) || (alpha < 1.0f / 255.0f));
+                if (!__any_sync(FULL_B, valid)) continue;
 
-            float v[18];
+                float v[18];
 #pragma unroll
-            for (int k = 0; k < 18; k++) v[k] = 0.f;
+                for (int k = 0; k < 18; k++) v[k] = 0.f;
 
-            if (valid) {
-                T = T / (1.f - alpha);
-                const float blending_weight = alpha * T;
-                const float4 q2 = s_q2[j];
-                const float4 q3 = s_q3[j];
-                const float col[3] = {q2.z, q2.w, q3.x};
-                float dL_dopa = 0.0f;
-#pragma unroll
-                for (int ch = 0; ch < 3; ch++) {
-                    const float c = col[ch];
-                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                    last_color[ch] = c;
-                    const float dL_dchannel = dL_dpixel[ch];
-                    dL_dopa += (c - accum_rec[ch]) * dL_dchannel;
-                    v[7 + ch] = blending_weight * dL_dchannel;
-                }
-                float dL_dt = 0.f;
-                float dL_dopa_sigma = 0.f;
-                const float2 rpl = {q1.z, q1.w};
-                if constexpr (GEOMETRY) {
-                    const float nrm[3] = {q3.y, q3.z, q3.w};
+                if (valid) {
+                    T = T / (1.f - alpha);
+                    const float blending_weight = alpha * T;
+                    const float4 q2 = rec[2];
+                    const float4 q3 = rec[3];
+                    const float col[3] = {q2.z, q2.w, q3.x};
+                    float dL_dopa = 0.0f;
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
-                        const float n = nrm[ch];
-                        accum_normal_rec[ch] =
-                            last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
-                        last_normal[ch] = n;
-                        const float dL_dchannel = dL_dpixel_normal[ch];
-                        dL_dopa += (n - accum_normal_rec[ch]) * dL_dchannel;
-                        v[10 + ch] = blending_weight * dL_dchannel;
+                        const float c = col[ch];
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = c;
+                        const float dL_dchannel = dL_dpixel[ch];
+                        dL_dopa += (c - accum_rec[ch]) * dL_dchannel;
+                        v[7 + ch] = blending_weight * dL_dchannel;
                     }
-                    const float t_peak = rpl.x * d.x + rpl.y * d.y + q2.x;
-                    const float rsigma = q2.y;
-                    const float t_delta = (mDepth - t_peak) * rsigma;
-                    const float G_exp = expf(-0.5f * t_delta * t_delta);
-                    const float Gt = alpha * G_exp;
-                    float dL_dGt = dL_dmt_dT_dtm * 0.25f / (1.f - Gt);
-                    dL_dGt = mDepth > t_peak ? dL_dGt : -dL_dGt;
-                    dL_dGt = rsigma > 0 ? dL_dGt : 0.f;
-                    dL_dopa_sigma = dL_dGt * G_exp - dL_dmt_dT_dtm * (t_delta > 0 ? 0.5f / (1.f - alpha) : 0.f);
-                    const float dL_ddelta = -dL_dGt * Gt * t_delta;
-                    v[16] = dL_ddelta * (mDepth - t_peak);
-                    const float dL_dt_peak = -dL_ddelta * rsigma;
-                    dL_dt = dL_dt_peak;
-                    v[15] = dL_dt;
-                    v[13] = dL_dt * d.x;
-                    v[14] = dL_dt * d.y;
-                }
-                dL_dopa *= T;
-                if constexpr (GEOMETRY) dL_dopa += dL_dopa_sigma;
-                dL_dopa += -T_final / (1.f - alpha) * dL_dfinalT;
-                last_alpha = alpha;
+                    float dL_dt = 0.f;
+                    float dL_dopa_sigma = 0.f;
+                    const float2 rpl = {q1.z, q1.w};
+                    if constexpr (GEOMETRY) {
+                        const float nrm[3] = {q3.y, q3.z, q3.w};
+#pragma unroll
+                        for (int ch = 0; ch < 3; ch++) {
+                            const float n = nrm[ch];
+                            accum_normal_rec[ch] =
+                                last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_normal_rec[ch];
+                            last_normal[ch] = n;
+                            const float dL_dchannel = dL_dpixel_normal[ch];
+                            dL_dopa += (n - accum_normal_rec[ch]) * dL_dchannel;
+                            v[10 + ch] = blending_weight * dL_dchannel;
+                        }
+                        const float t_peak = rpl.x * d.x + rpl.y * d.y + q2.x;
+                        const float rsigma = q2.y;
+                        const float t_delta = (mDepth - t_peak) * rsigma;
+                        const float G_exp = expf(-0.5f * t_delta * t_delta);
+                        const float Gt = alpha * G_exp;
+                        float dL_dGt = dL_dmt_dT_dtm * 0.25f / (1.f - Gt);
+                        dL_dGt = mDepth > t_peak ? dL_dGt : -dL_dGt;
+                        dL_dGt = rsigma > 0 ? dL_dGt : 0.f;
+                        dL_dopa_sigma = dL_dGt * G_exp - dL_dmt_dT_dtm * (t_delta > 0 ? 0.5f / (1.f - alpha) : 0.f);
+                        const float dL_ddelta = -dL_dGt * Gt * t_delta;
+                        v[16] = dL_ddelta * (mDepth - t_peak);
+                        const float dL_dt_peak = -dL_ddelta * rsigma;
+                        dL_dt = dL_dt_peak;
+                        v[15] = dL_dt;
+                        v[13] = dL_dt * d.x;
+                        v[14] = dL_dt * d.y;
+                    }
+                    dL_dopa *= T;
+                    if constexpr (GEOMETRY) dL_dopa += dL_dopa_sigma;
+                    dL_dopa += -T_final / (1.f - alpha) * dL_dfinalT;
+                    last_alpha = alpha;
 
-                const float dL_dG = con_o.w * dL_dopa;
-                const float gdx = G * d.x;
-                const float gdy = G * d.y;
-                const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                float dL_ddelx = dL_dG * dG_ddelx;
-                float dL_ddely = dL_dG * dG_ddely;
-                if constexpr (GEOMETRY) {
-                    dL_ddelx += dL_dt * rpl.x;
-                    dL_ddely += dL_dt * rpl.y;
+                    const float dL_dG = con_o.w * dL_dopa;
+                    const float gdx = G * d.x;
+                    const float gdy = G * d.y;
+                    const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+                    const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+                    float dL_ddelx = dL_dG * dG_ddelx;
+                    float dL_ddely = dL_dG * dG_ddely;
+                    if constexpr (GEOMETRY) {
+                        dL_ddelx += dL_dt * rpl.x;
+                        dL_ddely += dL_dt * rpl.y;
+                    }
+                    v[0] = dL_ddelx * ddelx_dx;
+                    v[1] = dL_ddely * ddely_dy;
+                    v[2] = fabsf(v[0]) + fabsf(v[1]);
+                    v[3] = -0.5f * gdx * d.x * dL_dG;
+                    v[4] = -0.5f * gdx * d.y * dL_dG;
+                    v[5] = -0.5f * gdy * d.y * dL_dG;
+                    v[6] = G * dL_dopa;
                 }
-                v[0] = dL_ddelx * ddelx_dx;
-                v[1] = dL_ddely * ddely_dy;
-                v[2] = fabsf(v[0]) + fabsf(v[1]);
-                v[3] = -0.5f * gdx * d.x * dL_dG;
-                v[4] = -0.5f * gdx * d.y * dL_dG;
-                v[5] = -0.5f * gdy * d.y * dL_dG;
-                v[6] = G * dL_dopa;
-            }
-            const float sum = warp_reduce_scatter17(v, lane);
-            if (my_comp >= 0) {
-                if (GEOMETRY || my_comp < 10)
-                    atomicAdd(grad_acc + (size_t)s_id[j] * GRAD_STRIDE + my_comp, sum);
+                const float sum = warp_reduce_scatter17(v, lane);
+                if (my_comp >= 0) {
+                    if (GEOMETRY || my_comp < 10)
+                        atomicAdd(grad_acc + (size_t)s_id[j] * GRAD_STRIDE + my_comp, sum);
+                }
             }
         }
     }
@@ -321,15 +345,15 @@ void launch_render_backward(const FrameParams& fp, const uint2* ranges, const ui
     rp.focal_y = fp.focal_y;
     rp.bg = fp.view.bg;
     const dim3 grid(fp.gx, fp.gy, 1);
-    const dim3 block(TILE_X, TILE_Y, 1);
+    const dim3 block(TILE_PIXELS, 1, 1);
     if (require_depth)
         render_backward_kernel<true><<<grid, block, 0, stream>>>(
             rp, ranges, point_list, records, in.alpha, in.normal, in.mdepth, in.n_contrib, in.max_contributor,
-            in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
+            in.accept_mask, in.warp_words, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
     else
         render_backward_kernel<false><<<grid, block, 0, stream>>>(
             rp, ranges, point_list, records, in.alpha, in.normal, in.mdepth, in.n_contrib, in.max_contributor,
-            in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
+            in.accept_mask, in.warp_words, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
 }
 
 }  // namespace ggs

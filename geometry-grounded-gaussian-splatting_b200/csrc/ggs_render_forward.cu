@@ -29,6 +29,7 @@ struct RenderParams {
 
 constexpr int BATCH = TILE_PIXELS;
 
+constexpr int REC_QUADS = 5;
 constexpr int MASK_WORDS = 256;  // per warp: acceptance bits for the first 8192 list positions
 constexpr uint32_t FULL = 0xffffffffu;
 constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0
@@ -48,11 +49,11 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                           const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
                           float* __restrict__ out_color, float* __restrict__ out_alpha,
                           float* __restrict__ out_normal, float* __restrict__ out_mdepth,
-                          uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ max_contributors) {
-    __shared__ float4 s_q0[BATCH];
-    __shared__ float4 s_q1[BATCH];
-    __shared__ float4 s_q2[BATCH];
-    __shared__ float4 s_q3[BATCH];
+                          uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ max_contributors,
+                          uint32_t* __restrict__ accept_mask, uint32_t* __restrict__ warp_words) {
+    // staged records, 80-byte stride (4 payload quads + 1 pad): conflict-free 16-byte stores by 8 consecutive
+    // threads, and one address computation per entry on the (broadcast) read side
+    __shared__ float4 s_rec[BATCH * REC_QUADS];
     __shared__ uint32_t s_mask[GEOMETRY ? TILE_PIXELS / 32 : 1][GEOMETRY ? MASK_WORDS : 1];
     __shared__ uint32_t s_red[TILE_PIXELS / 32];
     __shared__ uint32_t s_block_max;
@@ -75,6 +76,8 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const uint2 range = ranges[tile_id];
     const int rounds = ((range.y - range.x + BATCH - 1) / BATCH);
     int toDo = range.y - range.x;
+    // first word of this tile in the global acceptance mask (tiles are laid out in list order, one spare word each)
+    const uint32_t mask_base = range.x / 32 + tile_id;
 
     float T = 1.0f;
     uint32_t contributor = 0;
@@ -92,10 +95,11 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         if (range.x + progress < range.y) {
             const uint32_t id = __ldg(point_list + range.x + progress);
             const float4* src = reinterpret_cast<const float4*>(records + id);
-            s_q0[tid] = __ldg(src);
-            s_q1[tid] = __ldg(src + 1);
-            s_q2[tid] = __ldg(src + 2);
-            s_q3[tid] = __ldg(src + 3);
+            float4* dst = s_rec + tid * REC_QUADS;
+            dst[0] = __ldg(src);
+            dst[1] = __ldg(src + 1);
+            dst[2] = __ldg(src + 2);
+            dst[3] = __ldg(src + 3);
         }
         __syncthreads();
 
@@ -109,8 +113,9 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 bool blended = false;
                 if (!done) {
                     contributor++;
-                    const float4 q0 = s_q0[j];
-                    const float4 q1 = s_q1[j];
+                    const float4* rec = s_rec + j * REC_QUADS;
+                    const float4 q0 = rec[0];
+                    const float4 q1 = rec[1];
                     const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                     const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                     if (power <= 0.0f) {
@@ -121,8 +126,8 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                                 done = true;
                             } else {
                                 const float aT = alpha * T;
-                                const float4 q2 = s_q2[j];
-                                const float4 q3 = s_q3[j];
+                                const float4 q2 = rec[2];
+                                const float4 q3 = rec[3];
                                 C[0] += q2.z * aT;
                                 C[1] += q2.w * aT;
                                 C[2] += q3.x * aT;
@@ -140,15 +145,14 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                         }
                     }
                 }
-                if constexpr (GEOMETRY) {
-                    if (__any_sync(FULL, blended)) bits |= 1u << jj;
-                }
+                if (__any_sync(FULL, blended)) bits |= 1u << jj;
             }
-            if constexpr (GEOMETRY) {
-                const uint32_t gw = i * (BATCH / 32) + w;
-                if (lane == 0 && gw < MASK_WORDS) s_mask[warp][gw] = bits;
-                mask_words = gw + 1;
+            const uint32_t gw = i * (BATCH / 32) + w;
+            if (lane == 0) {
+                if (GEOMETRY && gw < MASK_WORDS) s_mask[warp][gw] = bits;
+                accept_mask[(size_t)(mask_base + gw) * 8 + warp] = bits;  // kept for the backward
             }
+            mask_words = gw + 1;
         }
     }
 
@@ -192,6 +196,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
 #pragma unroll
             for (int s = 1; s < SPLIT; s++) T_p[s] = 1.f;
             const float interval = (depth_max - depth_min) * ONE_OVER_SPLIT;
+            const float depth_hi = depth_min + interval * SPLIT;  // the last sample depth, as the loop forms it
             // last list position any pixel of this warp still needs
             const uint32_t warp_last = __reduce_max_sync(FULL, in_range ? last_contributor : 0u);
             for (int i = 0; i < rounds2; i++) {
@@ -200,9 +205,10 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 if (progress < max_contributor) {
                     const uint32_t id = __ldg(point_list + range.x + progress);
                     const float4* src = reinterpret_cast<const float4*>(records + id);
-                    s_q0[tid] = __ldg(src);
-                    s_q1[tid] = __ldg(src + 1);
-                    s_q2[tid] = __ldg(src + 2);
+                    float4* dst = s_rec + tid * REC_QUADS;
+                    dst[0] = __ldg(src);
+                    dst[1] = __ldg(src + 1);
+                    dst[2] = __ldg(src + 2);
                 }
                 __syncthreads();
                 for (int w = 0; w < BATCH / 32; w++) {
@@ -210,32 +216,38 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                     if (base >= warp_last) break;
                     const uint32_t gw = i * (BATCH / 32) + w;
                     uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
+                    uint32_t keep = 0;  // positions some pixel of the warp can still need in later iterations
                     while (bits) {
                         const int jj = __ffs(bits) - 1;
-                        bits &= bits - 1;
+                        const uint32_t bit = bits & (0u - bits);
+                        bits ^= bit;
                         const uint32_t pos = base + jj + 1;  // 1-based list position == `contributor`
                         if (pos > warp_last) break;
-                        const int j = w * 32 + jj;
-                        const float4 q0 = s_q0[j];
-                        const float4 q1 = s_q1[j];
+                        const float4* rec = s_rec + (w * 32 + jj) * REC_QUADS;
+                        const float4 q0 = rec[0];
+                        const float4 q1 = rec[1];
                         const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                         const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                         const float alpha = fminf(0.99f, q1.y * expf(power));
                         const bool act = in_range && pos <= last_contributor && !(power > 0.0f) &&
                                          !(alpha < 1.0f / 255.0f);
                         if (!__any_sync(FULL, act)) continue;
-                        const float2 rp2 = *reinterpret_cast<const float2*>(&s_q2[j]);
-                        const float t_peak = q1.z * d.x + q1.w * d.y + rp2.x;
-                        const float rsigma = rp2.y;
+                        const float4 q2 = rec[2];
+                        const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
+                        const float rsigma = q2.y;
                         const bool ball = rsigma > 0;
-                        // exact shortcut: the whole bracket is > 16 sigma away from this splat's depth profile
+                        // Exact shortcut.  Every sample depth lies in [depth_min, depth_hi] (rounding is monotone),
+                        // so if that whole interval is more than 16 sigma in front of / behind the splat's peak
+                        // depth then |delta| > 16 at every sample and exp(-delta^2/2) is exactly 0.
                         const float front = depth_min - t_peak;
-                        const float back = t_peak - depth_max;
-                        const float guard = 1e-5f * (depth_max + fabsf(t_peak));
-                        const bool far_front = ball && front * rsigma > FAR_SIGMAS && front > guard;
-                        const bool far_back = ball && back * rsigma > FAR_SIGMAS && back > guard;
-                        const bool near = act && !(far_front || far_back);
-                        if (__any_sync(FULL, near)) {
+                        const float back = t_peak - depth_hi;
+                        const bool far = ball && fmaxf(front, back) * rsigma > FAR_SIGMAS;
+                        const bool far_front = far && front > 0.f;
+                        // may be dropped for good only with some slack: the recomputed depth_hi of a later
+                        // iteration can sit a few ulps above this one
+                        const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
+                        if (__any_sync(FULL, act && !behind_for_good)) keep |= bit;
+                        if (__any_sync(FULL, act && !far)) {
                             if (act) {
                                 if (first) {
 #pragma unroll
@@ -261,6 +273,9 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                             }
                         }
                     }
+                    // positions that were behind every pixel's bracket stay behind it (brackets only shrink):
+                    // drop them from the warp's list.  Unvisited positions (beyond warp_last) are never needed.
+                    if (c1 == 1.0f && lane == 0 && gw < MASK_WORDS && gw < mask_words) s_mask[warp][gw] = keep;
                 }
             }
             if (first) in_range = (T_p[0] >= 0.5f) && (T_p[SPLIT] <= 0.5f) && in_range;
@@ -298,6 +313,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         }
     }
     if (tid == 0) max_contributors[tile_id] = max_contributor;
+    if (lane == 0) warp_words[tile_id * (TILE_PIXELS / 32) + warp] = mask_words;
 }
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
@@ -315,11 +331,11 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     if (require_depth)
         render_forward_kernel<true><<<grid, block, 0, stream>>>(rp, ranges, point_list, records, out.color, out.alpha,
                                                                out.normal, out.mdepth, out.n_contrib,
-                                                               out.max_contributor);
+                                                               out.max_contributor, out.accept_mask, out.warp_words);
     else
         render_forward_kernel<false><<<grid, block, 0, stream>>>(rp, ranges, point_list, records, out.color,
                                                                 out.alpha, out.normal, out.mdepth, out.n_contrib,
-                                                                out.max_contributor);
+                                                                out.max_contributor, out.accept_mask, out.warp_words);
 }
 
 }  // namespace ggs

@@ -67,9 +67,16 @@ def test_backward_vs_reference(tag, require_depth, device, ref_module):
     o_out, o_g = H.run_module(ours, sc, device, require_depth=require_depth)
     r_out, r_g = H.run_module(ref_module, sc, device, require_depth=require_depth)
     _check_images(o_out, r_out)
+    # float atomics make both implementations non-deterministic run to run; on scenes where a pixel's depth
+    # gradient is amplified by the 1/max(-dT/dt, 1e-7) term (render_backward.cu:879) that noise alone can exceed
+    # 1e-4 of the gradient scale.  Measure the floor and only ever widen the tolerance by it.
+    _, o_g2 = H.run_module(ours, sc, device, require_depth=require_depth)
+    _, r_g2 = H.run_module(ref_module, sc, device, require_depth=require_depth)
     for k in H.GRAD_NAMES:
         err = H.grad_rel_err(o_g[k], r_g[k])
-        assert err <= H.GRAD_TOL, f"grad {k}: rel err {err:.3e}"
+        noise = max(H.grad_rel_err(o_g2[k], o_g[k]), H.grad_rel_err(r_g2[k], r_g[k]))
+        assert noise <= 1e-3, f"grad {k}: run-to-run noise {noise:.3e}"
+        assert err <= max(H.GRAD_TOL, 3.0 * noise), f"grad {k}: rel err {err:.3e} (noise floor {noise:.3e})"
 
 
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
