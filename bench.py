@@ -169,13 +169,12 @@ class Step:
             cov3D_precomp=None)
         torch.autograd.backward([color, mdepth, alpha, normal], [g["color"], g["mdepth"], g["alpha"], g["normal"]])
         if self.allreduce:
-            import torch.distributed as dist
-
-            grads = [p[k].grad.reshape(-1) for k in ("means3D", "opacities", "scales", "rotations", "shs")]
+            # one NCCL all-reduce over the flat bucket of all parameter gradients (59 floats per Gaussian at SH3)
             if self.flat is None:
-                self.flat = torch.empty(sum(x.numel() for x in grads), device=self.device)
-            torch.cat(grads, out=self.flat)
-            dist.all_reduce(self.flat)
+                from diff_gaussian_rasterization.parallel import GradientBucket
+
+                self.flat = GradientBucket([p[k] for k in ("means3D", "opacities", "scales", "rotations", "shs")])
+            self.flat.allreduce()
         return color
 
     def resident(self):

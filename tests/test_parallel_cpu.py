@@ -1,0 +1,103 @@
+"""World-size-2 gloo tests of the multi-GPU plumbing (view-parallel gradient all-reduce, point-range sharding
+of integrate).  Only the collectives run here; the rasterizer itself needs a GPU."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import helpers  # noqa: F401  (sys.path)
+from diff_gaussian_rasterization import parallel
+
+
+def test_shard_range_covers_everything():
+    for n in (0, 1, 7, 8, 9, 50_000_001):
+        for world in (1, 2, 3, 8):
+            spans = [parallel.shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            for a, b in zip(spans, spans[1:]):
+                assert a[1] == b[0]
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        parallel.shard_range(10, 2, 2)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # ---- gradient bucket: rank r holds gradient (r+1) * pattern; the sum is 3 * pattern at world 2 ----
+        g = torch.Generator().manual_seed(0)
+        shapes = [(100, 3), (100, 1), (100, 16, 3), (100, 4)]
+        pattern = [torch.randn(*s, generator=g) for s in shapes]
+        params = [torch.zeros(*s, requires_grad=True) for s in shapes]
+        for p, pat in zip(params, pattern):
+            p.grad = (rank + 1) * pat.clone()
+        params[1].grad = None  # a missing gradient counts as zero
+        bucket = parallel.GradientBucket(params)
+        flat = bucket.allreduce()
+        total = sum(r + 1 for r in range(world))
+        ok = flat.numel() == sum(p.numel() for p in params)
+        for i, (p, pat) in enumerate(zip(params, pattern)):
+            want = torch.zeros_like(pat) if i == 1 else total * pat
+            ok = ok and torch.allclose(p.grad, want, rtol=1e-6, atol=1e-6)
+        # a second reduction reuses the views without copying
+        for p, pat in zip(params, pattern):
+            p.grad.copy_((rank + 1) * pat)
+        bucket.allreduce(average=True)
+        ok = ok and torch.allclose(params[0].grad, total * pattern[0] / world, rtol=1e-6, atol=1e-6)
+
+        # ---- integrate sharding: a stand-in for rasterizer.integrate that is a pure function of the point ----
+        calls = []
+
+        def fake_integrate(pts):
+            calls.append(pts.shape[0])
+            return pts.sum(dim=1) * 0.5, pts[:, 0] > 0
+
+        pts = torch.randn(1001, 3, generator=torch.Generator().manual_seed(5))
+        a, ins = parallel.integrate_sharded(fake_integrate, pts)
+        lo, hi = parallel.shard_range(1001, rank, world)
+        ok = ok and calls == [hi - lo]
+        ok = ok and torch.equal(a, pts.sum(dim=1) * 0.5) and torch.equal(ins, pts[:, 0] > 0)
+        # fewer points than ranks, and zero points
+        a1, i1 = parallel.integrate_sharded(fake_integrate, pts[:1])
+        ok = ok and torch.equal(a1, pts[:1].sum(dim=1) * 0.5) and i1.shape == (1,)
+        a0, i0 = parallel.integrate_sharded(fake_integrate, pts[:0])
+        ok = ok and a0.numel() == 0 and i0.numel() == 0
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_allreduce_and_point_sharding():
+    world = 2
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert dict(ret) == {0: True, 1: True}
+
+
+def test_single_process_paths_need_no_group():
+    pts = torch.randn(10, 3)
+    a, i = parallel.integrate_sharded(lambda p: (p[:, 0], p[:, 1] > 0), pts)
+    assert torch.equal(a, pts[:, 0]) and torch.equal(i, pts[:, 1] > 0)
+    p = torch.zeros(4, requires_grad=True)
+    p.grad = torch.ones(4)
+    b = parallel.GradientBucket([p])
+    b.allreduce()
+    assert torch.equal(p.grad, torch.ones(4))
