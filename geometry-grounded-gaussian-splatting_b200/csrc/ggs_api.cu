@@ -181,6 +181,11 @@ uint32_t* accept_mask(void* bin, int64_t D, int tiles) {
     return at<uint32_t>(bin, BL.accept_mask);
 }
 
+uint32_t* near_mask(void* bin, int64_t D, int tiles) {
+    const BinLayout BL = bin_layout((size_t)D, sort_passes(0, sort_end_bit(tiles)), tiles);
+    return at<uint32_t>(bin, BL.near_mask);
+}
+
 }  // namespace
 
 extern "C" {
@@ -248,6 +253,8 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     ro.max_contributor = at<uint32_t>(tile, TL.max_contributor);
     ro.accept_mask = accept_mask(bin, D, tiles);
     ro.warp_words = at<uint32_t>(tile, TL.warp_words);
+    ro.near_mask = near_mask(bin, D, tiles);
+    ro.near_first = at<uint32_t>(tile, TL.near_first);
     launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, D, tiles),
                           at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
     GGS_STAGE("render_forward", debug, stream);
@@ -296,6 +303,8 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     ri.max_contributor = at<uint32_t>(state->tile, TL.max_contributor);
     ri.accept_mask = accept_mask(state->binning, state->num_rendered, tiles);
     ri.warp_words = at<uint32_t>(state->tile, TL.warp_words);
+    ri.near_mask = near_mask(state->binning, state->num_rendered, tiles);
+    ri.near_first = at<uint32_t>(state->tile, TL.near_first);
     ri.dL_dcolor = bi->dL_dcolor;
     ri.dL_dmdepth = bi->dL_dmdepth;
     ri.dL_dalpha = bi->dL_dalpha;

@@ -16,6 +16,7 @@ constexpr int SPLIT = 8;                    // config.h:32
 constexpr float SAMPLE_RANGE = 0.4f;        // config.h:34 (TRAINING)
 constexpr int SPLIT_ITERATIONS = 5;         // config.h:35 (TRAINING)
 constexpr int POINT_BATCH = 2;              // config.h:27 SAMPLE_BATCH_SIZE
+constexpr int MASK_WORDS = 256;  // per warp, words of the acceptance mask the forward keeps (and thins) in shared memory
 
 // Per-Gaussian record consumed by the tile kernels: 16 floats = one 64-byte, 64-byte aligned
 // gather unit (two full 32-byte sectors, no wasted bytes).
@@ -119,6 +120,8 @@ struct BinLayout {
     size_t status;          // u32[passes][tiles][RADIX] decoupled look-back descriptors
     size_t counters;        // u32[MAX_PASSES] dynamic tile ids
     size_t accept_mask;     // u32[(D/32 + tiles) * 8]: per (tile, warp) bitmask of blended list positions
+    size_t near_mask;       // same shape: accept_mask thinned to the positions whose depth profile can still be
+                            // non-zero at the pixel's median depth (what the backward's dT/dt pass must visit)
     size_t bytes;
     size_t status_bytes;
 };
@@ -141,6 +144,7 @@ inline BinLayout bin_layout(size_t D, int passes, size_t tiles_for_mask = 0) {
     L.status = take(L.status_bytes);
     L.counters = take(MAX_PASSES * 4);
     L.accept_mask = take(tiles_for_mask ? (D / 32 + tiles_for_mask + 1) * 8 * 4 : 0);
+    L.near_mask = take(tiles_for_mask ? (D / 32 + tiles_for_mask + 1) * 8 * 4 : 0);
     L.bytes = o;
     return L;
 }
@@ -149,6 +153,7 @@ struct TileLayout {
     size_t ranges;           // uint2[tiles]
     size_t max_contributor;  // u32[tiles]
     size_t warp_words;       // u32[tiles][8]: words of accept_mask each warp of the tile produced
+    size_t near_first;       // u32[tiles][8]: list positions <= this are exactly zero in the warp's dT/dt pass
     size_t bytes;
 };
 inline TileLayout tile_layout(size_t tiles) {
@@ -156,7 +161,8 @@ inline TileLayout tile_layout(size_t tiles) {
     L.ranges = 0;
     L.max_contributor = align_up(tiles * 8, 256);
     L.warp_words = L.max_contributor + align_up(tiles * 4, 256);
-    L.bytes = L.warp_words + align_up(tiles * 32, 256);
+    L.near_first = L.warp_words + align_up(tiles * 32, 256);
+    L.bytes = L.near_first + align_up(tiles * 32, 256);
     return L;
 }
 

@@ -59,6 +59,8 @@ struct RenderOut {
     uint32_t* max_contributor;
     uint32_t* accept_mask;  // see BinLayout::accept_mask
     uint32_t* warp_words;   // see TileLayout::warp_words
+    uint32_t* near_mask;    // see BinLayout::near_mask
+    uint32_t* near_first;   // see TileLayout::near_first
 };
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
                            const SplatRecord* records, const RenderOut& out, bool require_depth,
@@ -73,6 +75,8 @@ struct RenderBwdIn {
     const uint32_t* max_contributor;
     const uint32_t* accept_mask;
     const uint32_t* warp_words;
+    const uint32_t* near_mask;
+    const uint32_t* near_first;
     const float* dL_dcolor;
     const float* dL_dmdepth;
     const float* dL_dalpha;

@@ -3,13 +3,19 @@
 //           dL_dmt_dT_dtm = dL/dmdepth * rln / max(-dT/dt_m, 1e-7);
 //   pass B: back-to-front over [0, max_contributor), recomputing alpha, with the colour / normal
 //           "accumulated behind" recurrences, depth-term gradients and dL/dalpha.
-// One CTA per 16x16 tile; warp w owns an 8x4 pixel block, as in the forward.  Both passes walk only the
-// list positions that the forward recorded as blended by at least one pixel of the warp (accept_mask):
-// about a third of the list.  Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
+// One CTA per 16x16 tile; warp w owns an 8x4 pixel block, as in the forward.  Pass B walks only the list
+// positions that the forward recorded as blended by at least one pixel of the warp (accept_mask): about a
+// third of the list.  Pass A walks fewer still: every term of dT/dt_m carries exp(-delta^2/2) of the splat's
+// depth profile at the median depth, which is exactly 0 (ex2.approx.ftz underflow) for the splats the forward's
+// bisection classified as far from the pixel's final bracket -- the forward exports that thinned mask
+// (near_mask) and the end of each warp's constant prefix (near_first).  Adding an exact zero changes nothing,
+// so skipping those entries is exact.  Batches are staged with cp.async into a double buffer (ggs_tile.cuh).
+// Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
 // scalar atomics from one lane (the reference), the warp runs ONE transposing butterfly (20
 // shuffles) that leaves component c on its own lane, and those 17 lanes issue a single predicated
 // RED into the entry's contiguous 80-byte accumulator row.
 #include "ggs_kernels.cuh"
+#include "ggs_tile.cuh"
 
 namespace ggs {
 
@@ -19,8 +25,10 @@ struct RenderBwdParams {
     const float* bg;  // device [3]
 };
 
-constexpr int BATCH_B = TILE_PIXELS;
-constexpr int REC_QUADS_B = 5;  // 80-byte shared-memory stride (see ggs_render_forward.cu)
+constexpr int BATCH_B = TILE_BATCH;
+constexpr int REC_QUADS_B = REC_QUADS;
+constexpr size_t BWD_REC_BYTES = (size_t)2 * STAGE_QUADS * sizeof(float4);
+constexpr size_t BWD_ID_BYTES = (size_t)2 * BATCH_B * sizeof(uint32_t);
 constexpr uint32_t FULL_B = 0xffffffffu;
 
 // Butterfly reduce-scatter of 17 values (v[17] must be 0).  Returns the warp-wide sum of component
@@ -89,11 +97,15 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                            const float* __restrict__ alphas, const float* __restrict__ normalmap,
                            const float* __restrict__ mdepth, const uint32_t* __restrict__ n_contrib,
                            const uint32_t* __restrict__ max_contributors, const uint32_t* __restrict__ accept_mask,
-                           const uint32_t* __restrict__ warp_words, const float* __restrict__ dL_dpixels,
+                           const uint32_t* __restrict__ warp_words, const uint32_t* __restrict__ near_mask,
+                           const uint32_t* __restrict__ near_first, const float* __restrict__ dL_dpixels,
                            const float* __restrict__ dL_dpixel_mdepths, const float* __restrict__ dL_dalphas,
                            const float* __restrict__ dL_dpixel_normals, float* __restrict__ grad_acc) {
-    __shared__ uint32_t s_id[BATCH_B];
-    __shared__ float4 s_rec[BATCH_B * REC_QUADS_B];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* const s_rec = reinterpret_cast<float4*>(smem_raw);                     // [2][STAGE_QUADS]
+    uint32_t* const s_id = reinterpret_cast<uint32_t*>(smem_raw + BWD_REC_BYTES);  // [2][BATCH_B]
+    __shared__ uint32_t s_first[TILE_WARPS];
+    __shared__ uint32_t s_last[TILE_WARPS];
 
     const int W = rp.W, H = rp.H;
     const size_t HW = (size_t)H * W;
@@ -111,6 +123,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const uint2 range = ranges[tile_id];
     const uint32_t max_contributor = max_contributors[tile_id];
     const uint32_t mask_base = range.x / 32 + tile_id;
+    const uint32_t* const list = point_list + range.x;
     const uint32_t mask_words = warp_words[tile_id * (TILE_PIXELS / 32) + warp];
     const uint32_t* my_mask = accept_mask + (size_t)mask_base * 8 + warp;  // word gw at my_mask[gw * 8]
 
@@ -158,29 +171,53 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         float dT_dtm = 0.f;
         const bool live = !((mDepth == 0) || (last_contributor == 0) || !inside);
         const uint32_t warp_last_a = __reduce_max_sync(FULL_B, live ? last_contributor : 0u);
-        for (int i = 0; i < rounds; i++) {
+        // list positions <= nf have exp() == 0 at this warp's median depths (the forward folded them)
+        const uint32_t nf = near_first[tile_id * TILE_WARPS + warp];
+        const uint32_t* my_near = near_mask + (size_t)mask_base * 8 + warp;
+        if (lane == 0) {
+            s_first[warp] = warp_last_a ? min(nf, warp_last_a) : 0xffffffffu;
+            s_last[warp] = warp_last_a;
+        }
+        __syncthreads();
+        uint32_t block_first = 0xffffffffu, block_last = 0;
+#pragma unroll
+        for (int w = 0; w < TILE_WARPS; w++) {
+            block_first = min(block_first, s_first[w]);
+            block_last = max(block_last, s_last[w]);
+        }
+        const int b0 = block_last ? block_first / BATCH_B : 0;
+        const int b1 = (block_last + BATCH_B - 1) / BATCH_B;
+        uint32_t id_next = 0;
+        if (b0 < b1) {
+            const uint32_t e = b0 * BATCH_B + tid;
+            if (e < block_last) stage_record(s_rec, tid, records, __ldg(list + e), 3);
+            cp_async_commit();
+            if (e + BATCH_B < block_last) id_next = __ldg(list + e + BATCH_B);
+        }
+        for (int i = b0; i < b1; i++) {
+            cp_async_wait_all();
             __syncthreads();
-            const uint32_t progress = i * BATCH_B + tid;
-            if (progress < max_contributor) {
-                const uint32_t id = __ldg(point_list + range.x + progress);
-                const float4* src = reinterpret_cast<const float4*>(records + id);
-                float4* dst = s_rec + tid * REC_QUADS_B;
-                dst[0] = __ldg(src);
-                dst[1] = __ldg(src + 1);
-                dst[2] = __ldg(src + 2);
+            const int k = i - b0;
+            const float4* const buf = s_rec + (k & 1) * STAGE_QUADS;
+            if (i + 1 < b1) {
+                const uint32_t e = (i + 1) * BATCH_B + tid;
+                if (e < block_last) stage_record(s_rec + ((k + 1) & 1) * STAGE_QUADS, tid, records, id_next, 3);
+                cp_async_commit();
+                if (e + BATCH_B < block_last) id_next = __ldg(list + e + BATCH_B);
             }
-            __syncthreads();
             for (int w = 0; w < BATCH_B / 32; w++) {
                 const uint32_t base = i * BATCH_B + w * 32;
                 if (base >= warp_last_a) break;
+                if (base + 32 <= nf) continue;
                 const uint32_t gw = i * (BATCH_B / 32) + w;
-                uint32_t bits = gw < mask_words ? __ldg(my_mask + (size_t)gw * 8) : 0u;
+                uint32_t bits = gw < mask_words ? __ldg((gw < MASK_WORDS ? my_near : my_mask) + (size_t)gw * 8) : 0u;
                 while (bits) {
                     const int jj = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const uint32_t pos = base + jj + 1;
                     if (pos > warp_last_a) break;
-                    const float4* rec = s_rec + (w * 32 + jj) * REC_QUADS_B;
+                    if (pos <= nf) continue;
+                    const float4* rec = buf + (w * 32 + jj) * REC_QUADS_B;
                     const float4 q0 = rec[0];
                     const float4 q1 = rec[1];
                     const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
@@ -200,6 +237,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 }
             }
         }
+        __syncthreads();  // pass B reuses the staging buffers
         dL_dmt_dT_dtm = dL_dpixel_mt / fmaxf(-dT_dtm, 1e-7f);
     }
 
@@ -212,20 +250,31 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const float ddely_dy = 0.5f * H;
     const int my_comp = warp_component(lane);
 
-    for (int i = rounds - 1; i >= 0; i--) {
-        __syncthreads();
-        const uint32_t progress = i * BATCH_B + tid;
-        if (progress < max_contributor) {
-            const uint32_t id = __ldg(point_list + range.x + progress);
+    // batches are walked back to front; batch i is staged into buffer (rounds - 1 - i) & 1
+    {
+        const uint32_t e = (rounds - 1) * BATCH_B + tid;
+        if (rounds > 0 && e < max_contributor) {
+            const uint32_t id = __ldg(list + e);
             s_id[tid] = id;
-            const float4* src = reinterpret_cast<const float4*>(records + id);
-            float4* dst = s_rec + tid * REC_QUADS_B;
-            dst[0] = __ldg(src);
-            dst[1] = __ldg(src + 1);
-            dst[2] = __ldg(src + 2);
-            dst[3] = __ldg(src + 3);
+            stage_record(s_rec, tid, records, id, 4);
         }
+        cp_async_commit();
+    }
+    uint32_t id_prev = 0;
+    if (rounds > 1) id_prev = __ldg(list + (rounds - 2) * BATCH_B + tid);
+    for (int i = rounds - 1; i >= 0; i--) {
+        cp_async_wait_all();
         __syncthreads();
+        const int k = rounds - 1 - i;
+        const float4* const buf = s_rec + (k & 1) * STAGE_QUADS;
+        const uint32_t* const ids = s_id + (k & 1) * BATCH_B;
+        if (i > 0) {
+            // batch i-1 is full (only the last batch of the list can be partial)
+            s_id[((k + 1) & 1) * BATCH_B + tid] = id_prev;
+            stage_record(s_rec + ((k + 1) & 1) * STAGE_QUADS, tid, records, id_prev, 4);
+            cp_async_commit();
+            if (i > 1) id_prev = __ldg(list + (i - 2) * BATCH_B + tid);
+        }
 
         for (int w = BATCH_B / 32 - 1; w >= 0; w--) {
             const uint32_t base = i * BATCH_B + w * 32;
@@ -237,7 +286,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 bits ^= 1u << jj;
                 const uint32_t idx = base + jj;  // 0-based list position == the reference's `contributor`
                 const int j = w * 32 + jj;
-                const float4* rec = s_rec + j * REC_QUADS_B;
+                const float4* rec = buf + j * REC_QUADS_B;
                 const float4 q0 = rec[0];
                 const float4 q1 = rec[1];
                 const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
@@ -327,7 +376,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 const float sum = warp_reduce_scatter17(v, lane);
                 if (my_comp >= 0) {
                     if (GEOMETRY || my_comp < 10)
-                        atomicAdd(grad_acc + (size_t)s_id[j] * GRAD_STRIDE + my_comp, sum);
+                        atomicAdd(grad_acc + (size_t)ids[j] * GRAD_STRIDE + my_comp, sum);
                 }
             }
         }
@@ -346,14 +395,23 @@ void launch_render_backward(const FrameParams& fp, const uint2* ranges, const ui
     rp.bg = fp.view.bg;
     const dim3 grid(fp.gx, fp.gy, 1);
     const dim3 block(TILE_PIXELS, 1, 1);
+    constexpr size_t SMEM = BWD_REC_BYTES + BWD_ID_BYTES;
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(render_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
+        cudaFuncSetAttribute(render_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
+        configured = true;
+    }
     if (require_depth)
-        render_backward_kernel<true><<<grid, block, 0, stream>>>(
+        render_backward_kernel<true><<<grid, block, SMEM, stream>>>(
             rp, ranges, point_list, records, in.alpha, in.normal, in.mdepth, in.n_contrib, in.max_contributor,
-            in.accept_mask, in.warp_words, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
+            in.accept_mask, in.warp_words, in.near_mask, in.near_first, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha,
+            in.dL_dnormal, grad_acc);
     else
-        render_backward_kernel<false><<<grid, block, 0, stream>>>(
+        render_backward_kernel<false><<<grid, block, SMEM, stream>>>(
             rp, ranges, point_list, records, in.alpha, in.normal, in.mdepth, in.n_contrib, in.max_contributor,
-            in.accept_mask, in.warp_words, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha, in.dL_dnormal, grad_acc);
+            in.accept_mask, in.warp_words, in.near_mask, in.near_first, in.dL_dcolor, in.dL_dmdepth, in.dL_dalpha,
+            in.dL_dnormal, grad_acc);
 }
 
 }  // namespace ggs

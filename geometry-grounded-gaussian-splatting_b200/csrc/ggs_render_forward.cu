@@ -8,16 +8,24 @@
 //     first iteration and 7 new ones afterwards, linear interpolation at the end.
 //
 // Design (one CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel block):
-//   * list entries are gathered as 64-byte SplatRecords into shared memory, 256 per batch;
-//   * pass 1 leaves, per warp, a bitmask of the list positions that at least one of its pixels blended.
-//     The five bisection passes walk only those positions (about one third of the list), instead of
-//     re-testing every entry against every pixel as the reference does;
-//   * in a bisection pass a splat whose depth profile is more than 16 sigma away from the whole current
-//     bracket contributes exp() == 0 exactly (ex2.approx.ftz underflows), so its factor is exactly
-//     (1 - alpha) in front of the bracket and exactly 1 behind it: no exp / rsqrt is issued for it unless
-//     some pixel of the warp is close to it.  Brackets shrink 8x per iteration, so most splats are "far"
-//     in iterations 2-5.  Both shortcuts are exact: outputs are bit-identical to the plain evaluation.
+//   * list entries are gathered as 64-byte SplatRecords into shared memory, 256 per batch, with cp.async
+//     into a double buffer: the gather of batch i+1 overlaps the arithmetic on batch i, one barrier per batch;
+//   * pass 1: each lane first tests ONE entry of a 32-entry chunk against the warp's 8x4 pixel rectangle
+//     (exact minimum of the conic's quadratic form over the rectangle against the alpha >= 1/255 threshold,
+//     with slack); only entries that can touch the rectangle are evaluated per pixel.  The pass leaves, per
+//     warp, a bitmask of the list positions that at least one of its pixels blended;
+//   * the five bisection passes walk only those positions.  A splat whose depth profile is more than 16 sigma
+//     away from the whole current bracket contributes exp() == 0 exactly (ex2.approx.ftz underflows), so its
+//     factor is exactly (1 - alpha) in front of the bracket and exactly 1 behind it: no exp / rsqrt is issued
+//     for it unless some pixel of the warp is close to it.  Brackets only shrink, so such a splat stays far:
+//       - the leading run of far / inactive entries of a pixel multiplies every sample by the same floats in
+//         the same order in every iteration: its product is carried over (pre_T, pre_pos) instead of being
+//         recomputed, and the warp starts its walk after the shortest such prefix of its pixels;
+//       - entries behind every pixel's bracket for good are dropped from the warp's mask.
+//     All shortcuts keep the order of the per-pixel floating-point products: outputs are bit-identical to
+//     the plain evaluation.  The thinned mask and the prefix end are exported for the backward's dT/dt pass.
 #include "ggs_kernels.cuh"
+#include "ggs_tile.cuh"
 
 namespace ggs {
 
@@ -27,12 +35,46 @@ struct RenderParams {
     const float* bg;  // device [3]
 };
 
-constexpr int BATCH = TILE_PIXELS;
-
-constexpr int REC_QUADS = 5;
-constexpr int MASK_WORDS = 256;  // per warp: acceptance bits for the first 8192 list positions
+constexpr int BATCH = TILE_BATCH;
+constexpr int WARPS = TILE_WARPS;
 constexpr uint32_t FULL = 0xffffffffu;
-constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0
+constexpr uint32_t NEVER = 0xffffffffu;
+constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0 (it does from 13.3 sigma on)
+constexpr size_t REC_BYTES = (size_t)2 * BATCH * REC_QUADS * sizeof(float4);
+constexpr size_t MASK_BYTES = (size_t)WARPS * MASK_WORDS * sizeof(uint32_t);
+
+// Can the splat (q0 = mean.xy, conic.xy; q1 = conic.z, opacity, ..) reach alpha >= 1/255 on any pixel centre of
+// the rectangle [x0, x0+7] x [y0, y0+3]?  Conservative: `false` only when every pixel is provably rejected.
+//   alpha = min(0.99, o * exp(power)) >= 1/255  needs  -power = q(d)/2 <= log(255 o),  q(d) = A dx^2 + 2 B dx dy + C dy^2.
+// The minimum of the convex q over the rectangle of offsets d is 0 when the rectangle contains the centre and
+// otherwise lies on one of the four edges, where it is a clamped 1-D parabola minimum.
+__device__ __forceinline__ bool may_touch(const float4 q0, const float4 q1, float x0, float y0) {
+    const float A = q0.z, B = q0.w, C = q1.x, o = q1.y;
+    const float dx1 = q0.x - x0, dx0 = dx1 - 7.f;  // d = mean - pixel ranges over [dx0, dx1] x [dy0, dy1]
+    const float dy1 = q0.y - y0, dy0 = dy1 - 3.f;
+    const float det = A * C - B * B;
+    if (!(A > 0.f && C > 0.f && det > 0.f)) return true;  // not positive definite (or NaN): no claim
+    const float L = __logf(255.f * o);
+    if (L < -0.01f) return false;  // o < 1/255: power <= 0 can never lift alpha over the threshold
+    if (dx0 <= 0.f && dx1 >= 0.f && dy0 <= 0.f && dy1 >= 0.f) return true;
+    const float rA = __frcp_rn(A), rC = __frcp_rn(C);
+    float qmin;
+    {
+        const float ya = fminf(fmaxf(-B * dx0 * rC, dy0), dy1);
+        const float yb = fminf(fmaxf(-B * dx1 * rC, dy0), dy1);
+        const float xa = fminf(fmaxf(-B * dy0 * rA, dx0), dx1);
+        const float xb = fminf(fmaxf(-B * dy1 * rA, dx0), dx1);
+        const float e0 = A * dx0 * dx0 + 2.f * B * dx0 * ya + C * ya * ya;
+        const float e1 = A * dx1 * dx1 + 2.f * B * dx1 * yb + C * yb * yb;
+        const float e2 = A * xa * xa + 2.f * B * xa * dy0 + C * dy0 * dy0;
+        const float e3 = A * xb * xb + 2.f * B * xb * dy1 + C * dy1 * dy1;
+        qmin = fminf(fminf(e0, e1), fminf(e2, e3));
+    }
+    // rounding slack: both this evaluation and the per-pixel `power` are sums of terms bounded by M
+    const float Dx = fmaxf(fabsf(dx0), fabsf(dx1)), Dy = fmaxf(fabsf(dy0), fabsf(dy1));
+    const float M = A * Dx * Dx + 2.f * fabsf(B) * Dx * Dy + C * Dy * Dy;
+    return !(0.5f * qmin - 1e-5f * M > L + 0.01f);
+}
 
 // One depth sample of the vacancy-corrected transmittance product (render_forward.cu:603-621).
 __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsigma, bool ball, float alpha) {
@@ -44,276 +86,339 @@ __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsi
 }
 
 template <bool GEOMETRY>
-__global__ void __launch_bounds__(TILE_PIXELS)
+__global__ void __launch_bounds__(TILE_PIXELS, 4)
     render_forward_kernel(const RenderParams rp, const uint2* __restrict__ ranges,
                           const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
                           float* __restrict__ out_color, float* __restrict__ out_alpha,
                           float* __restrict__ out_normal, float* __restrict__ out_mdepth,
                           uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ max_contributors,
-                          uint32_t* __restrict__ accept_mask, uint32_t* __restrict__ warp_words) {
-    // staged records, 80-byte stride (4 payload quads + 1 pad): conflict-free 16-byte stores by 8 consecutive
-    // threads, and one address computation per entry on the (broadcast) read side
-    __shared__ float4 s_rec[BATCH * REC_QUADS];
-    __shared__ uint32_t s_mask[GEOMETRY ? TILE_PIXELS / 32 : 1][GEOMETRY ? MASK_WORDS : 1];
-    __shared__ uint32_t s_red[TILE_PIXELS / 32];
-    __shared__ uint32_t s_block_max;
+                          uint32_t* __restrict__ accept_mask, uint32_t* __restrict__ warp_words,
+                          uint32_t* __restrict__ near_mask, uint32_t* __restrict__ near_first) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* const s_rec = reinterpret_cast<float4*>(smem_raw);  // [2][BATCH * REC_QUADS]
+    uint32_t(*const s_mask)[MASK_WORDS] = reinterpret_cast<uint32_t(*)[MASK_WORDS]>(smem_raw + REC_BYTES);
+    __shared__ uint32_t s_red[WARPS];
+    __shared__ uint32_t s_first[WARPS];
+    __shared__ uint32_t s_last[WARPS];
 
     const int W = rp.W, H = rp.H;
     const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
     const uint32_t tid = threadIdx.x;
     const uint32_t warp = tid >> 5, lane = tid & 31;
     // warp w owns the 8x4 pixel block (w & 1, w >> 1) of the tile
-    const uint2 pix = {blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7), blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3)};
+    const uint2 pix0 = {blockIdx.x * TILE_X + (warp & 1) * 8, blockIdx.y * TILE_Y + (warp >> 1) * 4};
+    const uint2 pix = {pix0.x + (lane & 7), pix0.y + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
-    const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
-                          (pixf.y - static_cast<float>(H - 1) / 2.f) / rp.focal_y};
-    const float rln = rnorm3df(pixnf.x, pixnf.y, 1.f);
 
     const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
     bool done = !inside;
 
     const uint2 range = ranges[tile_id];
-    const int rounds = ((range.y - range.x + BATCH - 1) / BATCH);
-    int toDo = range.y - range.x;
-    // first word of this tile in the global acceptance mask (tiles are laid out in list order, one spare word each)
+    const uint32_t n = range.y - range.x;
+    const int rounds = (n + BATCH - 1) / BATCH;
+    const uint32_t* const list = point_list + range.x;
+    // first word of this tile in the global acceptance masks (tiles are laid out in list order, one spare word each)
     const uint32_t mask_base = range.x / 32 + tile_id;
 
     float T = 1.0f;
-    uint32_t contributor = 0;
     uint32_t last_contributor = 0;
-    float C[3] = {0.f, 0.f, 0.f};
-    float Normal[3] = {0.f, 0.f, 0.f};
     float mDepthinit = 0.f;
-    uint32_t mask_words = 0;  // words of s_mask[warp] that pass 1 produced (warp-uniform)
+    uint32_t mask_words = 0;  // words of the warp's mask that pass 1 produced (warp-uniform)
 
-    for (int i = 0; i < rounds; i++, toDo -= BATCH) {
-        const int block_done = __syncthreads_and(done);
-        if (block_done) break;
-
-        const int progress = i * BATCH + tid;
-        if (range.x + progress < range.y) {
-            const uint32_t id = __ldg(point_list + range.x + progress);
-            const float4* src = reinterpret_cast<const float4*>(records + id);
-            float4* dst = s_rec + tid * REC_QUADS;
-            dst[0] = __ldg(src);
-            dst[1] = __ldg(src + 1);
-            dst[2] = __ldg(src + 2);
-            dst[3] = __ldg(src + 3);
-        }
-        __syncthreads();
-
-        const int lim = min(BATCH, toDo);
-        for (int w = 0; w * 32 < lim; w++) {
-            if (__all_sync(FULL, done)) break;
-            uint32_t bits = 0;
-            const int jend = min(32, lim - w * 32);
-            for (int jj = 0; jj < jend; jj++) {
-                const int j = w * 32 + jj;
-                bool blended = false;
-                if (!done) {
-                    contributor++;
-                    const float4* rec = s_rec + j * REC_QUADS;
-                    const float4 q0 = rec[0];
-                    const float4 q1 = rec[1];
-                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                    if (power <= 0.0f) {
-                        const float alpha = fminf(0.99f, q1.y * expf(power));
-                        if (alpha >= 1.0f / 255.0f) {
-                            const float test_T = T * (1.f - alpha);
-                            if (test_T < 0.0001f) {
-                                done = true;
-                            } else {
-                                const float aT = alpha * T;
-                                const float4 q2 = rec[2];
-                                const float4 q3 = rec[3];
-                                C[0] += q2.z * aT;
-                                C[1] += q2.w * aT;
-                                C[2] += q3.x * aT;
-                                if constexpr (GEOMETRY) {
-                                    const float t = q1.z * d.x + q1.w * d.y + q2.x;
-                                    Normal[0] += q3.y * aT;
-                                    Normal[1] += q3.z * aT;
-                                    Normal[2] += q3.w * aT;
-                                    mDepthinit = T > 0.5f ? t : mDepthinit;
-                                }
-                                T = test_T;
-                                last_contributor = contributor;
-                                blended = true;
-                            }
-                        }
-                    }
-                }
-                if (__any_sync(FULL, blended)) bits |= 1u << jj;
-            }
-            const uint32_t gw = i * (BATCH / 32) + w;
-            if (lane == 0) {
-                if (GEOMETRY && gw < MASK_WORDS) s_mask[warp][gw] = bits;
-                accept_mask[(size_t)(mask_base + gw) * 8 + warp] = bits;  // kept for the backward
-            }
-            mask_words = gw + 1;
-        }
-    }
-
-    // block-wide max of last_contributor
+    // ---- pass 1: colour / normal / alpha ---------------------------------------------------------------
     {
-        const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
-        if (lane == 0) s_red[warp] = wmax;
-        __syncthreads();
-        if (tid == 0) {
-            uint32_t m = 0;
-#pragma unroll
-            for (int w = 0; w < TILE_PIXELS / 32; w++) m = max(m, s_red[w]);
-            s_block_max = m;
-        }
-        __syncthreads();
-    }
-    const uint32_t max_contributor = s_block_max;
+        float C[3] = {0.f, 0.f, 0.f};
+        float Normal[3] = {0.f, 0.f, 0.f};
+        const float rx0 = static_cast<float>(pix0.x), ry0 = static_cast<float>(pix0.y);
+        uint32_t id_next = 0;
+        if (tid < n) stage_record(s_rec, tid, records, __ldg(list + tid), 4);
+        cp_async_commit();
+        if (BATCH + tid < n) id_next = __ldg(list + BATCH + tid);
 
-    float mDepth = 0.f;
-    if constexpr (GEOMETRY) {
-        const int rounds2 = (max_contributor + BATCH - 1) / BATCH;
-        float T_p[SPLIT + 1];
-        float depth_min = fmaxf(mDepthinit - SAMPLE_RANGE, 0.f);
-        float depth_max = fmaxf(mDepthinit + SAMPLE_RANGE, 0.f);
-        bool in_range = T <= MIN_TRANSMITTANCE;
-        // rsqrt.approx(1.0): the vacancy factor of a splat whose Gaussian term underflowed
-        float c1;
-        {
-            const float one = 1.0f;
-            asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(c1) : "f"(one));
-        }
-
-#pragma unroll 1
-        for (int it = 0; it < SPLIT_ITERATIONS; it++) {
-            const bool first = (it == 0);
-            constexpr float ONE_OVER_SPLIT = 1.f / static_cast<float>(SPLIT);
-            if (first) {
-                T_p[0] = 1.f;
-                T_p[SPLIT] = 1.f;
+        for (int i = 0; i < rounds; i++) {
+            cp_async_wait_all();
+            if (__syncthreads_and(done)) break;
+            const float4* const buf = s_rec + (i & 1) * (BATCH * REC_QUADS);
+            if (i + 1 < rounds) {
+                const uint32_t e = (i + 1) * BATCH + tid;
+                if (e < n) stage_record(s_rec + ((i + 1) & 1) * (BATCH * REC_QUADS), tid, records, id_next, 4);
+                cp_async_commit();
+                if (e + BATCH < n) id_next = __ldg(list + e + BATCH);
             }
-#pragma unroll
-            for (int s = 1; s < SPLIT; s++) T_p[s] = 1.f;
-            const float interval = (depth_max - depth_min) * ONE_OVER_SPLIT;
-            const float depth_hi = depth_min + interval * SPLIT;  // the last sample depth, as the loop forms it
-            // last list position any pixel of this warp still needs
-            const uint32_t warp_last = __reduce_max_sync(FULL, in_range ? last_contributor : 0u);
-            for (int i = 0; i < rounds2; i++) {
-                __syncthreads();
-                const uint32_t progress = i * BATCH + tid;
-                if (progress < max_contributor) {
-                    const uint32_t id = __ldg(point_list + range.x + progress);
-                    const float4* src = reinterpret_cast<const float4*>(records + id);
-                    float4* dst = s_rec + tid * REC_QUADS;
-                    dst[0] = __ldg(src);
-                    dst[1] = __ldg(src + 1);
-                    dst[2] = __ldg(src + 2);
-                }
-                __syncthreads();
-                for (int w = 0; w < BATCH / 32; w++) {
-                    const uint32_t base = i * BATCH + w * 32;
-                    if (base >= warp_last) break;
-                    const uint32_t gw = i * (BATCH / 32) + w;
-                    uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
-                    uint32_t keep = 0;  // positions some pixel of the warp can still need in later iterations
-                    while (bits) {
-                        const int jj = __ffs(bits) - 1;
-                        const uint32_t bit = bits & (0u - bits);
-                        bits ^= bit;
-                        const uint32_t pos = base + jj + 1;  // 1-based list position == `contributor`
-                        if (pos > warp_last) break;
-                        const float4* rec = s_rec + (w * 32 + jj) * REC_QUADS;
+            const int lim = min((uint32_t)BATCH, n - i * BATCH);
+            for (int w = 0; w * 32 < lim; w++) {
+                if (__all_sync(FULL, done)) break;
+                // lane-parallel candidate test: one entry per lane against the warp's pixel rectangle
+                const int jl = w * 32 + lane;
+                bool c = false;
+                if (jl < lim) c = may_touch(buf[jl * REC_QUADS], buf[jl * REC_QUADS + 1], rx0, ry0);
+                uint32_t cand = __ballot_sync(FULL, c);
+                uint32_t bits = 0;
+                while (cand) {
+                    const int jj = __ffs(cand) - 1;
+                    cand &= cand - 1;
+                    bool blended = false;
+                    if (!done) {
+                        const float4* rec = buf + (w * 32 + jj) * REC_QUADS;
                         const float4 q0 = rec[0];
                         const float4 q1 = rec[1];
                         const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                         const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                        const float alpha = fminf(0.99f, q1.y * expf(power));
-                        const bool act = in_range && pos <= last_contributor && !(power > 0.0f) &&
-                                         !(alpha < 1.0f / 255.0f);
-                        if (!__any_sync(FULL, act)) continue;
-                        const float4 q2 = rec[2];
-                        const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
-                        const float rsigma = q2.y;
-                        const bool ball = rsigma > 0;
-                        // Exact shortcut.  Every sample depth lies in [depth_min, depth_hi] (rounding is monotone),
-                        // so if that whole interval is more than 16 sigma in front of / behind the splat's peak
-                        // depth then |delta| > 16 at every sample and exp(-delta^2/2) is exactly 0.
-                        const float front = depth_min - t_peak;
-                        const float back = t_peak - depth_hi;
-                        const bool far = ball && fmaxf(front, back) * rsigma > FAR_SIGMAS;
-                        const bool far_front = far && front > 0.f;
-                        // may be dropped for good only with some slack: the recomputed depth_hi of a later
-                        // iteration can sit a few ulps above this one
-                        const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
-                        if (__any_sync(FULL, act && !behind_for_good)) keep |= bit;
-                        if (__any_sync(FULL, act && !far)) {
-                            if (act) {
-                                if (first) {
-#pragma unroll
-                                    for (int s = 0; s < SPLIT + 1; s++)
-                                        T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
+                        if (power <= 0.0f) {
+                            const float alpha = fminf(0.99f, q1.y * expf(power));
+                            if (alpha >= 1.0f / 255.0f) {
+                                const float test_T = T * (1.f - alpha);
+                                if (test_T < 0.0001f) {
+                                    done = true;
                                 } else {
-#pragma unroll
-                                    for (int s = 1; s < SPLIT; s++)
-                                        T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
-                                }
-                            }
-                        } else if (act) {
-                            // exp underflows to 0 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
-                            const float f = (far_front ? (1.f - alpha) : 1.0f) * c1;
-                            if (far_front || c1 != 1.0f) {
-                                if (first) {
-#pragma unroll
-                                    for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
-                                } else {
-#pragma unroll
-                                    for (int s = 1; s < SPLIT; s++) T_p[s] *= f;
+                                    const float aT = alpha * T;
+                                    const float4 q2 = rec[2];
+                                    const float4 q3 = rec[3];
+                                    C[0] += q2.z * aT;
+                                    C[1] += q2.w * aT;
+                                    C[2] += q3.x * aT;
+                                    if constexpr (GEOMETRY) {
+                                        const float t = q1.z * d.x + q1.w * d.y + q2.x;
+                                        Normal[0] += q3.y * aT;
+                                        Normal[1] += q3.z * aT;
+                                        Normal[2] += q3.w * aT;
+                                        mDepthinit = T > 0.5f ? t : mDepthinit;
+                                    }
+                                    T = test_T;
+                                    last_contributor = i * BATCH + w * 32 + jj + 1;  // 1-based list position
+                                    blended = true;
                                 }
                             }
                         }
                     }
-                    // positions that were behind every pixel's bracket stay behind it (brackets only shrink):
-                    // drop them from the warp's list.  Unvisited positions (beyond warp_last) are never needed.
-                    if (c1 == 1.0f && lane == 0 && gw < MASK_WORDS && gw < mask_words) s_mask[warp][gw] = keep;
+                    if (__any_sync(FULL, blended)) bits |= 1u << jj;
                 }
+                const uint32_t gw = i * (BATCH / 32) + w;
+                if (lane == 0) {
+                    if (GEOMETRY && gw < MASK_WORDS) s_mask[warp][gw] = bits;
+                    accept_mask[(size_t)(mask_base + gw) * 8 + warp] = bits;  // kept for the backward
+                }
+                mask_words = gw + 1;
             }
-            if (first) in_range = (T_p[0] >= 0.5f) && (T_p[SPLIT] <= 0.5f) && in_range;
-            int start_id = 0;
-#pragma unroll
-            for (int p = 1; p < SPLIT; p++) start_id = T_p[p] >= 0.5f ? p : start_id;
-            depth_max = depth_min + (start_id + 1) * interval;
-            depth_min = depth_min + (start_id + 0) * interval;
-            float lo = T_p[0], hi = T_p[1];
-#pragma unroll
-            for (int p = 1; p < SPLIT; p++) {
-                lo = (start_id == p) ? T_p[p] : lo;
-                hi = (start_id == p) ? T_p[p + 1] : hi;
-            }
-            T_p[0] = lo;
-            T_p[SPLIT] = hi;
         }
-        const float w_max = __saturatef((T_p[0] - 0.5f) / (T_p[0] - T_p[SPLIT]));
-        const float w_min = 1.f - w_max;
-        mDepth = in_range ? w_max * depth_max + w_min * depth_min : 0.f;
+        cp_async_wait_all();
+
+        // colour, alpha and normal are final here (render_forward.cu:648-670)
+        if (inside) {
+            n_contrib[pix_id] = last_contributor;
+            const size_t HW = (size_t)H * W;
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = C[ch] + T * __ldg(rp.bg + ch);
+            out_alpha[pix_id] = 1.f - T;
+            if constexpr (GEOMETRY) {
+                const float len_normal = 1.f - T;
+#pragma unroll
+                for (int ch = 0; ch < 3; ch++)
+                    out_normal[ch * HW + pix_id] = last_contributor ? Normal[ch] / len_normal : 0.f;
+            }
+        }
     }
 
-    if (inside) {
-        n_contrib[pix_id] = last_contributor;
-        const size_t HW = (size_t)H * W;
+    // block-wide max of last_contributor
+    uint32_t max_contributor;
+    {
+        const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+        if (lane == 0) s_red[warp] = wmax;
+        __syncthreads();
+        uint32_t m = 0;
 #pragma unroll
-        for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = C[ch] + T * __ldg(rp.bg + ch);
-        out_alpha[pix_id] = 1.f - T;
-        if constexpr (GEOMETRY) {
-            out_mdepth[pix_id] = mDepth * rln;
-            const float len_normal = 1.f - T;
-#pragma unroll
-            for (int ch = 0; ch < 3; ch++)
-                out_normal[ch * HW + pix_id] = last_contributor ? Normal[ch] / len_normal : 0.f;
-        }
+        for (int w = 0; w < WARPS; w++) m = max(m, s_red[w]);
+        max_contributor = m;
     }
     if (tid == 0) max_contributors[tile_id] = max_contributor;
-    if (lane == 0) warp_words[tile_id * (TILE_PIXELS / 32) + warp] = mask_words;
+    if (lane == 0) warp_words[tile_id * WARPS + warp] = mask_words;
+    if constexpr (!GEOMETRY) return;
+
+    // ---- passes 2-6: median depth by 8-way bisection ---------------------------------------------------
+    const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
+                          (pixf.y - static_cast<float>(H - 1) / 2.f) / rp.focal_y};
+    const float rln = rnorm3df(pixnf.x, pixnf.y, 1.f);
+    float T_p[SPLIT + 1];
+    float depth_min = fmaxf(mDepthinit - SAMPLE_RANGE, 0.f);
+    float depth_max = fmaxf(mDepthinit + SAMPLE_RANGE, 0.f);
+    bool in_range = T <= MIN_TRANSMITTANCE;
+    // rsqrt.approx(1.0): the vacancy factor of a splat whose Gaussian term underflowed.  The carry-over of
+    // constant prefixes and the thinning rely on it being exactly 1 (it is on sm_100; checked at run time).
+    float c1;
+    {
+        const float one = 1.0f;
+        asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(c1) : "f"(one));
+    }
+    const bool exact_one = (c1 == 1.0f);
+    // Per pixel: every list position <= pre_pos multiplies each sample by the same constants in every remaining
+    // iteration; their product, formed in list order, is pre_T.
+    float pre_T = 1.f;
+    uint32_t pre_pos = in_range ? 0u : NEVER;
+
+#pragma unroll 1
+    for (int it = 0; it < SPLIT_ITERATIONS; it++) {
+        const bool first = (it == 0);
+        constexpr float ONE_OVER_SPLIT = 1.f / static_cast<float>(SPLIT);
+        if (first) {
+            T_p[0] = 1.f;
+            T_p[SPLIT] = 1.f;
+        }
+#pragma unroll
+        for (int s = 1; s < SPLIT; s++) T_p[s] = pre_T;
+        const float interval = (depth_max - depth_min) * ONE_OVER_SPLIT;
+        const float depth_hi = depth_min + interval * SPLIT;  // the last sample depth, as the loop forms it
+        // list positions (1-based) any pixel of this warp still needs: (warp_first, warp_last]
+        const uint32_t warp_last = __reduce_max_sync(FULL, in_range ? last_contributor : 0u);
+        const uint32_t warp_first = __reduce_min_sync(FULL, pre_pos);
+        if (lane == 0) {
+            s_first[warp] = warp_last ? min(warp_first, warp_last) : NEVER;
+            s_last[warp] = warp_last;
+        }
+        __syncthreads();  // also: every warp is done with the staging buffers of the previous iteration
+        uint32_t block_first = NEVER, block_last = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) {
+            block_first = min(block_first, s_first[w]);
+            block_last = max(block_last, s_last[w]);
+        }
+        const int b0 = block_last ? block_first / BATCH : 0;
+        const int b1 = (block_last + BATCH - 1) / BATCH;
+        bool pfx = exact_one;  // still extending this pixel's constant prefix
+
+        uint32_t id_next = 0;
+        if (b0 < b1) {
+            const uint32_t e = b0 * BATCH + tid;
+            if (e < block_last) stage_record(s_rec, tid, records, __ldg(list + e), 3);
+            cp_async_commit();
+            if (e + BATCH < block_last) id_next = __ldg(list + e + BATCH);
+        }
+        for (int i = b0; i < b1; i++) {
+            cp_async_wait_all();
+            __syncthreads();
+            const int k = i - b0;
+            const float4* const buf = s_rec + (k & 1) * (BATCH * REC_QUADS);
+            if (i + 1 < b1) {
+                const uint32_t e = (i + 1) * BATCH + tid;
+                if (e < block_last) stage_record(s_rec + ((k + 1) & 1) * (BATCH * REC_QUADS), tid, records, id_next, 3);
+                cp_async_commit();
+                if (e + BATCH < block_last) id_next = __ldg(list + e + BATCH);
+            }
+            for (int w = 0; w < BATCH / 32; w++) {
+                const uint32_t base = i * BATCH + w * 32;
+                if (base >= warp_last) break;
+                if (base + 32 <= warp_first) continue;
+                const uint32_t gw = i * (BATCH / 32) + w;
+                uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
+                uint32_t keep = 0;  // positions some pixel of the warp can still need in later iterations
+                while (bits) {
+                    const int jj = __ffs(bits) - 1;
+                    const uint32_t bit = bits & (0u - bits);
+                    bits ^= bit;
+                    const uint32_t pos = base + jj + 1;  // 1-based list position == `contributor`
+                    if (pos > warp_last) break;
+                    if (pos <= warp_first) continue;
+                    const float4* rec = buf + (w * 32 + jj) * REC_QUADS;
+                    const float4 q0 = rec[0];
+                    const float4 q1 = rec[1];
+                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                    const float alpha = fminf(0.99f, q1.y * expf(power));
+                    const bool open = pos > pre_pos;  // not yet folded into this pixel's prefix (false if !in_range)
+                    const bool act = open && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (!__any_sync(FULL, act)) {
+                        if (pfx && open) pre_pos = pos;  // contributes to none of this pixel's samples, ever
+                        continue;
+                    }
+                    const float4 q2 = rec[2];
+                    const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
+                    const float rsigma = q2.y;
+                    const bool ball = rsigma > 0;
+                    // Exact shortcut.  Every sample depth lies in [depth_min, depth_hi] (rounding is monotone),
+                    // so if that whole interval is more than 16 sigma in front of / behind the splat's peak
+                    // depth then |delta| > 16 at every sample and exp(-delta^2/2) is exactly 0.  (Splats thinner
+                    // than a few ulps of the depth itself are never treated as far: the backward re-derives the
+                    // median depth through a multiply that may move it by an ulp.)
+                    const float front = depth_min - t_peak;
+                    const float back = t_peak - depth_hi;
+                    const bool far = ball && fmaxf(front, back) * rsigma > FAR_SIGMAS && rsigma * depth_hi < 4e6f;
+                    const bool far_front = far && front > 0.f;  // stays so: depth_min never decreases
+                    // may be dropped for good only with some slack: the recomputed depth_hi of a later
+                    // iteration can sit a few ulps above this one
+                    const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
+                    // constant factor in every remaining iteration: (1 - alpha) in front, 1 behind, none if inactive
+                    const bool constant = !act || far_front || behind_for_good;
+                    const bool fold = pfx && open && constant;
+                    if (__any_sync(FULL, act && !behind_for_good && !fold)) keep |= bit;
+                    if (__any_sync(FULL, act && !far)) {
+                        if (act) {
+                            if (first) {
+#pragma unroll
+                                for (int s = 0; s < SPLIT + 1; s++)
+                                    T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
+                            } else {
+#pragma unroll
+                                for (int s = 1; s < SPLIT; s++)
+                                    T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
+                            }
+                        }
+                    } else if (act) {
+                        // exp underflows to 0 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
+                        const float f = (far_front ? (1.f - alpha) : 1.0f) * c1;
+                        if (far_front || !exact_one) {
+                            if (first) {
+#pragma unroll
+                                for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
+                            } else {
+#pragma unroll
+                                for (int s = 1; s < SPLIT; s++) T_p[s] *= f;
+                            }
+                        }
+                    }
+                    if (fold) {
+                        pre_pos = pos;
+                        pre_T = T_p[1];  // all samples of this iteration are still equal here
+                    } else if (open) {
+                        pfx = false;
+                    }
+                }
+                // positions that were behind every pixel's bracket stay behind it (brackets only shrink):
+                // drop them from the warp's list.  Unvisited positions (beyond warp_last) are never needed.
+                if (exact_one && lane == 0 && gw < MASK_WORDS && gw < mask_words) {
+                    // bits below warp_first in this word were skipped, not examined: they are folded everywhere
+                    s_mask[warp][gw] = keep;
+                }
+            }
+        }
+        if (first) {
+            in_range = (T_p[0] >= 0.5f) && (T_p[SPLIT] <= 0.5f) && in_range;
+            if (!in_range) pre_pos = NEVER;
+        }
+        int start_id = 0;
+#pragma unroll
+        for (int p = 1; p < SPLIT; p++) start_id = T_p[p] >= 0.5f ? p : start_id;
+        depth_max = depth_min + (start_id + 1) * interval;
+        depth_min = depth_min + (start_id + 0) * interval;
+        float lo = T_p[0], hi = T_p[1];
+#pragma unroll
+        for (int p = 1; p < SPLIT; p++) {
+            lo = (start_id == p) ? T_p[p] : lo;
+            hi = (start_id == p) ? T_p[p + 1] : hi;
+        }
+        T_p[0] = lo;
+        T_p[SPLIT] = hi;
+    }
+    const float w_max = __saturatef((T_p[0] - 0.5f) / (T_p[0] - T_p[SPLIT]));
+    const float w_min = 1.f - w_max;
+    const float mDepth = in_range ? w_max * depth_max + w_min * depth_min : 0.f;
+    if (inside) out_mdepth[pix_id] = mDepth * rln;
+
+    // what the backward's dT/dt pass has to visit: (near_first, ...] restricted to the thinned mask
+    const uint32_t nf = __reduce_min_sync(FULL, in_range ? pre_pos : NEVER);
+    if (lane == 0) near_first[tile_id * WARPS + warp] = nf;
+    __syncwarp();
+    for (uint32_t gw = lane; gw < min(mask_words, (uint32_t)MASK_WORDS); gw += 32)
+        near_mask[(size_t)(mask_base + gw) * 8 + warp] = s_mask[warp][gw];
 }
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
@@ -328,14 +433,21 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     rp.bg = fp.view.bg;
     const dim3 grid(fp.gx, fp.gy, 1);
     const dim3 block(TILE_PIXELS, 1, 1);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(render_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(REC_BYTES + MASK_BYTES));
+        cudaFuncSetAttribute(render_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)REC_BYTES);
+        configured = true;
+    }
     if (require_depth)
-        render_forward_kernel<true><<<grid, block, 0, stream>>>(rp, ranges, point_list, records, out.color, out.alpha,
-                                                               out.normal, out.mdepth, out.n_contrib,
-                                                               out.max_contributor, out.accept_mask, out.warp_words);
+        render_forward_kernel<true><<<grid, block, REC_BYTES + MASK_BYTES, stream>>>(
+            rp, ranges, point_list, records, out.color, out.alpha, out.normal, out.mdepth, out.n_contrib,
+            out.max_contributor, out.accept_mask, out.warp_words, out.near_mask, out.near_first);
     else
-        render_forward_kernel<false><<<grid, block, 0, stream>>>(rp, ranges, point_list, records, out.color,
-                                                                out.alpha, out.normal, out.mdepth, out.n_contrib,
-                                                                out.max_contributor, out.accept_mask, out.warp_words);
+        render_forward_kernel<false><<<grid, block, REC_BYTES, stream>>>(
+            rp, ranges, point_list, records, out.color, out.alpha, out.normal, out.mdepth, out.n_contrib,
+            out.max_contributor, out.accept_mask, out.warp_words, out.near_mask, out.near_first);
 }
 
 }  // namespace ggs
