@@ -289,8 +289,8 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     const ImgLayout IL = img_layout(npix);
     (void)IL;
 
-    const size_t acc_bytes = (size_t)fp.P * GRAD_STRIDE * 4;
-    float* acc = static_cast<float*>(alloc(GGS_SLOT_BACKWARD, acc_bytes, user));
+    const size_t acc_bytes = (size_t)fp.P * GRAD_STRIDE * sizeof(double);
+    double* acc = static_cast<double*>(alloc(GGS_SLOT_BACKWARD, acc_bytes, user));
     if (!acc) return fail(GGS_ERR_ALLOC, "backward workspace allocation failed");
     prof_mark(stream, EV_B0);
     GGS_CUDA(cudaMemsetAsync(acc, 0, acc_bytes, stream));
@@ -330,6 +330,41 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     GGS_STAGE("gaussian_backward", debug, stream);
     prof_mark(stream, EV_GBWD);
     g_prof.have_bwd = g_prof.on;
+    return GGS_OK;
+}
+
+int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                                   const int32_t* radii, const double* accumulators, const GgsGradients* grads,
+                                   void* stream_) {
+    static_assert(GGS_ACCUMULATOR_STRIDE == GRAD_STRIDE && GGS_ACCUMULATOR_LIVE == GRAD_LIVE, "header out of sync");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (fp.P == 0) return GGS_OK;
+    if (!state || !state->geometry || !radii || !accumulators || !grads)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null state/radii/accumulators/grads");
+    if (!grads->dL_dmeans3D || !grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity ||
+        !grads->dL_dscales || !grads->dL_drotations || (in.shs && !grads->dL_dsh))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
+    const GeomLayout GL = geom_layout(fp.P);
+    GaussianGrads gg;
+    gg.dL_dmeans3D = grads->dL_dmeans3D;
+    gg.dL_dmeans2D = grads->dL_dmeans2D;
+    gg.dL_dcolors = grads->dL_dcolors;
+    gg.dL_dopacity = grads->dL_dopacity;
+    gg.dL_dscales = grads->dL_dscales;
+    gg.dL_drotations = grads->dL_drotations;
+    gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
+    const bool sg = in.shs && fp.SGM;
+    if (sg && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");
+    gg.dL_dsg_axis = sg ? grads->dL_dsg_axis : nullptr;
+    gg.dL_dsg_sharpness = sg ? grads->dL_dsg_sharpness : nullptr;
+    gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
+    launch_gaussian_backward(fp, in, radii, at<uint8_t>(state->geometry, GL.clamped), accumulators, gg, stream);
+    GGS_STAGE("gaussian_backward", frame->debug != 0, stream);
     return GGS_OK;
 }
 

@@ -30,13 +30,17 @@ struct __align__(16) SplatRecord {
 static_assert(sizeof(SplatRecord) == 64, "record must be 64 bytes");
 
 // Per-Gaussian gradient accumulator written by the tile backward with warp-aggregated
-// reductions: 17 live floats, padded to 20 (80 bytes, 16-byte aligned).
+// reductions: 17 live values, padded to 18, held in DOUBLE precision (144 bytes, 16-byte aligned).
+// The per-warp partial sums are float (as in the reference); only the cross-warp / cross-tile accumulation
+// through global atomics is done in double.  Several warps add partial sums of opposite sign into the same
+// row in a timing-dependent order; in float that order noise reaches 1e-4 of a gradient on splats whose
+// contributions cancel (measured: tools/grad_outlier.py), in double it is below 1e-12.
 //   [0..2]  dL/dmean2D (x, y, |x|+|y|)
 //   [3..6]  dL/dconic (x, y, z), dL/d(opacity*coef)
 //   [7..9]  dL/dcolor
 //   [10..12] dL/dnormal
 //   [13..16] dL/dray_plane (x, y, tc, rsigma)
-constexpr int GRAD_STRIDE = 20;
+constexpr int GRAD_STRIDE = 18;
 constexpr int GRAD_LIVE = 17;
 
 // Camera tensors stay in device memory (as in the reference, which takes raw device pointers);

@@ -3,6 +3,13 @@
 // by preprocessCUDA (:661-713, colour backward :56-191).  It consumes the 17-float accumulator row
 // written by the tile backward and writes EVERY output gradient row exactly once (zeros for culled
 // Gaussians), so the host never zero-fills the [P,SHM,3] gradient tensor separately.
+//
+// Memory access: the SH coefficients and their gradients are [P][SHM*3] rows of 192 bytes (SH3).  One thread
+// per Gaussian reading / writing its own row would touch 32 different 128-byte lines per warp instruction, so
+// each warp moves the contiguous slab of its 32 Gaussians through shared memory instead: coalesced 16-byte
+// loads into rows with an odd stride (conflict-free per-thread access), the per-Gaussian arithmetic on the
+// thread's own row, the gradient written back into the same row, and a coalesced store of the whole slab
+// (zeros for culled Gaussians; their coefficients are never read).
 #include "ggs_kernels.cuh"
 #include "ggs_math.cuh"
 
@@ -28,39 +35,94 @@ __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
     return r;
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int GB_THREADS = 128;
+
+__global__ void __launch_bounds__(GB_THREADS)
     gaussian_backward_kernel(const FrameParams fp, const GaussianInputs in, const int* __restrict__ radii,
-                             const uint8_t* __restrict__ clamped, const float* __restrict__ grad_acc,
+                             const uint8_t* __restrict__ clamped, const double* __restrict__ grad_acc,
                              const GaussianGrads g) {
+    extern __shared__ float s_slab[];  // [warps][32][RS]
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (size_t)fp.P) return;
     const int SHM = fp.SHM, SGM = fp.SGM;
     const bool has_sh = in.shs != nullptr;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vis = idx < (size_t)fp.P && radii[idx] > 0;
 
-    if (!(radii[idx] > 0)) {
-        st3(g.dL_dmeans3D, idx, 0.f, 0.f, 0.f);
-        st3(g.dL_dmeans2D, idx, 0.f, 0.f, 0.f);
-        st3(g.dL_dcolors, idx, 0.f, 0.f, 0.f);
-        g.dL_dopacity[idx] = 0.f;
-        st3(g.dL_dscales, idx, 0.f, 0.f, 0.f);
-        reinterpret_cast<float4*>(g.dL_drotations)[idx] = {0.f, 0.f, 0.f, 0.f};
-        if (g.dL_dsh) {
-            float* o = g.dL_dsh + idx * (size_t)SHM * 3;
-            for (int k = 0; k < SHM * 3; k++) o[k] = 0.f;
-        }
-        if (g.dL_dsg_axis) {
-            for (int k = 0; k < SGM; k++) {
-                st3(g.dL_dsg_axis, idx * (size_t)SGM + k, 0.f, 0.f, 0.f);
-                st3(g.dL_dsg_color, idx * (size_t)SGM + k, 0.f, 0.f, 0.f);
-                g.dL_dsg_sharpness[idx * (size_t)SGM + k] = 0.f;
+    // ---- SH slab of this warp's 32 Gaussians -> shared memory ---------------------------------------
+    const int F = SHM * 3;   // floats per Gaussian
+    const int RS = F | 1;    // odd row stride: conflict-free when every lane walks its own row
+    float* const swarp = s_slab + (size_t)warp * 32 * RS;
+    float* const srow = swarp + lane * RS;
+    const size_t g0 = (size_t)blockIdx.x * blockDim.x + warp * 32;  // first Gaussian of the warp
+    const int ng = g0 < (size_t)fp.P ? (int)min((size_t)32, (size_t)fp.P - g0) : 0;
+    const uint32_t vm = __ballot_sync(0xffffffffu, vis);
+    const bool vec4 = (F & 3) == 0;
+    if (has_sh && vm) {
+        if (vec4) {
+            const int Q = F >> 2;
+            const float4* src = reinterpret_cast<const float4*>(in.shs + g0 * F);
+            int gi = 0, rem = lane;
+            for (int e = lane; e < ng * Q; e += 32, rem += 32) {
+                while (rem >= Q) {
+                    rem -= Q;
+                    gi++;
+                }
+                if ((vm >> gi) & 1u) {
+                    const float4 v = __ldg(src + e);
+                    float* d = swarp + gi * RS + rem * 4;
+                    d[0] = v.x;
+                    d[1] = v.y;
+                    d[2] = v.z;
+                    d[3] = v.w;
+                }
+            }
+        } else {
+            const float* src = in.shs + g0 * F;
+            int gi = 0, rem = lane;
+            for (int e = lane; e < ng * F; e += 32, rem += 32) {
+                while (rem >= F) {
+                    rem -= F;
+                    gi++;
+                }
+                if ((vm >> gi) & 1u) swarp[gi * RS + rem] = __ldg(src + e);
             }
         }
-        return;
     }
+    __syncwarp();
 
+    if (!vis) {
+        if (idx < (size_t)fp.P) {
+            st3(g.dL_dmeans3D, idx, 0.f, 0.f, 0.f);
+            st3(g.dL_dmeans2D, idx, 0.f, 0.f, 0.f);
+            st3(g.dL_dcolors, idx, 0.f, 0.f, 0.f);
+            g.dL_dopacity[idx] = 0.f;
+            st3(g.dL_dscales, idx, 0.f, 0.f, 0.f);
+            reinterpret_cast<float4*>(g.dL_drotations)[idx] = {0.f, 0.f, 0.f, 0.f};
+            if (g.dL_dsh)
+                for (int k = 0; k < F; k++) srow[k] = 0.f;
+            if (g.dL_dsg_axis) {
+                for (int k = 0; k < SGM; k++) {
+                    st3(g.dL_dsg_axis, idx * (size_t)SGM + k, 0.f, 0.f, 0.f);
+                    st3(g.dL_dsg_color, idx * (size_t)SGM + k, 0.f, 0.f, 0.f);
+                    g.dL_dsg_sharpness[idx * (size_t)SGM + k] = 0.f;
+                }
+            }
+        }
+    } else {
     // ---- gather the accumulator row -----------------------------------------------------------
-    const float4* row = reinterpret_cast<const float4*>(grad_acc + idx * GRAD_STRIDE);
-    const float4 r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2), r3 = __ldg(row + 3), r4 = __ldg(row + 4);
+    // 17 doubles (see ggs_common.cuh), rounded to float once
+    float4 r0, r1, r2, r3, r4;
+    {
+        const double2* row = reinterpret_cast<const double2*>(grad_acc + idx * GRAD_STRIDE);
+        double2 d[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) d[k] = __ldg(row + k);
+        r0 = {(float)d[0].x, (float)d[0].y, (float)d[1].x, (float)d[1].y};
+        r1 = {(float)d[2].x, (float)d[2].y, (float)d[3].x, (float)d[3].y};
+        r2 = {(float)d[4].x, (float)d[4].y, (float)d[5].x, (float)d[5].y};
+        r3 = {(float)d[6].x, (float)d[6].y, (float)d[7].x, (float)d[7].y};
+        r4 = {(float)d[8].x, 0.f, 0.f, 0.f};
+    }
     const float3 dL_dmean2D = {r0.x, r0.y, r0.z};
     const float4 dL_dconic = {r0.w, r1.x, r1.y, r1.z};
     const float3 dL_dcolor = {r1.w, r2.x, r2.y};
@@ -320,8 +382,8 @@ __global__ void __launch_bounds__(256)
         const float3 dir_orig = {mean.x - fp.view.campos[0], mean.y - fp.view.campos[1], mean.z - fp.view.campos[2]};
         const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
         const float3 dir = {dir_orig.x / len, dir_orig.y / len, dir_orig.z / len};
-        const float* sh = in.shs + idx * (size_t)SHM * 3;
-        auto Csh = [&](int k) -> float3 { return ld3g(sh, k); };
+        // the thread's SH row lives in shared memory: every coefficient is read before the gradients overwrite it
+        auto Csh = [&](int k) -> float3 { return float3{srow[3 * k], srow[3 * k + 1], srow[3 * k + 2]}; };
         const uint8_t mask = clamped[idx];
         float3 dL_dRGB = dL_dcolor;
         dL_dRGB.x *= (mask & 1) ? 0 : 1;
@@ -330,33 +392,20 @@ __global__ void __launch_bounds__(256)
 
         float3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
         const float x = dir.x, y = dir.y, z = dir.z;
-        float* dsh = g.dL_dsh + idx * (size_t)SHM * 3;
-        auto put = [&](int k, float w) { st3(dsh, k, w * dL_dRGB.x, w * dL_dRGB.y, w * dL_dRGB.z); };
+        const float xx = x * x, yy = y * y, zz = z * z;
+        const float xy = x * y, yz = y * z, xz = x * z;
         auto axpy = [](float3& acc, float w, const float3& c) {
             acc.x += w * c.x;
             acc.y += w * c.y;
             acc.z += w * c.z;
         };
-        put(0, kSH_C0);
-        int written = 1;
+        // ---- d colour / d direction: same term order as render_backward.cu:83-166 ----
         if (fp.SHD > 0) {
-            put(1, -kSH_C1 * y);
-            put(2, kSH_C1 * z);
-            put(3, -kSH_C1 * x);
-            written = 4;
             const float3 s1 = Csh(1), s2 = Csh(2), s3 = Csh(3);
             axpy(dRGBdx, -kSH_C1, s3);
             axpy(dRGBdy, -kSH_C1, s1);
             axpy(dRGBdz, kSH_C1, s2);
             if (fp.SHD > 1) {
-                const float xx = x * x, yy = y * y, zz = z * z;
-                const float xy = x * y, yz = y * z, xz = x * z;
-                put(4, kSH_C2[0] * xy);
-                put(5, kSH_C2[1] * yz);
-                put(6, kSH_C2[2] * (2.f * zz - xx - yy));
-                put(7, kSH_C2[3] * xz);
-                put(8, kSH_C2[4] * (xx - yy));
-                written = 9;
                 const float3 s4 = Csh(4), s5 = Csh(5), s6 = Csh(6), s7 = Csh(7), s8 = Csh(8);
                 axpy(dRGBdx, kSH_C2[0] * y, s4);
                 axpy(dRGBdx, kSH_C2[2] * 2.f * -x, s6);
@@ -370,14 +419,6 @@ __global__ void __launch_bounds__(256)
                 axpy(dRGBdz, kSH_C2[2] * 2.f * 2.f * z, s6);
                 axpy(dRGBdz, kSH_C2[3] * x, s7);
                 if (fp.SHD > 2) {
-                    put(9, kSH_C3[0] * y * (3.f * xx - yy));
-                    put(10, kSH_C3[1] * xy * z);
-                    put(11, kSH_C3[2] * y * (4.f * zz - xx - yy));
-                    put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                    put(13, kSH_C3[4] * x * (4.f * zz - xx - yy));
-                    put(14, kSH_C3[5] * z * (xx - yy));
-                    put(15, kSH_C3[6] * x * (xx - 3.f * yy));
-                    written = 16;
                     const float3 s9 = Csh(9), s10 = Csh(10), s11 = Csh(11), s12 = Csh(12), s13 = Csh(13),
                                  s14 = Csh(14), s15 = Csh(15);
                     axpy(dRGBdx, kSH_C3[0] * 3.f * 2.f * xy, s9);
@@ -402,7 +443,39 @@ __global__ void __launch_bounds__(256)
                 }
             }
         }
-        for (int k = written; k < SHM; k++) st3(dsh, k, 0.f, 0.f, 0.f);
+        // ---- d colour / d SH coefficient: overwrite the row with the gradient (render_backward.cu:76-160) ----
+        auto put = [&](int k, float w) {
+            srow[3 * k] = w * dL_dRGB.x;
+            srow[3 * k + 1] = w * dL_dRGB.y;
+            srow[3 * k + 2] = w * dL_dRGB.z;
+        };
+        put(0, kSH_C0);
+        int written = 1;
+        if (fp.SHD > 0) {
+            put(1, -kSH_C1 * y);
+            put(2, kSH_C1 * z);
+            put(3, -kSH_C1 * x);
+            written = 4;
+            if (fp.SHD > 1) {
+                put(4, kSH_C2[0] * xy);
+                put(5, kSH_C2[1] * yz);
+                put(6, kSH_C2[2] * (2.f * zz - xx - yy));
+                put(7, kSH_C2[3] * xz);
+                put(8, kSH_C2[4] * (xx - yy));
+                written = 9;
+                if (fp.SHD > 2) {
+                    put(9, kSH_C3[0] * y * (3.f * xx - yy));
+                    put(10, kSH_C3[1] * xy * z);
+                    put(11, kSH_C3[2] * y * (4.f * zz - xx - yy));
+                    put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                    put(13, kSH_C3[4] * x * (4.f * zz - xx - yy));
+                    put(14, kSH_C3[5] * z * (xx - yy));
+                    put(15, kSH_C3[6] * x * (xx - 3.f * yy));
+                    written = 16;
+                }
+            }
+        }
+        for (int k = written * 3; k < F; k++) srow[k] = 0.f;
 
         float3 dL_ddir = {dRGBdx.x * dL_dRGB.x + dRGBdx.y * dL_dRGB.y + dRGBdx.z * dL_dRGB.z,
                           dRGBdy.x * dL_dRGB.x + dRGBdy.y * dL_dRGB.y + dRGBdy.z * dL_dRGB.z,
@@ -442,13 +515,49 @@ __global__ void __launch_bounds__(256)
     g.dL_dopacity[idx] = dL_dopacity;
     st3(g.dL_dscales, idx, dL_dscale.x, dL_dscale.y, dL_dscale.z);
     reinterpret_cast<float4*>(g.dL_drotations)[idx] = dL_dq;
+    }  // vis
+
+    // ---- gradient slab of the warp's 32 Gaussians: shared memory -> global, coalesced ---------------
+    if (g.dL_dsh) {
+        __syncwarp();
+        if (vec4) {
+            const int Q = F >> 2;
+            float4* dst = reinterpret_cast<float4*>(g.dL_dsh + g0 * F);
+            int gi = 0, rem = lane;
+            for (int e = lane; e < ng * Q; e += 32, rem += 32) {
+                while (rem >= Q) {
+                    rem -= Q;
+                    gi++;
+                }
+                const float* sr = swarp + gi * RS + rem * 4;
+                dst[e] = float4{sr[0], sr[1], sr[2], sr[3]};
+            }
+        } else {
+            float* dst = g.dL_dsh + g0 * F;
+            int gi = 0, rem = lane;
+            for (int e = lane; e < ng * F; e += 32, rem += 32) {
+                while (rem >= F) {
+                    rem -= F;
+                    gi++;
+                }
+                dst[e] = swarp[gi * RS + rem];
+            }
+        }
+    }
 }
 
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
-                              const uint8_t* clamped, const float* grad_acc, const GaussianGrads& g,
+                              const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
                               cudaStream_t stream) {
     if (fp.P == 0) return;
-    gaussian_backward_kernel<<<(fp.P + 255) / 256, 256, 0, stream>>>(fp, in, radii, clamped, grad_acc, g);
+    const size_t smem = (size_t)(GB_THREADS / 32) * 32 * ((fp.SHM * 3) | 1) * sizeof(float);
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        cudaFuncSetAttribute(gaussian_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    gaussian_backward_kernel<<<(fp.P + GB_THREADS - 1) / GB_THREADS, GB_THREADS, smem, stream>>>(fp, in, radii, clamped,
+                                                                                               grad_acc, g);
 }
 
 }  // namespace ggs

@@ -83,7 +83,7 @@ struct RenderBwdIn {
     const float* dL_dnormal;
 };
 void launch_render_backward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
-                            const SplatRecord* records, const RenderBwdIn& in, float* grad_acc,
+                            const SplatRecord* records, const RenderBwdIn& in, double* grad_acc,
                             bool require_depth, cudaStream_t stream);
 
 struct GaussianGrads {
@@ -99,7 +99,7 @@ struct GaussianGrads {
     float* dL_dsg_color;      // [P,SGM,3] or null
 };
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
-                              const uint8_t* clamped, const float* grad_acc, const GaussianGrads& g,
+                              const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
                               cudaStream_t stream);
 
 // ---- point queries (integrate) ----------------------------------------------------------------

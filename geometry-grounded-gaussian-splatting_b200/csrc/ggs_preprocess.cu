@@ -1,6 +1,8 @@
 // Stage 1 of the forward: per-Gaussian projection, 2D covariance + Mip 2D filter, ray-plane /
-// normal, SH + spherical-Gaussian colour.  One thread per Gaussian, inputs read through the
-// read-only path, outputs written as one 64-byte SplatRecord plus SoA side arrays.
+// normal, SH + spherical-Gaussian colour.  One thread per Gaussian; outputs written as one 64-byte
+// SplatRecord plus SoA side arrays.  The SH coefficients ([P][SHM*3] rows, 192 bytes at SH3) are moved per
+// warp as one contiguous slab through shared memory with coalesced 16-byte loads (rows of culled Gaussians
+// are skipped), instead of 48 strided scalar loads per thread.
 //
 // Behaviour follows DGR/cuda_rasterizer/render_forward.cu:283-386 (preprocessCUDA) with helpers
 // :22-78 (colour), :81-243 (computeCov2D) and auxiliary.h:38-49,133-153.  The float pipelines that
@@ -15,15 +17,15 @@ __device__ __forceinline__ float3 ld3(const float* p, size_t i) {
 }
 
 // Colour from SH (degree <= 3) + spherical Gaussians (render_forward.cu:22-78).
-__device__ __forceinline__ float3 eval_color(size_t idx, const FrameParams& fp, const float3 pos, const float* shs,
+__device__ __forceinline__ float3 eval_color(size_t idx, const FrameParams& fp, const float3 pos, const float* sh,
                                              const float* sg_axis, const float* sg_sharpness, const float* sg_color,
                                              uint8_t& clamp_mask) {
     float3 dir = {pos.x - fp.view.campos[0], pos.y - fp.view.campos[1], pos.z - fp.view.campos[2]};
     float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
     dir = {dir.x / len, dir.y / len, dir.z / len};
 
-    const float* sh = shs + idx * (size_t)fp.SHM * 3;
-    auto C = [&](int k) -> float3 { return ld3(sh, k); };
+    // `sh` is this Gaussian's coefficient row (shared memory)
+    auto C = [&](int k) -> float3 { return float3{sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]}; };
     float3 s0 = C(0);
     float3 res = {kSH_C0 * s0.x, kSH_C0 * s0.y, kSH_C0 * s0.z};
     auto acc = [&](float w, const float3& c) {
@@ -70,23 +72,24 @@ __device__ __forceinline__ float3 eval_color(size_t idx, const FrameParams& fp, 
     return {fmaxf(res.x, 0.f), fmaxf(res.y, 0.f), fmaxf(res.z, 0.f)};
 }
 
-__global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, const GaussianInputs in,
-                                                         const bool want_color, SplatRecord* __restrict__ records,
-                                                         float* __restrict__ depths,
-                                                         uint32_t* __restrict__ tiles_touched,
-                                                         uint2* __restrict__ rects, uint8_t* __restrict__ clamped,
-                                                         int* __restrict__ radii) {
-    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (size_t)fp.P) return;
+struct Projected {
+    float3 p_orig;
+    float tc, my_radius, coef;
+    float2 point_image;
+    float3 conic, normal;
+    float4 ray_plane;
+    uint2 rect_min, rect_max;
+};
 
-    radii[idx] = 0;
-    tiles_touched[idx] = 0;
-
+// Geometry part of the preprocess; false when the Gaussian is culled (near plane, singular covariance, empty
+// tile rectangle), in the order the reference tests them.
+__device__ __forceinline__ bool project_gaussian(const size_t idx, const FrameParams& fp, const GaussianInputs& in,
+                                                 Projected& o) {
     const float* viewmatrix = fp.view.view;
     const float3 p_orig = ld3(in.means3D, idx);
     // near cull (auxiliary.h:133-153)
     const float3 p_view = xform_point_4x3(p_orig, viewmatrix);
-    if (p_view.z <= 0.2f) return;
+    if (p_view.z <= 0.2f) return false;
 
     const float4 p_hom = xform_point_4x4(p_orig, fp.view.proj);
     const float p_w = 1.0f / (p_hom.w + 0.0000001f);
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, c
     }
 
     // ---- conic, radius, tile rectangle (render_forward.cu:347-368) ----------------------------
-    if (det == 0.0f) return;
+    if (det == 0.0f) return false;
     const float det_inv = rcp_approx(det);
     const float3 conic = {MUL(cc, det_inv), MUL(det_inv, -cb), MUL(ca, det_inv)};
 
@@ -216,7 +219,83 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, c
     const float2 point_image = {ndc_to_pix(p_proj.x, fp.W), ndc_to_pix(p_proj.y, fp.H)};
     uint2 rect_min, rect_max;
     tile_rect(point_image, my_radius, rect_min, rect_max, fp.gx, fp.gy);
-    if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) return;
+    if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) return false;
+    o.p_orig = p_orig;
+    o.tc = tc;
+    o.my_radius = my_radius;
+    o.coef = coef;
+    o.point_image = point_image;
+    o.conic = conic;
+    o.normal = normal;
+    o.ray_plane = ray_plane;
+    o.rect_min = rect_min;
+    o.rect_max = rect_max;
+    return true;
+}
+
+constexpr int PRE_THREADS = 128;
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FrameParams fp, const GaussianInputs in,
+                                                                 const bool want_color, SplatRecord* __restrict__ records,
+                                                                 float* __restrict__ depths,
+                                                                 uint32_t* __restrict__ tiles_touched,
+                                                                 uint2* __restrict__ rects, uint8_t* __restrict__ clamped,
+                                                                 int* __restrict__ radii) {
+    extern __shared__ float s_slab[];  // [warps][32][RS] SH rows (only when colours come from SH)
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool in_range = idx < (size_t)fp.P;
+
+    Projected pr;
+    const bool vis = in_range && project_gaussian(idx, fp, in, pr);
+    if (in_range && !vis) {
+        radii[idx] = 0;
+        tiles_touched[idx] = 0;
+    }
+
+    // ---- SH slab of the warp's visible Gaussians -> shared memory -------------------------------------
+    const bool use_sh = want_color && in.colors_precomp == nullptr;
+    const int F = fp.SHM * 3;
+    const int RS = F | 1;  // odd row stride: conflict-free when every lane walks its own row
+    float* const swarp = s_slab + (size_t)warp * 32 * RS;
+    if (use_sh) {
+        const size_t g0 = (size_t)blockIdx.x * blockDim.x + warp * 32;
+        const int ng = g0 < (size_t)fp.P ? (int)min((size_t)32, (size_t)fp.P - g0) : 0;
+        const uint32_t vm = __ballot_sync(0xffffffffu, vis);
+        if (vm) {
+            if ((F & 3) == 0) {
+                const int Q = F >> 2;
+                const float4* src = reinterpret_cast<const float4*>(in.shs + g0 * F);
+                int gi = 0, rem = lane;
+                for (int e = lane; e < ng * Q; e += 32, rem += 32) {
+                    while (rem >= Q) {
+                        rem -= Q;
+                        gi++;
+                    }
+                    if ((vm >> gi) & 1u) {
+                        const float4 v = __ldg(src + e);
+                        float* d = swarp + gi * RS + rem * 4;
+                        d[0] = v.x;
+                        d[1] = v.y;
+                        d[2] = v.z;
+                        d[3] = v.w;
+                    }
+                }
+            } else {
+                const float* src = in.shs + g0 * F;
+                int gi = 0, rem = lane;
+                for (int e = lane; e < ng * F; e += 32, rem += 32) {
+                    while (rem >= F) {
+                        rem -= F;
+                        gi++;
+                    }
+                    if ((vm >> gi) & 1u) swarp[gi * RS + rem] = __ldg(src + e);
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (!vis) return;
 
     // ---- colour -------------------------------------------------------------------------------
     float3 rgb = {0.f, 0.f, 0.f};
@@ -225,36 +304,38 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const FrameParams fp, c
         if (in.colors_precomp != nullptr)
             rgb = ld3(in.colors_precomp, idx);
         else
-            rgb = eval_color(idx, fp, p_orig, in.shs, in.sg_axis, in.sg_sharpness, in.sg_color, mask);
+            rgb = eval_color(idx, fp, pr.p_orig, swarp + lane * RS, in.sg_axis, in.sg_sharpness, in.sg_color, mask);
     }
 
-    depths[idx] = tc;
-    radii[idx] = my_radius;
+    depths[idx] = pr.tc;
+    radii[idx] = pr.my_radius;
     clamped[idx] = mask;
-    rects[idx] = {rect_min.x | (rect_min.y << 16), rect_max.x | (rect_max.y << 16)};
-    tiles_touched[idx] = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+    rects[idx] = {pr.rect_min.x | (pr.rect_min.y << 16), pr.rect_max.x | (pr.rect_max.y << 16)};
+    tiles_touched[idx] = (pr.rect_max.y - pr.rect_min.y) * (pr.rect_max.x - pr.rect_min.x);
 
-    const float opac = MUL(coef, __ldg(in.opacities + idx));
-    SplatRecord rec;
-    rec.q0 = {point_image.x, point_image.y, conic.x, conic.y};
-    rec.q1 = {conic.z, opac, ray_plane.x, ray_plane.y};
-    rec.q2 = {ray_plane.z, ray_plane.w, rgb.x, rgb.y};
-    rec.q3 = {rgb.z, normal.x, normal.y, normal.z};
+    const float opac = MUL(pr.coef, __ldg(in.opacities + idx));
     float4* dst = reinterpret_cast<float4*>(records + idx);
-    dst[0] = rec.q0;
-    dst[1] = rec.q1;
-    dst[2] = rec.q2;
-    dst[3] = rec.q3;
+    dst[0] = {pr.point_image.x, pr.point_image.y, pr.conic.x, pr.conic.y};
+    dst[1] = {pr.conic.z, opac, pr.ray_plane.x, pr.ray_plane.y};
+    dst[2] = {pr.ray_plane.z, pr.ray_plane.w, rgb.x, rgb.y};
+    dst[3] = {rgb.z, pr.normal.x, pr.normal.y, pr.normal.z};
 }
 
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
                        cudaStream_t stream) {
     if (fp.P == 0) return;
-    const int threads = 256;
+    const int threads = PRE_THREADS;
     const int blocks = (fp.P + threads - 1) / threads;
-    preprocess_kernel<<<blocks, threads, 0, stream>>>(fp, in, want_color, records, depths, tiles_touched, rects,
-                                                      clamped, radii);
+    const bool use_sh = want_color && in.colors_precomp == nullptr;
+    const size_t smem = use_sh ? (size_t)(PRE_THREADS / 32) * 32 * ((fp.SHM * 3) | 1) * sizeof(float) : 0;
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    preprocess_kernel<<<blocks, threads, smem, stream>>>(fp, in, want_color, records, depths, tiles_touched, rects,
+                                                         clamped, radii);
 }
 
 // Frustum visibility only (reference checkFrustum, rasterizer_impl.cu:54-66).

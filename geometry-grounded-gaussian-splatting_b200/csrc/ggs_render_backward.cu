@@ -13,7 +13,7 @@
 // Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
 // scalar atomics from one lane (the reference), the warp runs ONE transposing butterfly (20
 // shuffles) that leaves component c on its own lane, and those 17 lanes issue a single predicated
-// RED into the entry's contiguous 80-byte accumulator row.
+// RED (double precision, see ggs_common.cuh) into the entry's contiguous 144-byte accumulator row.
 #include "ggs_kernels.cuh"
 #include "ggs_tile.cuh"
 
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                            const uint32_t* __restrict__ warp_words, const uint32_t* __restrict__ near_mask,
                            const uint32_t* __restrict__ near_first, const float* __restrict__ dL_dpixels,
                            const float* __restrict__ dL_dpixel_mdepths, const float* __restrict__ dL_dalphas,
-                           const float* __restrict__ dL_dpixel_normals, float* __restrict__ grad_acc) {
+                           const float* __restrict__ dL_dpixel_normals, double* __restrict__ grad_acc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* const s_rec = reinterpret_cast<float4*>(smem_raw);                     // [2][STAGE_QUADS]
     uint32_t* const s_id = reinterpret_cast<uint32_t*>(smem_raw + BWD_REC_BYTES);  // [2][BATCH_B]
@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                 const float sum = warp_reduce_scatter17(v, lane);
                 if (my_comp >= 0) {
                     if (GEOMETRY || my_comp < 10)
-                        atomicAdd(grad_acc + (size_t)ids[j] * GRAD_STRIDE + my_comp, sum);
+                        atomicAdd(grad_acc + (size_t)ids[j] * GRAD_STRIDE + my_comp, static_cast<double>(sum));
                 }
             }
         }
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
 }
 
 void launch_render_backward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
-                            const SplatRecord* records, const RenderBwdIn& in, float* grad_acc,
+                            const SplatRecord* records, const RenderBwdIn& in, double* grad_acc,
                             bool require_depth, cudaStream_t stream) {
     RenderBwdParams rp;
     rp.W = fp.W;

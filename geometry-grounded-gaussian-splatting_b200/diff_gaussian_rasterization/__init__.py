@@ -164,6 +164,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             arena = _abi.Arena(device)
             n = _lib.ggs_rasterize_forward(C.byref(frame), C.byref(g), arena.fn, None, C.byref(out), C.byref(state),
                                            _abi.stream_handle(device))
+            arena.done()
             if n < 0:
                 if arena.error is not None:
                     raise arena.error
@@ -224,6 +225,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             arena = _abi.Arena(device)
             rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn, None,
                                              C.byref(grads), _abi.stream_handle(device))
+            arena.done()
             if rc < 0:
                 if arena.error is not None:
                     raise arena.error
@@ -315,6 +317,7 @@ class GaussianRasterizer(nn.Module):
                 arena = _abi.Arena(device)
                 n = _lib.ggs_integrate_points(C.byref(frame), C.byref(g), _abi.ptr(pts), PN, arena.fn, None,
                                               _abi.ptr(transmittance), _abi.ptr(inside), _abi.stream_handle(device))
+                arena.done()
                 if n < 0:
                     if arena.error is not None:
                         raise arena.error

@@ -76,6 +76,7 @@ class GgsStageTimes(C.Structure):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
+           "ggs_backward_from_accumulators",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
 
@@ -95,6 +96,10 @@ def _load():
     lib.ggs_rasterize_backward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.POINTER(GgsForwardState),
                                            C.POINTER(GgsBackwardInputs), ALLOC_FN, C.c_void_p,
                                            C.POINTER(GgsGradients), C.c_void_p]
+    lib.ggs_backward_from_accumulators.restype = C.c_int
+    lib.ggs_backward_from_accumulators.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians),
+                                                   C.POINTER(GgsForwardState), C.c_void_p, C.c_void_p,
+                                                   C.POINTER(GgsGradients), C.c_void_p]
     lib.ggs_integrate_points.restype = C.c_int64
     lib.ggs_integrate_points.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                          ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -138,23 +143,35 @@ def ptr(t):
 
 class Arena:
     """Hands torch-owned device buffers to the library (the reference's resize lambdas,
-    rasterize_points.cu:27-37).  The tensors stay referenced here until the arena is dropped."""
+    rasterize_points.cu:27-37).  The tensors stay referenced in `buffers` until the arena is dropped.
+
+    The C callback closes over a plain dict, not over the arena, and `done()` drops it after the call: no
+    reference cycle, so the (hundreds of MB of) workspaces are released by reference counting as soon as the
+    autograd context dies instead of waiting for Python's cycle collector."""
 
     def __init__(self, device):
         self.device = device
-        self.buffers = {}
-        self.error = None
+        self.buffers = buffers = {}
+        self._err = err = []
 
         def _alloc(slot, nbytes, _user):
             try:
-                t = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
-                self.buffers[int(slot)] = t
+                t = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+                buffers[int(slot)] = t
                 return t.data_ptr()
             except Exception as ex:  # surfaces as GGS_ERR_ALLOC
-                self.error = ex
+                err.append(ex)
                 return 0
 
         self.fn = ALLOC_FN(_alloc)
+
+    @property
+    def error(self):
+        return self._err[0] if self._err else None
+
+    def done(self):
+        """Call after the library call returned: the callback is not needed any more."""
+        self.fn = None
 
 
 def stream_handle(device) -> C.c_void_p:

@@ -161,6 +161,17 @@ GGS_API int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* ga
                            const GgsBackwardInputs* in, GgsAllocFn alloc, void* user, const GgsGradients* grads,
                            void* stream);
 
+/* Second half of the backward on its own: the per-Gaussian chain rule (the reference's computeCov2DCUDA +
+ * preprocessCUDA backward, render_backward.cu:249-713) applied to a caller-provided accumulator array
+ * double[P][GGS_ACCUMULATOR_STRIDE] in the layout ggs_rasterize_backward leaves in its GGS_SLOT_BACKWARD scratch:
+ * dL/d(mean2D xy, |x|+|y|), conic xyz, opacity*coef, colour rgb, normal xyz, ray-plane xyzw.  The chain is linear in
+ * the accumulators, which lets tests measure its conditioning component by component. */
+#define GGS_ACCUMULATOR_STRIDE 18
+#define GGS_ACCUMULATOR_LIVE 17
+GGS_API int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* gaussians,
+                                   const GgsForwardState* state, const int32_t* radii, const double* accumulators,
+                                   const GgsGradients* grads, void* stream);
+
 /* Transmittance of query points seen from `frame` (integrate): out_transmittance [PN] and
  * inside [PN] (uint8 0/1) must be zero-initialised by the caller.  Returns num_rendered. */
 GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,

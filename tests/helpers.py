@@ -210,6 +210,116 @@ def grad_rel_err(a, b):
     return float((a - b).abs().max()) / den
 
 
+def ours_backward_raw(sc, device, require_depth=True):
+    """Forward + backward through the C ABI with the scene's fixed upstream gradients, keeping the backward scratch.
+    Returns (grads dict, accumulators double[P,18], ctx) where ctx can be passed to `chain_from_accumulators`."""
+    import ctypes as C
+
+    import diff_gaussian_rasterization as ours
+    from diff_gaussian_rasterization import _abi
+
+    dev = torch.device(device)
+    rs = settings_for(ours, sc, device, require_depth)
+    keep = []
+    P, Hh, W = sc.P, sc.cam.H, sc.cam.W
+    t = {k: getattr(sc, k).to(device).contiguous() for k in
+         ("means3D", "opacities", "scales", "rotations", "shs", "sg_axis", "sg_sharpness", "sg_color")}
+    frame = ours._frame(rs, dev, keep)
+    g = ours._gaussians(t["means3D"], t["opacities"], t["scales"], t["rotations"], t["shs"], t["sg_axis"],
+                        t["sg_sharpness"], t["sg_color"], None, sc.sg_degree)
+    color = torch.empty(3, Hh, W, device=device)
+    mdepth = torch.zeros(1, Hh, W, device=device)
+    alpha = torch.empty(1, Hh, W, device=device)
+    normal = torch.zeros(3, Hh, W, device=device)
+    radii = torch.empty(P, dtype=torch.int32, device=device)
+    out = _abi.GgsForwardOutputs(_abi.ptr(color), _abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth),
+                                 _abi.ptr(radii))
+    state = _abi.GgsForwardState()
+    arena = _abi.Arena(dev)
+    stream = _abi.stream_handle(dev)
+    n = _abi.lib.ggs_rasterize_forward(C.byref(frame), C.byref(g), arena.fn, None, C.byref(out), C.byref(state), stream)
+    _abi.check(n, "ggs_rasterize_forward")
+    up = {k: v.to(device).contiguous() for k, v in sc.grads.items()}
+    if not require_depth:
+        up["mdepth"] = torch.zeros_like(up["mdepth"])
+        up["normal"] = torch.zeros_like(up["normal"])
+    bi = _abi.GgsBackwardInputs(_abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth), _abi.ptr(radii),
+                                _abi.ptr(up["color"]), _abi.ptr(up["mdepth"]), _abi.ptr(up["alpha"]),
+                                _abi.ptr(up["normal"]))
+
+    def alloc_grads():
+        SHM, SGM = t["shs"].shape[1], t["sg_color"].shape[1]
+        d = dict(means3D=torch.empty(P, 3, device=device), means2D=torch.empty(P, 3, device=device),
+                 colors=torch.empty(P, 3, device=device), opacities=torch.empty(P, 1, device=device),
+                 scales=torch.empty(P, 3, device=device), rotations=torch.empty(P, 4, device=device),
+                 shs=torch.empty(P, SHM, 3, device=device), sg_axis=torch.empty(P, SGM, 3, device=device),
+                 sg_sharpness=torch.empty(P, SGM, device=device), sg_color=torch.empty(P, SGM, 3, device=device))
+        st = _abi.GgsGradients(*[_abi.ptr(d[k]) for k in ("means3D", "means2D", "colors", "opacities", "scales",
+                                                           "rotations", "shs", "sg_axis", "sg_sharpness", "sg_color")])
+        return d, st
+
+    grads, gst = alloc_grads()
+    barena = _abi.Arena(dev)
+    rc = _abi.lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), barena.fn, None,
+                                         C.byref(gst), stream)
+    _abi.check(rc, "ggs_rasterize_backward")
+    torch.cuda.synchronize(device)
+    acc = barena.buffers[_abi.SLOT_BACKWARD][:P * 18 * 8].view(torch.float64).view(P, 18).clone()
+    ctx = dict(frame=frame, g=g, state=state, radii=radii, alloc_grads=alloc_grads, stream=stream,
+               keep=(keep, t, arena, barena, color, mdepth, alpha, normal, up))
+    return grads, acc, ctx
+
+
+def chain_from_accumulators(ctx, acc):
+    """Per-Gaussian chain rule on a caller-provided accumulator array (ggs_backward_from_accumulators)."""
+    import ctypes as C
+
+    from diff_gaussian_rasterization import _abi
+
+    grads, gst = ctx["alloc_grads"]()
+    acc = acc.contiguous()
+    rc = _abi.lib.ggs_backward_from_accumulators(C.byref(ctx["frame"]), C.byref(ctx["g"]), C.byref(ctx["state"]),
+                                                 _abi.ptr(ctx["radii"]), _abi.ptr(acc), C.byref(gst), ctx["stream"])
+    _abi.check(rc, "ggs_backward_from_accumulators")
+    torch.cuda.synchronize()
+    return grads
+
+
+def grad_cancellation(mod, sc, device, require_depth=True):
+    """Conditioning of the per-Gaussian chain rule with respect to its 17 accumulated sums.
+
+    The chain (render_backward.cu:249-713) is linear in the accumulators a_j, so grad = sum_j chain(a_j e_j) and
+    A = sum_j |chain(a_j e_j)| is the magnitude a relative perturbation of the a_j is multiplied with.  The reference
+    accumulates the a_j with float atomics (relative error of a few eps32 each, in a timing-dependent order); on a
+    thin, strongly anisotropic splat the chain multiplies that by (s_max / s_min)^2 and the result moves by more
+    than 1e-4 although both implementations are correct.  Returns A per gradient tensor (CPU, double)."""
+    _, acc, ctx = ours_backward_raw(sc, device, require_depth)
+    A = None
+    for j in range(17):
+        a = torch.zeros_like(acc)
+        a[:, j] = acc[:, j]
+        gr = chain_from_accumulators(ctx, a)
+        if A is None:
+            A = {n: v.abs().double().cpu() for n, v in gr.items()}
+        else:
+            for n, v in gr.items():
+                A[n] += v.abs().double().cpu()
+    return A
+
+
+def grad_excess(a, b, cancel, tol=None, k_eps=32.0):
+    """max over elements of |a-b| - (tol * max|b| + k_eps * eps32 * cancel): <= 0 means within tolerance.
+    k_eps = 32: a float-atomic sum of a few dozen partial sums is off by a few eps32, and the chain's own float
+    arithmetic (identical in both implementations up to instruction order) adds a few more."""
+    tol = GRAD_TOL if tol is None else tol
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    if b.numel() == 0:
+        return 0.0
+    bound = tol * float(b.abs().max()) + k_eps * 5.96e-8 * cancel
+    return float(((a - b).abs() - bound).max())
+
+
 def int_mismatch(a, b):
     a = a.detach().cpu()
     b = b.detach().cpu()

@@ -52,10 +52,30 @@ def main():
         print(f"{name:40s} device {e0.elapsed_time(e1) / args.steps:7.3f} ms/step   host {(t1 - t0) * 1e3 / args.steps:7.3f} ms/step")
         _abi.profile_enable(False)
 
+    def with_sampler(period):
+        smp = bench.ClockSampler(0, period_s=period)
+        smp.start()
+        loop(f"no sync, NVML sampler every {period * 1e3:.0f} ms", False, False)
+        print("    ", smp.stop())
+
     loop("no sync, stage profiler on", False, True)
     loop("no sync, stage profiler off", False, False)
     loop("sync per step, profiler off", True, False)
     loop("no sync, stage profiler off (again)", False, False)
+    with_sampler(0.02)
+    with_sampler(0.1)
+    loop("no sync, stage profiler off (again)", False, False)
+
+    # per-step device times of a no-sync loop (outliers = allocator / driver hiccups)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs[0].record()
+    for i in range(args.steps):
+        step.resident()
+        evs[i + 1].record()
+    torch.cuda.synchronize()
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    print("per-step device ms: min %.3f median %.3f max %.3f" % (min(per), sorted(per)[len(per) // 2], max(per)),
+          " ".join("%.2f" % x for x in per))
 
     # host time inside the two ABI calls
     import ctypes as C
