@@ -11,8 +11,9 @@ and normal all carry upstream gradients) on the workload BASELINE.json quotes th
   e2e    same step through the Python surface, plus per-step host<->device traffic of what changes
          every training iteration: camera + background + the four upstream-gradient images (stand-in for
          the ground-truth image of the loss) copied H2D from pinned memory, the rendered colour image
-         and a gradient checksum copied D2H.  The Gaussian parameters are the model and stay resident,
-         exactly as in the reference's train.py.
+         and a gradient checksum copied D2H, on a copy stream with double buffering so that the copies
+         of neighbouring steps overlap the kernels.  The Gaussian parameters are the model and stay
+         resident, exactly as in the reference's train.py.
   N > 1  one process per GPU; rank r renders view r of an N-view batch of the same scene and the
          parameter gradients are summed with one NCCL all-reduce inside the timed region (weak scaling).
   --impl reference   the UNMODIFIED reference CUDA rasterizer compiled into oracle/_ref (the reference
@@ -165,11 +166,9 @@ class Step:
         # host staging for the end-to-end variant
         self.cam_host = {k: v.cpu().pin_memory() for k, v in self.cam_dev.items()}
         self.grads_host = {k: v.cpu().pin_memory() for k, v in sc.grads.items()}
-        self.color_host = torch.empty(3, c.H, c.W).pin_memory()
-        self.check_host = torch.empty(1).pin_memory()
         self.h2d_bytes = sum(v.numel() * 4 for v in self.cam_host.values()) + \
             sum(v.numel() * 4 for v in self.grads_host.values())
-        self.d2h_bytes = self.color_host.numel() * 4 + 4
+        self.d2h_bytes = 3 * c.H * c.W * 4 + 4
         self.flat = None
 
     def _settings(self, cam):
@@ -203,13 +202,58 @@ class Step:
     def resident(self):
         self._fwd_bwd(self.cam_dev, self.grads_dev)
 
+    def _pipeline(self):
+        """Double-buffered device copies of the per-step inputs and outputs + a copy stream."""
+        dev = self.device
+        self.copy_stream = torch.cuda.Stream(dev)
+        self.slots = []
+        for _ in range(2):
+            slot = dict(cam={k: torch.empty_like(v, device=dev) for k, v in self.cam_host.items()},
+                        g={k: torch.empty_like(v, device=dev) for k, v in self.grads_host.items()},
+                        out=torch.empty(3, self.sc.cam.H, self.sc.cam.W, device=dev),
+                        chk=torch.empty(1, device=dev), ready=torch.cuda.Event(), free=torch.cuda.Event(),
+                        color_host=torch.empty(3, self.sc.cam.H, self.sc.cam.W).pin_memory(),
+                        check_host=torch.empty(1).pin_memory())
+            slot["free"].record()
+            self.slots.append(slot)
+        self.pipe_i = 0
+        self.prev_d2h = None
+        self._prefetch(self.slots[0])
+
+    def _prefetch(self, slot):
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(slot["free"])  # the step that last read this slot has finished
+            for k, v in self.cam_host.items():
+                slot["cam"][k].copy_(v, non_blocking=True)
+            for k, v in self.grads_host.items():
+                slot["g"][k].copy_(v, non_blocking=True)
+            slot["ready"].record(self.copy_stream)
+
     def end_to_end(self):
-        cam = {k: v.to(self.device, non_blocking=True) for k, v in self.cam_host.items()}
-        g = {k: v.to(self.device, non_blocking=True) for k, v in self.grads_host.items()}
-        color = self._fwd_bwd(cam, g)
-        self.color_host.copy_(color.detach(), non_blocking=True)
-        self.check_host.copy_(self.params["means3D"].grad.abs().sum().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        """One step with its host traffic: H2D of this step's camera + upstream-gradient images from pinned memory
+        and D2H of its colour image + gradient checksum.  The copies run on a copy stream, double-buffered, so the
+        H2D of step i+1 and the D2H of step i-1 overlap the kernels of step i (what a trainer's data loader does);
+        the host waits every step for the previous step's result to have landed.  Same harness for both arms."""
+        if not hasattr(self, "slots"):
+            self._pipeline()
+        cur = torch.cuda.current_stream()
+        slot = self.slots[self.pipe_i & 1]
+        self._prefetch(self.slots[(self.pipe_i + 1) & 1])
+        cur.wait_event(slot["ready"])
+        color = self._fwd_bwd(slot["cam"], slot["g"])
+        slot["out"].copy_(color.detach())
+        torch.sum(self.params["means3D"].grad.abs(), dim=None, out=slot["chk"].view(()))
+        slot["free"].record(cur)
+        d2h = torch.cuda.Event()
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(slot["free"])
+            slot["color_host"].copy_(slot["out"], non_blocking=True)
+            slot["check_host"].copy_(slot["chk"], non_blocking=True)
+            d2h.record(self.copy_stream)
+        if self.prev_d2h is not None:
+            self.prev_d2h.synchronize()
+        self.prev_d2h = d2h
+        self.pipe_i += 1
 
 
 def timed(fn, steps, warmup, world, sampler=None):
