@@ -397,6 +397,7 @@ def main():
                 acc[k] = acc.get(k, 0.0) + float(v)
             reps += 1
         stages = {k[:-3]: acc[k] / reps for k in acc if k.endswith("_ms")}
+        sort_passes_run = int(t["sort_passes"])
         _abi.profile_enable(False)
     else:
         reps = 0
@@ -452,8 +453,11 @@ def main():
         outs, inter = H.ours_forward_raw(sc, str(device))
         stats = {"P": sc.P, "visible": int((outs["radii"] > 0).sum()), "num_rendered": inter["num_rendered"],
                  "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
-        passes = (stats["sort_bits"] + 7) // 8
-        line["gpu_launches"] = args.steps * (3 + 2 + passes + 1 + 1 + 2)
+        # launches of OUR kernels per step: preprocess, scan, duplicate, histogram, offsets, the onesweep passes
+        # actually run (5 of the 6 eight-bit digits when the depth keys allow the compact plan), ranges, render fwd,
+        # render bwd, per-Gaussian bwd
+        stats["sort_passes_run"] = sort_passes_run
+        line["gpu_launches"] = args.steps * (3 + 2 + sort_passes_run + 1 + 1 + 2)
         alg = algorithmic(stats)
         per_stage = {}
         for k, b in alg.items():

@@ -42,6 +42,7 @@ struct Profiler {
     bool have_fwd = false, have_bwd = false;
     cudaEvent_t ev[EV_COUNT] = {};
     bool created = false;
+    int sort_passes = 0;
 };
 Profiler g_prof;  // process-wide: autograd runs the backward on its own thread
 
@@ -128,7 +129,7 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     prof_mark(stream, EV_F0);
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
                       at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
-                      at<uint8_t>(geom, GL.clamped), radii, stream);
+                      at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.total) + 1, stream);
     GGS_STAGE("preprocess", debug, stream);
     prof_mark(stream, EV_PRE);
     launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
@@ -136,34 +137,40 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
                 at<uint32_t>(geom, GL.total), stream);
     GGS_STAGE("scan", debug, stream);
     prof_mark(stream, EV_SCAN);
+    // one small read-back where the reference blocks too (rasterizer_impl.cu:384): D and the depth-key range
     uint32_t* host = pinned_word();
     if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
-    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(geom, GL.total), 4, cudaMemcpyDeviceToHost, stream));
+    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(geom, GL.total), 12, cudaMemcpyDeviceToHost, stream));
     GGS_CUDA(cudaStreamSynchronize(stream));
-    const uint32_t D = *host;
+    const uint32_t D = host[0];
+    const uint32_t depth_max_bits = host[1], depth_min_bits = ~host[2];
     if (D >= (1u << 30)) return fail(GGS_ERR_UNSUPPORTED, "more than 2^30 (tile, Gaussian) pairs");
     *D_out = D;
 
     const int tiles = fp.gx * fp.gy;
     const int end_bit = sort_end_bit(tiles);
-    const int passes = sort_passes(0, end_bit);
-    const BinLayout BL = bin_layout(D, passes, tiles);
+    const BinLayout BL = bin_layout(D, sort_passes(0, end_bit), tiles);
     void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
     if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
     *bin = b;
+    const SortPlan plan = rasterizer_sort_plan(end_bit, depth_min_bits, depth_max_bits);
+    // the sorted pairs always end up in keys_a / vals_a: with an odd number of passes the unsorted pairs start in *_b
+    const bool odd = plan.passes & 1;
+    g_prof.sort_passes = plan.passes;
+    uint64_t* k_in = at<uint64_t>(b, odd ? BL.keys_b : BL.keys_a);
+    uint64_t* k_other = at<uint64_t>(b, odd ? BL.keys_a : BL.keys_b);
+    uint32_t* v_in = at<uint32_t>(b, odd ? BL.vals_b : BL.vals_a);
+    uint32_t* v_other = at<uint32_t>(b, odd ? BL.vals_a : BL.vals_b);
     prof_mark(stream, EV_DUP0);
     launch_duplicate_keys(fp.P, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
-                          at<float>(geom, GL.depths), fp.gx, at<uint64_t>(b, BL.keys_a), at<uint32_t>(b, BL.vals_a),
-                          D, stream);
+                          at<float>(geom, GL.depths), fp.gx, k_in, v_in, D, stream);
     GGS_STAGE("duplicate_keys", debug, stream);
     prof_mark(stream, EV_DUP);
-    const int where = launch_radix_sort(at<uint64_t>(b, BL.keys_a), at<uint64_t>(b, BL.keys_b),
-                                        at<uint32_t>(b, BL.vals_a), at<uint32_t>(b, BL.vals_b), D, 0, end_bit,
-                                        at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), BL.status_bytes,
-                                        at<uint32_t>(b, BL.counters), stream);
+    launch_radix_sort(k_in, k_other, v_in, v_other, D, plan, at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status),
+                      BL.status_bytes, at<uint32_t>(b, BL.counters), stream);
     GGS_STAGE("radix_sort", debug, stream);
     prof_mark(stream, EV_SORT);
-    const uint64_t* sorted_keys = where ? at<uint64_t>(b, BL.keys_b) : at<uint64_t>(b, BL.keys_a);
+    const uint64_t* sorted_keys = at<uint64_t>(b, BL.keys_a);
     launch_tile_ranges(sorted_keys, D, ranges, tiles, stream);
     GGS_STAGE("tile_ranges", debug, stream);
     prof_mark(stream, EV_RANGES);
@@ -173,7 +180,7 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
 const uint32_t* sorted_list(void* bin, int64_t D, int tiles) {
     const int passes = sort_passes(0, sort_end_bit(tiles));
     const BinLayout BL = bin_layout((size_t)D, passes, tiles);
-    return (passes & 1) ? at<uint32_t>(bin, BL.vals_b) : at<uint32_t>(bin, BL.vals_a);
+    return at<uint32_t>(bin, BL.vals_a);  // bin_gaussians arranges the ping-pong so that the result lands here
 }
 
 uint32_t* accept_mask(void* bin, int64_t D, int tiles) {
@@ -433,9 +440,10 @@ int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussian
     launch_point_keys(PN, at<uint32_t>(pts, p_offsets), at<uint32_t>(pts, p_touched), at<float2>(pts, p_xy), fp.gx,
                       fp.gy, at<uint64_t>(pbin, PL.keys_a), at<uint32_t>(pbin, PL.vals_a), stream);
     const int where = launch_radix_sort(at<uint64_t>(pbin, PL.keys_a), at<uint64_t>(pbin, PL.keys_b),
-                                        at<uint32_t>(pbin, PL.vals_a), at<uint32_t>(pbin, PL.vals_b), E, 32, 32 + bit,
-                                        at<uint32_t>(pbin, PL.hist), at<uint32_t>(pbin, PL.status), PL.status_bytes,
-                                        at<uint32_t>(pbin, PL.counters), stream);
+                                        at<uint32_t>(pbin, PL.vals_a), at<uint32_t>(pbin, PL.vals_b), E,
+                                        plain_sort_plan(32, 32 + bit), at<uint32_t>(pbin, PL.hist),
+                                        at<uint32_t>(pbin, PL.status), PL.status_bytes, at<uint32_t>(pbin, PL.counters),
+                                        stream);
     const uint64_t* pkeys = where ? at<uint64_t>(pbin, PL.keys_b) : at<uint64_t>(pbin, PL.keys_a);
     const uint32_t* plist = where ? at<uint32_t>(pbin, PL.vals_b) : at<uint32_t>(pbin, PL.vals_a);
     launch_tile_ranges(pkeys, E, at<uint2>(tile, t_pranges), tiles, stream);
@@ -477,6 +485,7 @@ int ggs_profile_read(GgsStageTimes* t) {
         if ((rc = span(EV_RANGES, EV_RENDER, &t->render_forward_ms))) return rc;
         t->have_forward = 1;
     }
+    t->sort_passes = g_prof.sort_passes;
     if (g_prof.have_bwd) {
         if ((rc = span(EV_B0, EV_RBWD, &t->render_backward_ms))) return rc;
         if ((rc = span(EV_RBWD, EV_GBWD, &t->gaussian_backward_ms))) return rc;
@@ -514,7 +523,7 @@ int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_re
     const int passes = sort_passes(0, end_bit);
     const BinLayout BL = bin_layout((size_t)num_rendered, passes, tiles);
     L->binning_bytes = BL.bytes;
-    const bool in_b = passes & 1;
+    const bool in_b = false;  // the ping-pong is arranged so that the sorted pairs land in keys_a / vals_a
     L->sorted_keys = in_b ? BL.keys_b : BL.keys_a;
     L->point_list = in_b ? BL.vals_b : BL.vals_a;
     L->unsorted_keys = in_b ? BL.keys_a : BL.keys_b;
@@ -551,7 +560,7 @@ int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
     GGS_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
     GGS_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
     const int where = launch_radix_sort(keys_out, at<uint64_t>(scratch, BL.keys_b), vals_out,
-                                        at<uint32_t>(scratch, BL.vals_b), (uint32_t)n, begin_bit, end_bit,
+                                        at<uint32_t>(scratch, BL.vals_b), (uint32_t)n, plain_sort_plan(begin_bit, end_bit),
                                         at<uint32_t>(scratch, BL.hist), at<uint32_t>(scratch, BL.status),
                                         BL.status_bytes, at<uint32_t>(scratch, BL.counters), stream);
     if (where) {

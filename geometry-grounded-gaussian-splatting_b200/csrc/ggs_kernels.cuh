@@ -27,9 +27,11 @@ struct GaussianInputs {
 };
 
 // ---- stage 1: per-Gaussian preprocess + scan -------------------------------------------------
+// depth_extremes[0] = max over visible Gaussians of the depth's float bits, [1] = max of their complement
+// (i.e. ~min); zeroed here.  The host uses them to plan the sort (SortPlan).
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       cudaStream_t stream);
+                       uint32_t* depth_extremes, cudaStream_t stream);
 
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
                  cudaStream_t stream);
@@ -42,9 +44,27 @@ void launch_duplicate_keys(int P, const uint32_t* offsets, const uint2* rects, c
 void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,
                        int gy, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
 
-// Sorts (keys_a, vals_a) on bits [begin_bit, end_bit); returns 0 if the result is in *_a, 1 if in *_b.
+// Digit plan of the radix sort.  Plain: 8-bit digits of bits [begin_bit, end_bit).  Compact (rasterizer keys
+// tile<<32 | depth bits only): the top byte of a positive float depth takes very few distinct values (sign + 7
+// exponent bits: 0.2 .. 100 spans five), so after three plain passes over depth bits 0..23 the remaining order is
+// that of the narrow virtual key  (tile << nb) | (depth_top_byte - emin)  with nb <= 4 bits: two more passes
+// instead of three.  Same stable order as sorting bits [0, 32 + tile_bits) of the real key; keys are not modified.
+struct SortPlan {
+    int begin_bit, end_bit;
+    int passes;
+    bool compact;
+    uint32_t emin;  // smallest depth top byte present
+    int nb;         // bits that hold (top byte - emin)
+    int tile_bits;  // end_bit - 32
+};
+SortPlan plain_sort_plan(int begin_bit, int end_bit);
+// depth_min_bits / depth_max_bits: extremes of the 32 low key bits over all keys (any superset range is fine)
+SortPlan rasterizer_sort_plan(int end_bit, uint32_t depth_min_bits, uint32_t depth_max_bits);
+
+// Sorts (keys_in, vals_in); both buffer pairs are clobbered.  Returns 0 if the result is in *_a, 1 if in *_b, when
+// the input was in *_a (callers that want the result in a fixed buffer put the input in *_b when plan.passes is odd).
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
-                      int begin_bit, int end_bit, uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
+                      const SortPlan& plan, uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
                       cudaStream_t stream);
 
 void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream);

@@ -240,7 +240,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
                                                                  float* __restrict__ depths,
                                                                  uint32_t* __restrict__ tiles_touched,
                                                                  uint2* __restrict__ rects, uint8_t* __restrict__ clamped,
-                                                                 int* __restrict__ radii) {
+                                                                 int* __restrict__ radii,
+                                                                 uint32_t* __restrict__ depth_extremes) {
     extern __shared__ float s_slab[];  // [warps][32][RS] SH rows (only when colours come from SH)
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -251,6 +252,16 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
     if (in_range && !vis) {
         radii[idx] = 0;
         tiles_touched[idx] = 0;
+    }
+    {
+        // range of the depth keys (positive floats order like their bits), for the sort's digit plan
+        const uint32_t bits = vis ? __float_as_uint(pr.tc) : 0u;
+        const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
+        const uint32_t wnmax = __reduce_max_sync(0xffffffffu, vis ? ~bits : 0u);
+        if (lane == 0 && wnmax) {
+            atomicMax(depth_extremes, wmax);
+            atomicMax(depth_extremes + 1, wnmax);
+        }
     }
 
     // ---- SH slab of the warp's visible Gaussians -> shared memory -------------------------------------
@@ -323,7 +334,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
 
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       cudaStream_t stream) {
+                       uint32_t* depth_extremes, cudaStream_t stream) {
+    cudaMemsetAsync(depth_extremes, 0, 8, stream);
     if (fp.P == 0) return;
     const int threads = PRE_THREADS;
     const int blocks = (fp.P + threads - 1) / threads;
@@ -335,7 +347,7 @@ void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool wan
         configured = smem;
     }
     preprocess_kernel<<<blocks, threads, smem, stream>>>(fp, in, want_color, records, depths, tiles_touched, rects,
-                                                         clamped, radii);
+                                                         clamped, radii, depth_extremes);
 }
 
 // Frustum visibility only (reference checkFrustum, rasterizer_impl.cu:54-66).

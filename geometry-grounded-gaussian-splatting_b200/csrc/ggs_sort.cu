@@ -26,20 +26,83 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Digit extraction of one pass (see SortPlan).  vshift < 0: plain digit (key >> shift) & mask.
+struct DigitSpec {
+    int shift;
+    uint32_t mask;
+    int vshift;  // >= 0: digit of the virtual key ((tile & tile_mask) << nb) | (depth_top_byte - emin)
+    uint32_t emin, tile_mask;
+    int nb;
+};
+__device__ __forceinline__ uint32_t digit_of(const uint64_t key, const DigitSpec& s) {
+    if (s.vshift < 0) return (uint32_t)(key >> s.shift) & s.mask;
+    const uint32_t v = ((((uint32_t)(key >> 32)) & s.tile_mask) << s.nb) | ((((uint32_t)key) >> 24) - s.emin);
+    return (v >> s.vshift) & s.mask;
+}
+struct PassSpecs {
+    DigitSpec d[MAX_PASSES];
+};
+
+static DigitSpec pass_spec(const SortPlan& p, int pass) {
+    DigitSpec s;
+    s.emin = p.emin;
+    s.nb = p.nb;
+    s.tile_mask = p.tile_bits >= 32 ? 0xffffffffu : ((1u << p.tile_bits) - 1u);
+    if (!p.compact || pass < 3) {
+        s.shift = p.begin_bit + RADIX_BITS * pass;
+        const int width = p.end_bit - s.shift < RADIX_BITS ? p.end_bit - s.shift : RADIX_BITS;
+        s.mask = (1u << width) - 1u;
+        s.vshift = -1;
+    } else {
+        s.shift = 0;
+        s.vshift = RADIX_BITS * (pass - 3);
+        const int vbits = p.tile_bits + p.nb;
+        const int width = vbits - s.vshift < RADIX_BITS ? vbits - s.vshift : RADIX_BITS;
+        s.mask = (1u << width) - 1u;
+    }
+    return s;
+}
+
+SortPlan plain_sort_plan(int begin_bit, int end_bit) {
+    SortPlan p;
+    p.begin_bit = begin_bit;
+    p.end_bit = end_bit;
+    p.passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
+    p.compact = false;
+    p.emin = 0;
+    p.nb = 0;
+    p.tile_bits = end_bit > 32 ? end_bit - 32 : 0;
+    return p;
+}
+
+SortPlan rasterizer_sort_plan(int end_bit, uint32_t depth_min_bits, uint32_t depth_max_bits) {
+    SortPlan p = plain_sort_plan(0, end_bit);
+    if (end_bit <= 32 || depth_max_bits < depth_min_bits) return p;
+    const uint32_t emin = depth_min_bits >> 24, emax = depth_max_bits >> 24;
+    int nb = 0;
+    while ((1u << nb) < emax - emin + 1) nb++;
+    const int compact_passes = 3 + (p.tile_bits + nb + RADIX_BITS - 1) / RADIX_BITS;
+    if (nb <= 4 && compact_passes < p.passes) {
+        p.compact = true;
+        p.emin = emin;
+        p.nb = nb;
+        p.passes = compact_passes;
+    }
+    return p;
+}
+
 __global__ void __launch_bounds__(256) histogram_kernel(const uint64_t* __restrict__ keys, uint32_t n,
-                                                        int begin_bit, int end_bit, int passes, uint32_t* __restrict__ hist) {
+                                                        const PassSpecs specs, int passes, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_hist[MAX_PASSES][RADIX];
     for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += blockDim.x) (&s_hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        // only bits [begin_bit, end_bit) take part (the last digit may be narrower than 8 bits)
-        uint64_t k = __ldg(keys + i) >> begin_bit;
-        const int width = end_bit - begin_bit;
-        if (width < 64) k &= (1ull << width) - 1ull;
+        // only the planned digits take part (the last one may be narrower than 8 bits)
+        const uint64_t k = __ldg(keys + i);
 #pragma unroll
         for (int p = 0; p < MAX_PASSES; p++) {
-            if (p < passes) atomicAdd(&s_hist[p][(uint32_t)(k >> (RADIX_BITS * p)) & (RADIX - 1)], 1u);
+            if (p < passes) atomicAdd(&s_hist[p][digit_of(k, specs.d[p])], 1u);
         }
     }
     __syncthreads();
@@ -75,8 +138,8 @@ __global__ void __launch_bounds__(RADIX) offsets_kernel(uint32_t* __restrict__ h
 __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* __restrict__ keys_in,
                                                                 uint64_t* __restrict__ keys_out,
                                                                 const uint32_t* __restrict__ vals_in,
-                                                                uint32_t* __restrict__ vals_out, uint32_t n, int shift,
-                                                                uint32_t digit_mask,
+                                                                uint32_t* __restrict__ vals_out, uint32_t n,
+                                                                const DigitSpec spec,
                                                                 const uint32_t* __restrict__ bin_offsets,
                                                                 uint32_t* __restrict__ status,
                                                                 uint32_t* __restrict__ counter) {
@@ -116,7 +179,8 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     const uint32_t lanemask_lt = (1u << lane) - 1;
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
+        // padding (beyond the end of the input) must rank after every real pair: it takes the largest digit
+        const uint32_t d = (warp_base + i * 32 + lane < count) ? digit_of(key[i], spec) : spec.mask;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
@@ -183,7 +247,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     // ---- reorder through shared memory, then coalesced digit runs ------------------------------
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const uint32_t dg = (uint32_t)(key[i] >> shift) & digit_mask;
+        const uint32_t dg = (warp_base + i * 32 + lane < count) ? digit_of(key[i], spec) : spec.mask;
         const uint32_t pos = s_bin_start[dg] + s_warp_hist[warp][dg] + rank[i];
         s_keys[pos] = key[i];
         s_vals[pos] = val[i];
@@ -191,7 +255,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     __syncthreads();
     for (uint32_t p = tid; p < count; p += SORT_THREADS) {
         const uint64_t k = s_keys[p];
-        const uint32_t dg = (uint32_t)(k >> shift) & digit_mask;
+        const uint32_t dg = digit_of(k, spec);
         const uint32_t out = s_global_base[dg] + p;
         keys_out[out] = k;
         vals_out[out] = s_vals[p];
@@ -199,27 +263,26 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
 }
 
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
-                      int begin_bit, int end_bit, uint32_t* hist, uint32_t* status, size_t status_bytes,
+                      const SortPlan& plan, uint32_t* hist, uint32_t* status, size_t status_bytes,
                       uint32_t* counters, cudaStream_t stream) {
     if (n == 0) return 0;
-    const int passes = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
+    const int passes = plan.passes;
+    PassSpecs specs;
+    for (int p = 0; p < MAX_PASSES; p++) specs.d[p] = pass_spec(plan, p < passes ? p : 0);
     const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
     cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
     cudaMemsetAsync(status, 0, status_bytes, stream);
     cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
     const int hist_blocks = (int)min((uint32_t)(148 * 8), (n + 255) / 256);
-    histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_a, n, begin_bit, end_bit, passes, hist);
+    histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_a, n, specs, passes, hist);
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
     uint64_t* kin = keys_a;
     uint64_t* kout = keys_b;
     uint32_t* vin = vals_a;
     uint32_t* vout = vals_b;
     for (int p = 0; p < passes; p++) {
-        const int shift = begin_bit + RADIX_BITS * p;
-        const int width = end_bit - shift < RADIX_BITS ? end_bit - shift : RADIX_BITS;
-        onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, shift, (1u << width) - 1u,
-                                                            hist + p * RADIX, status + (size_t)p * tiles * RADIX,
-                                                            counters + p);
+        onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX,
+                                                            status + (size_t)p * tiles * RADIX, counters + p);
         uint64_t* tk = kin;
         kin = kout;
         kout = tk;

@@ -70,7 +70,7 @@ class GgsLayout(C.Structure):
 class GgsStageTimes(C.Structure):
     _fields_ = [("have_forward", C.c_int32), ("have_backward", C.c_int32)] + [(n, C.c_float) for n in (
         "preprocess_ms", "scan_ms", "duplicate_ms", "sort_ms", "ranges_ms", "render_forward_ms",
-        "render_backward_ms", "gaussian_backward_ms")]
+        "render_backward_ms", "gaussian_backward_ms")] + [("sort_passes", C.c_int32)]
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)

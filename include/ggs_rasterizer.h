@@ -191,6 +191,7 @@ typedef struct GgsStageTimes {
     int32_t have_forward, have_backward;
     float preprocess_ms, scan_ms, duplicate_ms, sort_ms, ranges_ms, render_forward_ms;
     float render_backward_ms, gaussian_backward_ms;
+    int32_t sort_passes; /* radix passes the most recent forward actually ran (5 with the compact digit plan) */
 } GgsStageTimes;
 GGS_API int ggs_profile_enable(int on);
 GGS_API int ggs_profile_read(GgsStageTimes* times);
