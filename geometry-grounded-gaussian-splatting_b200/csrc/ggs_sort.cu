@@ -135,6 +135,10 @@ __global__ void __launch_bounds__(RADIX) offsets_kernel(uint32_t* __restrict__ h
     }
 }
 
+// MATCH: rank with match.any (one instruction, ~10 cycles when most lanes hold different digits, as for depth
+// mantissa bits -- but measured ~65 cycles when lanes share digits in runs, as for tile bits of depth-sorted
+// pairs: the ADU pipe became the bottleneck of those passes).  !MATCH: eight ballots, constant cost.
+template <bool MATCH>
 __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* __restrict__ keys_in,
                                                                 uint64_t* __restrict__ keys_out,
                                                                 const uint32_t* __restrict__ vals_in,
@@ -181,7 +185,18 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     for (int i = 0; i < SORT_ITEMS; i++) {
         // padding (beyond the end of the input) must rank after every real pair: it takes the largest digit
         const uint32_t d = (warp_base + i * 32 + lane < count) ? digit_of(key[i], spec) : spec.mask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        uint32_t peers;
+        if constexpr (MATCH) {
+            peers = __match_any_sync(0xffffffffu, d);
+        } else {
+            peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < RADIX_BITS; b++) {
+                const bool one = (d >> b) & 1u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, one);
+                peers &= one ? bal : ~bal;
+            }
+        }
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (lane == leader) {
@@ -281,8 +296,16 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
     uint32_t* vin = vals_a;
     uint32_t* vout = vals_b;
     for (int p = 0; p < passes; p++) {
-        onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX,
-                                                            status + (size_t)p * tiles * RADIX, counters + p);
+        // tile-bit digits (virtual key, or plain digits above bit 32) come in runs: rank them with ballots
+        const bool tile_digit = specs.d[p].vshift >= 0 || specs.d[p].shift >= 32;
+        if (tile_digit)
+            onesweep_kernel<false><<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p],
+                                                                       hist + p * RADIX,
+                                                                       status + (size_t)p * tiles * RADIX, counters + p);
+        else
+            onesweep_kernel<true><<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p],
+                                                                      hist + p * RADIX,
+                                                                      status + (size_t)p * tiles * RADIX, counters + p);
         uint64_t* tk = kin;
         kin = kout;
         kout = tk;
