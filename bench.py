@@ -170,6 +170,8 @@ class Step:
             sum(v.numel() * 4 for v in self.grads_host.values())
         self.d2h_bytes = 3 * c.H * c.W * 4 + 4
         self.flat = None
+        # view-parallel runs of our arm: SH gradient summed over views from the all-gathered colour gradients
+        self.factored = bool(allreduce) and hasattr(mod, "_SH_FACTORING") and sc.sg_color.shape[1] == 0
 
     def _settings(self, cam):
         c = self.sc.cam
@@ -189,13 +191,23 @@ class Step:
             means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"], sg_axis=self.sg[0],
             sg_sharpness=self.sg[1], sg_color=self.sg[2], colors_precomp=None, scales=p["scales"], rotations=p["rotations"],
             cov3D_precomp=None)
-        torch.autograd.backward([color, mdepth, alpha, normal], [g["color"], g["mdepth"], g["alpha"], g["normal"]])
+        if self.factored:
+            from diff_gaussian_rasterization.parallel import factored_sh_gradients
+
+            with factored_sh_gradients():
+                torch.autograd.backward([color, mdepth, alpha, normal],
+                                        [g["color"], g["mdepth"], g["alpha"], g["normal"]])
+        else:
+            torch.autograd.backward([color, mdepth, alpha, normal], [g["color"], g["mdepth"], g["alpha"], g["normal"]])
         if self.allreduce:
-            # one NCCL all-reduce over the flat bucket of all parameter gradients (59 floats per Gaussian at SH3)
+            # the SH gradient came back already summed over views (factored_sh_gradients: 12 B per Gaussian and view
+            # all-gathered instead of 192 B all-reduced); one NCCL all-reduce over the flat bucket of the other
+            # parameter gradients (11 floats per Gaussian)
             if self.flat is None:
                 from diff_gaussian_rasterization.parallel import GradientBucket
 
-                self.flat = GradientBucket([p[k] for k in ("means3D", "opacities", "scales", "rotations", "shs")])
+                names = ("means3D", "opacities", "scales", "rotations") + (() if self.factored else ("shs",))
+                self.flat = GradientBucket([p[k] for k in names])
             self.flat.allreduce()
         return color
 
@@ -429,7 +441,10 @@ def main():
         "mpix_per_s": value * npix / 1e6,
         "config": {"workload": f"{args.workload}: {sc.P} Gaussians, {c.W}x{c.H}, SH{sc.sh_degree}, "
                                "require_depth=True, one view per rank",
-                   "views_per_step": n_ranks, "parallelism": f"view-parallel x{n_ranks}" if multi else "single GPU",
+                   "views_per_step": n_ranks,
+                   "parallelism": (f"view-parallel x{n_ranks}: one view per rank, NCCL all-gather of the per-view colour "
+                                   "gradients (SH gradient rebuilt locally) + all-reduce of the other parameter "
+                                   "gradients, inside the timed region") if multi else "single GPU",
                    "l2": "working set (>700 MB per step) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_value, "unit": "iters/s", "h2d_bytes_per_step": step.h2d_bytes,
                 "d2h_bytes_per_step": step.d2h_bytes},

@@ -285,7 +285,8 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     if (!grads->dL_dmeans3D || !grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity ||
         !grads->dL_dscales || !grads->dL_drotations)
         return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
-    if (in.shs && !grads->dL_dsh) return fail(GGS_ERR_INVALID_ARGUMENT, "dL_dsh required with shs");
+    if (in.shs && !grads->dL_dsh && !grads->dL_drgb)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "dL_dsh (or dL_drgb) required with shs");
     if (in.shs && fp.SGM && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
         return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");
     const bool debug = frame->debug != 0;
@@ -329,6 +330,7 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     gg.dL_dscales = grads->dL_dscales;
     gg.dL_drotations = grads->dL_drotations;
     gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
+    gg.dL_drgb = in.shs ? grads->dL_drgb : nullptr;
     const bool sg = in.shs && fp.SGM;
     gg.dL_dsg_axis = sg ? grads->dL_dsg_axis : nullptr;
     gg.dL_dsg_sharpness = sg ? grads->dL_dsg_sharpness : nullptr;
@@ -364,6 +366,7 @@ int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* ga
     gg.dL_dscales = grads->dL_dscales;
     gg.dL_drotations = grads->dL_drotations;
     gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
+    gg.dL_drgb = in.shs ? grads->dL_drgb : nullptr;
     const bool sg = in.shs && fp.SGM;
     if (sg && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
         return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");
@@ -372,6 +375,19 @@ int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* ga
     gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
     launch_gaussian_backward(fp, in, radii, at<uint8_t>(state->geometry, GL.clamped), accumulators, gg, stream);
     GGS_STAGE("gaussian_backward", frame->debug != 0, stream);
+    return GGS_OK;
+}
+
+int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t sh_coeffs, int32_t views, const float* means3D,
+                               const float* campos, const float* dL_drgb, float* dL_dsh, void* stream_) {
+    if (count < 0 || count > 0x7fffffffLL || views <= 0) return fail(GGS_ERR_INVALID_ARGUMENT, "bad count / views");
+    if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > sh_coeffs)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad sh_degree / sh_coeffs");
+    if (count == 0) return GGS_OK;
+    if (!means3D || !campos || !dL_drgb || !dL_dsh) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_sh_gradient_from_views((int)count, sh_degree, sh_coeffs, views, means3D, campos, dL_drgb, dL_dsh, stream);
+    GGS_STAGE("sh_gradient_from_views", false, stream);
     return GGS_OK;
 }
 

@@ -95,6 +95,7 @@ __global__ void __launch_bounds__(GB_THREADS)
             st3(g.dL_dmeans3D, idx, 0.f, 0.f, 0.f);
             st3(g.dL_dmeans2D, idx, 0.f, 0.f, 0.f);
             st3(g.dL_dcolors, idx, 0.f, 0.f, 0.f);
+            if (g.dL_drgb) st3(g.dL_drgb, idx, 0.f, 0.f, 0.f);
             g.dL_dopacity[idx] = 0.f;
             st3(g.dL_dscales, idx, 0.f, 0.f, 0.f);
             reinterpret_cast<float4*>(g.dL_drotations)[idx] = {0.f, 0.f, 0.f, 0.f};
@@ -443,7 +444,10 @@ __global__ void __launch_bounds__(GB_THREADS)
                 }
             }
         }
+        if (g.dL_drgb) st3(g.dL_drgb, idx, dL_dRGB.x, dL_dRGB.y, dL_dRGB.z);
         // ---- d colour / d SH coefficient: overwrite the row with the gradient (render_backward.cu:76-160) ----
+        // (skipped when the caller forms the SH gradient from dL_drgb itself: view-parallel training)
+        if (g.dL_dsh) {
         auto put = [&](int k, float w) {
             srow[3 * k] = w * dL_dRGB.x;
             srow[3 * k + 1] = w * dL_dRGB.y;
@@ -476,6 +480,7 @@ __global__ void __launch_bounds__(GB_THREADS)
             }
         }
         for (int k = written * 3; k < F; k++) srow[k] = 0.f;
+        }
 
         float3 dL_ddir = {dRGBdx.x * dL_dRGB.x + dRGBdx.y * dL_dRGB.y + dRGBdx.z * dL_dRGB.z,
                           dRGBdy.x * dL_dRGB.x + dRGBdy.y * dL_dRGB.y + dRGBdy.z * dL_dRGB.z,

@@ -117,6 +117,7 @@ struct GaussianGrads {
     float* dL_dsg_axis;       // [P,SGM,3] or null
     float* dL_dsg_sharpness;  // [P,SGM] or null
     float* dL_dsg_color;      // [P,SGM,3] or null
+    float* dL_drgb;           // [P,3] or null: dL/d(colour) after the clamp mask (the factor of the SH gradient)
 };
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
                               const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
@@ -130,6 +131,10 @@ void launch_integrate(int tiles, uint32_t max_blocks, const uint32_t* tile_offse
                       const uint2* point_ranges, const uint32_t* gaussian_list, const uint32_t* point_list,
                       const SplatRecord* records, const float2* points2D, const float* point_depths,
                       float* out_transmittance, uint8_t* inside, cudaStream_t stream);
+
+// View-parallel training: dL_dsh[p][k][c] = sum_v basis_k(dir(p, campos[v])) * dL_drgb[v][p][c]  (ggs_multiview.cu)
+void launch_sh_gradient_from_views(int P, int SHD, int SHM, int V, const float* means3D, const float* campos,
+                                   const float* dL_drgb, float* dL_dsh, cudaStream_t stream);
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 

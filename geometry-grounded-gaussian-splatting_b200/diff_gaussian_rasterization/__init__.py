@@ -48,6 +48,12 @@ class GaussianRasterizationSettings(NamedTuple):
     debug: bool
 
 
+# View-parallel training (parallel.factored_sh_gradients): when set, the backward does not write the per-view SH
+# gradient; it all-gathers the 3-float masked colour gradient of every view and forms the SUM over views locally
+# (ggs_sh_gradient_from_views).  Process-wide on purpose: autograd runs the backward on its own thread.
+_SH_FACTORING = {"on": False, "group": None}
+
+
 def _dev_f32(t, device):
     """Contiguous float32 tensor on `device` (the reference calls .contiguous() on everything)."""
     if t is None:
@@ -118,6 +124,29 @@ def rasterize_gaussians(means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, c
                         rotations, cov3Ds_precomp, raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, sg_axis, sg_sharpness, sg_color, colors_precomp,
                                      opacities, scales, rotations, cov3Ds_precomp, raster_settings)
+
+
+def _sum_sh_gradient_over_views(rs, means3D, d_rgb, SHM, device):
+    """dL_dsh summed over the views of all ranks: all-gather (dL_drgb [P,3], campos [3]) and rebuild the rank-one
+    per-view gradients locally.  12 bytes per Gaussian and view on the wire instead of all-reducing 12*SHM."""
+    import torch.distributed as dist
+
+    group = _SH_FACTORING["group"]
+    campos = _dev_f32(rs.campos, device).reshape(3)
+    P = means3D.shape[0]
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        world = dist.get_world_size(group)
+        all_rgb = torch.empty(world, P, 3, dtype=torch.float32, device=device)
+        all_cam = torch.empty(world, 3, dtype=torch.float32, device=device)
+        dist.all_gather_into_tensor(all_rgb, d_rgb, group=group)
+        dist.all_gather_into_tensor(all_cam, campos, group=group)
+    else:
+        world, all_rgb, all_cam = 1, d_rgb, campos
+    d_sh = torch.empty(P, SHM, 3, dtype=torch.float32, device=device)
+    _abi.check(_lib.ggs_sh_gradient_from_views(P, int(rs.sh_degree), SHM, world, _abi.ptr(means3D), _abi.ptr(all_cam),
+                                               _abi.ptr(all_rgb), _abi.ptr(d_sh), _abi.stream_handle(device)),
+               "ggs_sh_gradient_from_views")
+    return d_sh
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -206,7 +235,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         d_opacity = torch.empty(P, 1, **opts)
         d_scales = torch.empty(P, 3, **opts)
         d_rot = torch.empty(P, 4, **opts)
-        d_sh = torch.empty(P, SHM, 3, **opts)
+        factored = bool(_SH_FACTORING["on"]) and sh_ is not None and SGM == 0
+        d_sh = None if factored else torch.empty(P, SHM, 3, **opts)
+        d_rgb = torch.empty(P, 3, **opts) if factored else None
         d_sg_axis = torch.empty(P, SGM, 3, **opts)
         d_sg_sharp = torch.empty(P, SGM, **opts)
         d_sg_color = torch.empty(P, SGM, 3, **opts)
@@ -221,7 +252,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                                         _abi.ptr(gc), _abi.ptr(gd), _abi.ptr(ga), _abi.ptr(gn))
             grads = _abi.GgsGradients(_abi.ptr(d_means3D), _abi.ptr(d_means2D), _abi.ptr(d_colors),
                                       _abi.ptr(d_opacity), _abi.ptr(d_scales), _abi.ptr(d_rot), _abi.ptr(d_sh),
-                                      _abi.ptr(d_sg_axis), _abi.ptr(d_sg_sharp), _abi.ptr(d_sg_color))
+                                      _abi.ptr(d_sg_axis), _abi.ptr(d_sg_sharp), _abi.ptr(d_sg_color), _abi.ptr(d_rgb))
             arena = _abi.Arena(device)
             rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn, None,
                                              C.byref(grads), _abi.stream_handle(device))
@@ -230,6 +261,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 if arena.error is not None:
                     raise arena.error
                 _abi.check(rc, "ggs_rasterize_backward")
+            if factored:
+                d_sh = _sum_sh_gradient_over_views(rs, m3, d_rgb, SHM, device)
         had_sh, had_sa, had_ss, had_sgc, had_cp = ctx.had
         if SGM == 0:
             # lobes absent or unused: gradients of whatever was passed are zero

@@ -56,7 +56,7 @@ class GgsBackwardInputs(C.Structure):
 class GgsGradients(C.Structure):
     _fields_ = [("dL_dmeans3D", _f32p), ("dL_dmeans2D", _f32p), ("dL_dcolors", _f32p), ("dL_dopacity", _f32p),
                 ("dL_dscales", _f32p), ("dL_drotations", _f32p), ("dL_dsh", _f32p), ("dL_dsg_axis", _f32p),
-                ("dL_dsg_sharpness", _f32p), ("dL_dsg_color", _f32p)]
+                ("dL_dsg_sharpness", _f32p), ("dL_dsg_color", _f32p), ("dL_drgb", _f32p)]
 
 
 class GgsLayout(C.Structure):
@@ -76,7 +76,7 @@ class GgsStageTimes(C.Structure):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
-           "ggs_backward_from_accumulators",
+           "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
 
@@ -100,6 +100,9 @@ def _load():
     lib.ggs_backward_from_accumulators.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians),
                                                    C.POINTER(GgsForwardState), C.c_void_p, C.c_void_p,
                                                    C.POINTER(GgsGradients), C.c_void_p]
+    lib.ggs_sh_gradient_from_views.restype = C.c_int
+    lib.ggs_sh_gradient_from_views.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_integrate_points.restype = C.c_int64
     lib.ggs_integrate_points.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                          ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -11,10 +11,27 @@ One process per GPU (`torchrun`), `torch.distributed` with the NCCL backend on t
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Callable, Sequence
 
 import torch
 import torch.distributed as dist
+
+
+@contextlib.contextmanager
+def factored_sh_gradients(group=None):
+    """Inside this context the rasterizer's backward returns the SH-coefficient gradient already SUMMED over the
+    views of all ranks of `group`: instead of all-reducing [P, SHM, 3] (81 % of the parameter-gradient bytes at SH3)
+    every rank all-gathers the 3-float colour gradient per Gaussian and view and rebuilds the rank-one per-view SH
+    gradients locally.  Reduce the remaining parameters with `GradientBucket` as usual and leave `shs` out of it."""
+    from . import _SH_FACTORING
+
+    prev = dict(_SH_FACTORING)
+    _SH_FACTORING.update(on=True, group=group)
+    try:
+        yield
+    finally:
+        _SH_FACTORING.update(prev)
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:

@@ -147,6 +147,11 @@ typedef struct GgsGradients {
     float* dL_dsg_axis;      /* [P,sg_lobes,3]  or NULL */
     float* dL_dsg_sharpness; /* [P,sg_lobes]    or NULL */
     float* dL_dsg_color;     /* [P,sg_lobes,3]  or NULL */
+    /* Optional (NULL in the reference's contract): dL/d(colour) after the colour clamp mask, [P,3].  It is the
+     * factor of the rank-one SH gradient dL_dsh[p][k][c] = basis_k(dir_p) * dL_drgb[p][c]; when it is given and
+     * dL_dsh is NULL the SH gradient is not written (view-parallel training forms the sum over views with
+     * ggs_sh_gradient_from_views instead of all-reducing [P,sh_coeffs,3]). */
+    float* dL_drgb;
 } GgsGradients;
 
 GGS_API int ggs_abi_version(void);
@@ -171,6 +176,13 @@ GGS_API int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* ga
 GGS_API int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* gaussians,
                                    const GgsForwardState* state, const int32_t* radii, const double* accumulators,
                                    const GgsGradients* grads, void* stream);
+
+/* Sum over V views of the SH-coefficient gradient, from each view's masked colour gradient and camera position:
+ * dL_dsh[p][k][c] = sum_v basis_k(normalize(means3D[p] - campos[v])) * dL_drgb[v][p][c], rows k >= (sh_degree+1)^2
+ * zero.  campos is [V,3], dL_drgb is [V,P,3] (e.g. the all-gather of every rank's GgsGradients.dL_drgb). */
+GGS_API int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t sh_coeffs, int32_t views,
+                               const float* means3D, const float* campos, const float* dL_drgb, float* dL_dsh,
+                               void* stream);
 
 /* Transmittance of query points seen from `frame` (integrate): out_transmittance [PN] and
  * inside [PN] (uint8 0/1) must be zero-initialised by the caller.  Returns num_rendered. */

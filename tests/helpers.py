@@ -253,9 +253,11 @@ def ours_backward_raw(sc, device, require_depth=True):
                  colors=torch.empty(P, 3, device=device), opacities=torch.empty(P, 1, device=device),
                  scales=torch.empty(P, 3, device=device), rotations=torch.empty(P, 4, device=device),
                  shs=torch.empty(P, SHM, 3, device=device), sg_axis=torch.empty(P, SGM, 3, device=device),
-                 sg_sharpness=torch.empty(P, SGM, device=device), sg_color=torch.empty(P, SGM, 3, device=device))
+                 sg_sharpness=torch.empty(P, SGM, device=device), sg_color=torch.empty(P, SGM, 3, device=device),
+                 rgb=torch.empty(P, 3, device=device))
         st = _abi.GgsGradients(*[_abi.ptr(d[k]) for k in ("means3D", "means2D", "colors", "opacities", "scales",
-                                                           "rotations", "shs", "sg_axis", "sg_sharpness", "sg_color")])
+                                                           "rotations", "shs", "sg_axis", "sg_sharpness", "sg_color",
+                                                           "rgb")])
         return d, st
 
     grads, gst = alloc_grads()
