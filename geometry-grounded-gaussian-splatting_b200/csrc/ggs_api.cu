@@ -590,3 +590,223 @@ int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
 }
 
 }  // extern "C"
+
+// ---- sample_depth ---------------------------------------------------------------------------------------------
+namespace {
+
+struct SampleTileLayout {  // GGS_SLOT_TILE of the point-query paths
+    size_t granges, pranges, rounds, offsets, status, counter, total, bytes;
+};
+SampleTileLayout sample_tile_layout(int tiles) {
+    SampleTileLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t a = o;
+        o = align_up(o + bytes, 256);
+        return a;
+    };
+    L.granges = take((size_t)tiles * 8);
+    L.pranges = take((size_t)tiles * 8);
+    L.rounds = take((size_t)tiles * 4);
+    L.offsets = take((size_t)tiles * 4);
+    L.status = take(((size_t)tiles / SCAN_TILE + 2) * 8);
+    L.counter = take(256);
+    L.total = take(256);
+    L.bytes = o;
+    return L;
+}
+
+struct SamplePointLayout {  // GGS_SLOT_POINT
+    size_t xy, depth, touched, offsets, status, counter, total, radii, n_contrib, median_depth, bytes;
+};
+SamplePointLayout sample_point_layout(int PN, int P) {
+    SamplePointLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        size_t a = o;
+        o = align_up(o + bytes, 256);
+        return a;
+    };
+    L.xy = take((size_t)PN * 8);
+    L.depth = take((size_t)PN * 4);
+    L.touched = take((size_t)PN * 4);
+    L.offsets = take((size_t)PN * 4);
+    L.status = take(((size_t)PN / SCAN_TILE + 2) * 8);
+    L.counter = take(256);
+    L.total = take(256);
+    L.radii = take((size_t)P * 4);
+    L.n_contrib = take((size_t)PN * 4);
+    L.median_depth = take((size_t)PN * 4);
+    L.bytes = o;
+    return L;
+}
+
+}  // namespace
+
+extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                            int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
+                                            uint8_t* inside, GgsSampleState* state, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (!state) return fail(GGS_ERR_INVALID_ARGUMENT, "null state");
+    *state = GgsSampleState{};
+    if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
+    if (fp.P == 0 || num_points == 0) return 0;  // rasterize_points.cu:528
+    if (!points3D || !out_points || !inside || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    const bool debug = frame->debug != 0;
+    const int PN = (int)num_points;
+    const int tiles = fp.gx * fp.gy;
+    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;  // rasterizer_impl.cu:1084: geometry only
+    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
+
+    const GeomLayout GL = geom_layout(fp.P);
+    const SampleTileLayout TL = sample_tile_layout(tiles);
+    const SamplePointLayout PL = sample_point_layout(PN, fp.P);
+    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
+    void* tile = alloc(GGS_SLOT_TILE, TL.bytes, user);
+    void* pts = alloc(GGS_SLOT_POINT, PL.bytes, user);
+    if (!geom || !tile || !pts) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
+    state->geometry = geom;
+    state->tile = tile;
+    state->point = pts;
+
+    int64_t D = 0;
+    void* bin = nullptr;
+    rc = bin_gaussians(fp, in, false, at<int>(pts, PL.radii), geom, at<uint2>(tile, TL.granges), alloc, user, &bin, &D,
+                       debug, stream);
+    if (rc) return rc;
+    state->binning = bin;
+    state->num_rendered = D;
+
+    launch_preprocess_points(fp, PN, points3D, at<float2>(pts, PL.xy), at<float>(pts, PL.depth),
+                             at<uint32_t>(pts, PL.touched), nullptr, stream);
+    launch_scan(at<uint32_t>(pts, PL.touched), at<uint32_t>(pts, PL.offsets), PN, at<uint64_t>(pts, PL.status),
+                at<uint32_t>(pts, PL.counter), at<uint32_t>(pts, PL.total), stream);
+    GGS_STAGE("preprocess_points", debug, stream);
+    uint32_t* host = pinned_word();
+    if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
+    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(pts, PL.total), 4, cudaMemcpyDeviceToHost, stream));
+    GGS_CUDA(cudaStreamSynchronize(stream));
+    const uint32_t E = *host;
+    state->num_evaluated = E;
+
+    const int bit = (int)higher_msb((uint32_t)tiles);
+    const BinLayout QL = bin_layout(E, sort_passes(32, 32 + bit));
+    void* pbin = alloc(GGS_SLOT_POINT_BINNING, QL.bytes, user);
+    if (!pbin) return fail(GGS_ERR_ALLOC, "point binning workspace allocation failed");
+    state->point_binning = pbin;
+    launch_point_keys(PN, at<uint32_t>(pts, PL.offsets), at<uint32_t>(pts, PL.touched), at<float2>(pts, PL.xy), fp.gx,
+                      fp.gy, at<uint64_t>(pbin, QL.keys_a), at<uint32_t>(pbin, QL.vals_a), stream);
+    const int where = launch_radix_sort(at<uint64_t>(pbin, QL.keys_a), at<uint64_t>(pbin, QL.keys_b),
+                                        at<uint32_t>(pbin, QL.vals_a), at<uint32_t>(pbin, QL.vals_b), E,
+                                        plain_sort_plan(32, 32 + bit), at<uint32_t>(pbin, QL.hist),
+                                        at<uint32_t>(pbin, QL.status), QL.status_bytes, at<uint32_t>(pbin, QL.counters),
+                                        stream);
+    const uint64_t* pkeys = where ? at<uint64_t>(pbin, QL.keys_b) : at<uint64_t>(pbin, QL.keys_a);
+    launch_tile_ranges(pkeys, E, at<uint2>(tile, TL.pranges), tiles, stream);
+    launch_point_blocks(tiles, at<uint2>(tile, TL.pranges), at<uint32_t>(tile, TL.rounds), stream);
+    launch_scan(at<uint32_t>(tile, TL.rounds), at<uint32_t>(tile, TL.offsets), tiles, at<uint64_t>(tile, TL.status),
+                at<uint32_t>(tile, TL.counter), at<uint32_t>(tile, TL.total), stream);
+    GGS_STAGE("point_binning", debug, stream);
+
+    constexpr uint32_t PER_ROUND = TILE_PIXELS * POINT_BATCH;
+    const uint32_t max_blocks = E ? (uint32_t)std::min<uint64_t>((uint64_t)tiles + E / PER_ROUND, (uint64_t)E) : 0;
+    state->num_blocks = max_blocks;
+    void* blocks = alloc(GGS_SLOT_BLOCKS, (size_t)std::max<uint32_t>(max_blocks, 1) * 4, user);
+    if (!blocks) return fail(GGS_ERR_ALLOC, "block workspace allocation failed");
+    state->blocks = blocks;
+    GGS_CUDA(cudaMemsetAsync(blocks, 0, (size_t)std::max<uint32_t>(max_blocks, 1) * 4, stream));
+    const uint32_t* plist = where ? at<uint32_t>(pbin, QL.vals_b) : at<uint32_t>(pbin, QL.vals_a);
+    launch_sample_depth_forward(fp, tiles, max_blocks, at<uint32_t>(tile, TL.offsets), at<uint2>(tile, TL.granges),
+                                at<uint2>(tile, TL.pranges), sorted_list(bin, D, tiles), plist,
+                                at<SplatRecord>(geom, GL.records), at<float2>(pts, PL.xy),
+                                at<uint32_t>(pts, PL.n_contrib), at<float>(pts, PL.median_depth),
+                                at<uint32_t>(blocks, 0), out_points, inside, stream);
+    GGS_STAGE("sample_depth", debug, stream);
+    return D;
+}
+
+extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                         int64_t num_points, const GgsSampleState* state, const uint8_t* inside,
+                                         const float* dL_dout_points, GgsAllocFn alloc, void* user,
+                                         const GgsGradients* grads, float* dL_dpoints3D, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
+    if (!grads || !state || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null state/grads/alloc");
+    const int PN = (int)num_points;
+    const size_t P = (size_t)fp.P;
+    if (fp.P > 0) {
+        if (!grads->dL_dmeans3D || !grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity ||
+            !grads->dL_dscales || !grads->dL_drotations)
+            return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
+    }
+    if (PN > 0 && !dL_dpoints3D) return fail(GGS_ERR_INVALID_ARGUMENT, "null dL_dpoints3D");
+    if (fp.P == 0 || PN == 0) {
+        // rasterize_points.cu:600: nothing is launched, the zero-initialised gradients are returned
+        if (fp.P > 0) {
+            GGS_CUDA(cudaMemsetAsync(grads->dL_dmeans3D, 0, P * 12, stream));
+            GGS_CUDA(cudaMemsetAsync(grads->dL_dmeans2D, 0, P * 12, stream));
+            GGS_CUDA(cudaMemsetAsync(grads->dL_dcolors, 0, P * 12, stream));
+            GGS_CUDA(cudaMemsetAsync(grads->dL_dopacity, 0, P * 4, stream));
+            GGS_CUDA(cudaMemsetAsync(grads->dL_dscales, 0, P * 12, stream));
+            GGS_CUDA(cudaMemsetAsync(grads->dL_drotations, 0, P * 16, stream));
+        }
+        if (PN > 0) GGS_CUDA(cudaMemsetAsync(dL_dpoints3D, 0, (size_t)PN * 12, stream));
+        return GGS_OK;
+    }
+    if (!points3D || !inside || !dL_dout_points) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    if (!state->geometry || !state->binning || !state->point || !state->point_binning || !state->tile ||
+        !state->blocks)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "forward state is incomplete");
+    const bool debug = frame->debug != 0;
+    const int tiles = fp.gx * fp.gy;
+    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;
+    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
+    const GeomLayout GL = geom_layout(fp.P);
+    const SampleTileLayout TL = sample_tile_layout(tiles);
+    const SamplePointLayout PL = sample_point_layout(PN, fp.P);
+    const int bit = (int)higher_msb((uint32_t)tiles);
+    const int ppasses = sort_passes(32, 32 + bit);
+    const BinLayout QL = bin_layout((size_t)state->num_evaluated, ppasses);
+    const uint32_t* plist = (ppasses & 1) ? at<uint32_t>(state->point_binning, QL.vals_b)
+                                          : at<uint32_t>(state->point_binning, QL.vals_a);
+
+    // scratch: accumulator rows (double) + dL_dpoints2D
+    const size_t acc_bytes = align_up(P * GRAD_STRIDE * sizeof(double), 256);
+    const size_t p2d_bytes = align_up((size_t)PN * 8, 256);
+    char* scratch = static_cast<char*>(alloc(GGS_SLOT_BACKWARD, acc_bytes + p2d_bytes, user));
+    if (!scratch) return fail(GGS_ERR_ALLOC, "backward workspace allocation failed");
+    double* acc = reinterpret_cast<double*>(scratch);
+    float2* dp2d = reinterpret_cast<float2*>(scratch + acc_bytes);
+    GGS_CUDA(cudaMemsetAsync(scratch, 0, acc_bytes + p2d_bytes, stream));
+
+    void* pts = state->point;
+    launch_sample_depth_backward(fp, tiles, (uint32_t)state->num_blocks, at<uint32_t>(state->blocks, 0),
+                                 at<uint32_t>(state->tile, TL.offsets), at<uint2>(state->tile, TL.granges),
+                                 at<uint2>(state->tile, TL.pranges),
+                                 sorted_list(state->binning, state->num_rendered, tiles), plist,
+                                 at<SplatRecord>(state->geometry, GL.records), at<float2>(pts, PL.xy),
+                                 at<uint32_t>(pts, PL.n_contrib), at<float>(pts, PL.median_depth), inside,
+                                 dL_dout_points, dp2d, acc, stream);
+    GGS_STAGE("sample_depth_backward", debug, stream);
+
+    GaussianGrads gg{};
+    gg.dL_dmeans3D = grads->dL_dmeans3D;
+    gg.dL_dmeans2D = grads->dL_dmeans2D;
+    gg.dL_dcolors = grads->dL_dcolors;
+    gg.dL_dopacity = grads->dL_dopacity;
+    gg.dL_dscales = grads->dL_dscales;
+    gg.dL_drotations = grads->dL_drotations;
+    launch_gaussian_backward(fp, in, at<int>(pts, PL.radii), at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
+    GGS_STAGE("gaussian_backward", debug, stream);
+    launch_points_backward(fp, PN, points3D, at<uint32_t>(pts, PL.touched), dp2d, dL_dpoints3D, stream);
+    GGS_STAGE("points_backward", debug, stream);
+    return GGS_OK;
+}

@@ -136,6 +136,22 @@ void launch_integrate(int tiles, uint32_t max_blocks, const uint32_t* tile_offse
 void launch_sh_gradient_from_views(int P, int SHD, int SHM, int V, const float* means3D, const float* campos,
                                    const float* dL_drgb, float* dL_dsh, cudaStream_t stream);
 
+// ---- sampled median depth (sample_depth), ggs_sample_depth.cu ---------------------------------------------------
+void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
+                                 const uint2* gaussian_ranges, const uint2* point_ranges, const uint32_t* gaussian_list,
+                                 const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
+                                 uint32_t* n_contrib, float* median_depth, uint32_t* block_max_contributor,
+                                 float* output, uint8_t* inside, cudaStream_t stream);
+void launch_sample_depth_backward(const FrameParams& fp, int tiles, uint32_t max_blocks,
+                                  const uint32_t* block_max_contributor, const uint32_t* tile_offsets,
+                                  const uint2* gaussian_ranges, const uint2* point_ranges,
+                                  const uint32_t* gaussian_list, const uint32_t* point_list,
+                                  const SplatRecord* records, const float2* points2D, const uint32_t* n_contrib,
+                                  const float* median_depth, const uint8_t* inside, const float* dL_doutputs,
+                                  float2* dL_dpoints2D, double* grad_acc, cudaStream_t stream);
+void launch_points_backward(const FrameParams& fp, int PN, const float* points3D, const uint32_t* touched,
+                            const float2* dL_dpoints2D, float* dL_dpoints3D, cudaStream_t stream);
+
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 
 }  // namespace ggs

@@ -285,6 +285,85 @@ class _RasterizeGaussians(torch.autograd.Function):
         )
 
 
+class _SampleDepth(torch.autograd.Function):
+    """Autograd node of sample_depth (reference :486-655).  As in the reference, the forward runs with kernel_size
+    0 (:513) and the backward's per-Gaussian chain with the settings' kernel_size (:606)."""
+
+    @staticmethod
+    def forward(ctx, points3D, means3D, opacities, scales, rotations, raster_settings):
+        rs = raster_settings
+        _check_means(means3D)
+        if points3D.dim() < 1 or points3D.shape[-1] != 3:
+            raise RuntimeError("points3D must have shape (..., 3) with last dimension == 3")
+        device = means3D.device
+        pts = _dev_f32(points3D, device).reshape(-1, 3)
+        m3, op, sc, ro = (_dev_f32(t, device) for t in (means3D, opacities, scales, rotations))
+        PN, P = pts.shape[0], m3.shape[0]
+        out = torch.zeros(PN, 3, dtype=torch.float32, device=device)
+        inside = torch.zeros(PN, dtype=torch.bool, device=device)
+        keep = []
+        state = _abi.GgsSampleState()
+        arena = _abi.Arena(device)
+        with torch.cuda.device(device):
+            frame = _frame(rs, device, keep, kernel_size=0.0)
+            g = _gaussians(m3, op, sc, ro, None, None, None, None, None, 0)
+            n = _lib.ggs_sample_depth_forward(C.byref(frame), C.byref(g), _abi.ptr(pts), PN, arena.fn, None,
+                                              _abi.ptr(out), _abi.ptr(inside), C.byref(state),
+                                              _abi.stream_handle(device))
+            arena.done()
+            if n < 0:
+                if arena.error is not None:
+                    raise arena.error
+                _abi.check(n, "ggs_sample_depth_forward")
+        ctx.raster_settings = rs
+        ctx.arena = arena
+        ctx.counts = (int(state.num_rendered), int(state.num_evaluated), int(state.num_blocks))
+        ctx.pts_shape = points3D.shape
+        ctx.save_for_backward(pts, m3, op, sc, ro, inside)
+        inside_out = inside.reshape(points3D.shape[:-1])
+        ctx.mark_non_differentiable(inside_out)
+        return out.reshape(points3D.shape), inside_out
+
+    @staticmethod
+    def backward(ctx, grad_camera_points, grad_inside):
+        rs = ctx.raster_settings
+        pts, m3, op, sc, ro, inside = ctx.saved_tensors
+        device = m3.device
+        PN, P = pts.shape[0], m3.shape[0]
+        opts = dict(dtype=torch.float32, device=device)
+        gout = (torch.zeros(PN, 3, **opts) if grad_camera_points is None
+                else _dev_f32(grad_camera_points, device).reshape(-1, 3))
+        d_means3D = torch.empty(P, 3, **opts)
+        d_means2D = torch.empty(P, 3, **opts)
+        d_colors = torch.empty(P, 3, **opts)
+        d_opacity = torch.empty(P, 1, **opts)
+        d_scales = torch.empty(P, 3, **opts)
+        d_rot = torch.empty(P, 4, **opts)
+        d_pts = torch.empty(PN, 3, **opts)
+        keep = []
+        with torch.cuda.device(device):
+            frame = _frame(rs, device, keep)
+            g = _gaussians(m3, op, sc, ro, None, None, None, None, None, 0)
+            b = ctx.arena.buffers
+            nr, ne, nb = ctx.counts
+            state = _abi.GgsSampleState(
+                _abi.ptr(b.get(_abi.SLOT_GEOMETRY)), _abi.ptr(b.get(_abi.SLOT_BINNING)), _abi.ptr(b.get(_abi.SLOT_POINT)),
+                _abi.ptr(b.get(_abi.SLOT_POINT_BINNING)), _abi.ptr(b.get(_abi.SLOT_TILE)),
+                _abi.ptr(b.get(_abi.SLOT_BLOCKS)), nr, ne, nb)
+            grads = _abi.GgsGradients(_abi.ptr(d_means3D), _abi.ptr(d_means2D), _abi.ptr(d_colors),
+                                      _abi.ptr(d_opacity), _abi.ptr(d_scales), _abi.ptr(d_rot))
+            arena = _abi.Arena(device)
+            rc = _lib.ggs_sample_depth_backward(C.byref(frame), C.byref(g), _abi.ptr(pts), PN, C.byref(state),
+                                                _abi.ptr(inside), _abi.ptr(gout), arena.fn, None, C.byref(grads),
+                                                _abi.ptr(d_pts), _abi.stream_handle(device))
+            arena.done()
+            if rc < 0:
+                if arena.error is not None:
+                    raise arena.error
+                _abi.check(rc, "ggs_sample_depth_backward")
+        return d_pts.reshape(ctx.pts_shape), d_means3D, d_opacity, d_scales, d_rot, None
+
+
 class GaussianRasterizer(nn.Module):
     def __init__(self, raster_settings):
         super().__init__()
@@ -366,6 +445,11 @@ class GaussianRasterizer(nn.Module):
             "mesh_extract_tetrahedra.py:90-102 is commented out); see DESIGN.md")
 
     def sample_depth(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None):
-        raise NotImplementedError(
-            "sample_depth is the next row of the scope table (SURVEY.md 8(f) N1) and is not built yet; "
-            "see DESIGN.md")
+        """Camera-space points at the rendered median depth of arbitrary query points (differentiable; reference
+        :470-483).  Returns (camera_points [...,3], inside [...] bool)."""
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        if cov3D_precomp is not None and cov3D_precomp.numel():
+            raise NotImplementedError("cov3D_precomp is not supported; pass scales and rotations")
+        return _SampleDepth.apply(points3D, means3D, opacities, scales, rotations, self.raster_settings)

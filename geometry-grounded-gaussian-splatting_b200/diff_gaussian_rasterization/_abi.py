@@ -13,7 +13,8 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libggs_rasterizer.so")
 
-SLOT_GEOMETRY, SLOT_BINNING, SLOT_IMAGE, SLOT_TILE, SLOT_POINT, SLOT_POINT_BINNING, SLOT_BACKWARD = range(7)
+(SLOT_GEOMETRY, SLOT_BINNING, SLOT_IMAGE, SLOT_TILE, SLOT_POINT, SLOT_POINT_BINNING, SLOT_BACKWARD,
+ SLOT_BLOCKS) = range(8)
 
 _f32p = C.c_void_p
 
@@ -48,6 +49,12 @@ class GgsForwardState(C.Structure):
                 ("num_rendered", C.c_int64)]
 
 
+class GgsSampleState(C.Structure):
+    _fields_ = [("geometry", C.c_void_p), ("binning", C.c_void_p), ("point", C.c_void_p),
+                ("point_binning", C.c_void_p), ("tile", C.c_void_p), ("blocks", C.c_void_p),
+                ("num_rendered", C.c_int64), ("num_evaluated", C.c_int64), ("num_blocks", C.c_int64)]
+
+
 class GgsBackwardInputs(C.Structure):
     _fields_ = [("alpha", _f32p), ("normal", _f32p), ("mdepth", _f32p), ("radii", C.c_void_p),
                 ("dL_dcolor", _f32p), ("dL_dmdepth", _f32p), ("dL_dalpha", _f32p), ("dL_dnormal", _f32p)]
@@ -76,7 +83,8 @@ class GgsStageTimes(C.Structure):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
-           "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views",
+           "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
+           "ggs_sample_depth_backward",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
 
@@ -103,6 +111,14 @@ def _load():
     lib.ggs_sh_gradient_from_views.restype = C.c_int
     lib.ggs_sh_gradient_from_views.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                                C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_sample_depth_forward.restype = C.c_int64
+    lib.ggs_sample_depth_forward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
+                                             ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(GgsSampleState),
+                                             C.c_void_p]
+    lib.ggs_sample_depth_backward.restype = C.c_int
+    lib.ggs_sample_depth_backward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
+                                              C.POINTER(GgsSampleState), C.c_void_p, C.c_void_p, ALLOC_FN, C.c_void_p,
+                                              C.POINTER(GgsGradients), C.c_void_p, C.c_void_p]
     lib.ggs_integrate_points.restype = C.c_int64
     lib.ggs_integrate_points.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                          ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -66,7 +66,8 @@ typedef enum GgsSlot {
     GGS_SLOT_TILE = 3,
     GGS_SLOT_POINT = 4,
     GGS_SLOT_POINT_BINNING = 5,
-    GGS_SLOT_BACKWARD = 6
+    GGS_SLOT_BACKWARD = 6,
+    GGS_SLOT_BLOCKS = 7 /* per (tile, round of points) block state: the reference's duplicatedTileBuffer */
 } GgsSlot;
 
 /* Must return a device pointer to at least `bytes` bytes aligned to 256, or NULL on failure. */
@@ -189,6 +190,37 @@ GGS_API int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t
 GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
                              int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
                              uint8_t* inside, void* stream);
+
+/* Median depth sampled at query points (sample_depth): replaces Rasterizer::sampleDepth / sampleDepthBackward
+ * (rasterizer.h:170,197; rasterize_points.cu:459-634; pybind sample_rasterized_depth[_backward], ext.cpp:21-22).
+ * out_points [PN,3] (camera-space point on the ray through the query's pixel position at the median depth) and
+ * inside [PN] (uint8) must be zero-initialised by the caller: queries that project outside the image are not
+ * touched.  `state` receives the buffers the backward needs (slots GEOMETRY, BINNING, POINT, POINT_BINNING, TILE,
+ * BLOCKS).  Returns num_rendered.  The reference's Python wrapper passes kernel_size = 0 to the forward and the
+ * settings' kernel_size to the backward (__init__.py:513,606); callers wanting parity do the same. */
+typedef struct GgsSampleState {
+    void* geometry;
+    void* binning;
+    void* point;
+    void* point_binning;
+    void* tile;
+    void* blocks;
+    int64_t num_rendered;  /* (tile, Gaussian) pairs */
+    int64_t num_evaluated; /* query points inside the image */
+    int64_t num_blocks;    /* upper bound of (tile, round) blocks the kernels are launched with */
+} GgsSampleState;
+
+GGS_API int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                 int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
+                                 uint8_t* inside, GgsSampleState* state, void* stream);
+
+/* Gradients of ggs_sample_depth_forward: dL_dout_points [PN,3] in; dL_dpoints3D [PN,3] and the Gaussian
+ * gradients (means3D, opacity, scales, rotations of `grads`; its other members may be NULL except dL_dmeans2D and
+ * dL_dcolors, which are scratch outputs of the shared chain rule) out.  Every row is written. */
+GGS_API int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                              int64_t num_points, const GgsSampleState* state, const uint8_t* inside,
+                              const float* dL_dout_points, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                              float* dL_dpoints3D, void* stream);
 
 /* present[i] = 1 iff Gaussian i passes the near-plane test. */
 GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,

@@ -1,0 +1,95 @@
+"""sample_depth (median depth sampled at query points, forward + backward) against the compiled reference
+(DGR/diff_gaussian_rasterization/__init__.py:470-655, sample_forward.cu:430-700, sample_backward.cu)."""
+import pytest
+import torch
+
+import helpers as H
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "tiny": dict(scene=dict(name="tiny"), n=3000, seed=1),
+    "tiny_dense": dict(scene=dict(name="tiny", scale_mult=4.0, seed=77), n=5000, seed=2),
+    "c1": dict(scene=dict(name="c1"), n=70000, seed=3),
+    "c1_k01": dict(scene=dict(name="c1", kernel_size=0.1, seed=11), n=20000, seed=4),
+    "c2_small": dict(scene=dict(name="c2", P=60_000, seed=21), n=200000, seed=5),
+}
+
+
+def _queries(sc, n, seed, device):
+    """Query points: most inside the unit scene (so they project into the image and hit splats), some far away."""
+    g = torch.Generator().manual_seed(seed)
+    pts = torch.randn(n, 3, generator=g) * 0.7
+    far = torch.rand(n, generator=g) < 0.1
+    pts[far] = (torch.rand(int(far.sum()), 3, generator=g) - 0.5) * 12.0
+    up = torch.randn(n, 3, generator=g)
+    return pts.to(device), up.to(device)
+
+
+def _run(mod, sc, pts, up, device, shape=None):
+    rs = H.settings_for(mod, sc, device)
+    x = {k: getattr(sc, k).to(device).clone().requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations")}
+    p = pts.clone().requires_grad_(True)
+    q = p if shape is None else p.reshape(*shape, 3)
+    rast = mod.GaussianRasterizer(rs)
+    cam, inside = rast.sample_depth(q, x["means3D"], x["opacities"], x["scales"], x["rotations"])
+    (cam * up.reshape(cam.shape)).sum().backward()
+    torch.cuda.synchronize()
+    grads = {k: v.grad.detach().clone() for k, v in x.items()}
+    grads["points3D"] = p.grad.detach().clone()
+    return cam.detach(), inside.detach(), grads
+
+
+@pytest.mark.parametrize("tag", sorted(CASES))
+def test_sample_depth_vs_reference(tag, device, ref_module):
+    if ref_module is None:
+        pytest.skip("oracle/_ref not shipped")
+    import diff_gaussian_rasterization as ours
+
+    case = CASES[tag]
+    sc = scenes.make_scene(**case["scene"])
+    pts, up = _queries(sc, case["n"], case["seed"], device)
+    o_cam, o_in, o_g = _run(ours, sc, pts, up, device)
+    r_cam, r_in, r_g = _run(ref_module, sc, pts, up, device)
+    assert o_in.dtype == torch.bool and o_in.shape == r_in.shape
+    assert int(r_in.sum()) > case["n"] // 50, "test scene does not exercise the bisection"
+    assert H.int_mismatch(o_in, r_in) == 0
+    err, bad = H.image_rel_err(o_cam, r_cam)
+    assert err <= H.IMG_TOL, f"camera points: max rel err {err:.3e} ({bad} above tolerance)"
+    _, _, r_g2 = _run(ref_module, sc, pts, up, device)
+    for k in ("points3D", "means3D", "opacities", "scales", "rotations"):
+        e = H.grad_rel_err(o_g[k], r_g[k])
+        noise = H.grad_rel_err(r_g2[k], r_g[k])
+        assert e <= max(H.GRAD_TOL, 3.0 * noise), f"grad {k}: rel err {e:.3e} (reference noise {noise:.3e})"
+
+
+def test_sample_depth_shapes_and_empty(device):
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("tiny")
+    pts, up = _queries(sc, 24 * 16, 9, device)
+    cam, inside, g = _run(ours, sc, pts, up, device, shape=(24, 16))
+    assert cam.shape == (24, 16, 3) and inside.shape == (24, 16)
+    flat_cam, flat_in, _ = _run(ours, sc, pts, up, device)
+    assert torch.equal(cam.reshape(-1, 3), flat_cam) and torch.equal(inside.reshape(-1), flat_in)
+    # queries that are not inside (outside the image or no median depth) give a zero point
+    assert float(cam[~inside].abs().max() if (~inside).any() else 0.0) == 0.0
+    # no query points
+    rs = H.settings_for(ours, sc, device)
+    rast = ours.GaussianRasterizer(rs)
+    x = [getattr(sc, k).to(device) for k in ("means3D", "opacities", "scales", "rotations")]
+    cam0, in0 = rast.sample_depth(torch.zeros(0, 3, device=device), *x)
+    assert cam0.shape == (0, 3) and in0.shape == (0,)
+
+
+def test_sample_depth_is_deterministic(device):
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("c1")
+    pts, up = _queries(sc, 30000, 13, device)
+    a = _run(ours, sc, pts, up, device)
+    b = _run(ours, sc, pts, up, device)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    for k in a[2]:
+        assert torch.equal(a[2][k], b[2][k]), k
