@@ -643,9 +643,12 @@ SamplePointLayout sample_point_layout(int PN, int P) {
 
 }  // namespace
 
-extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
-                                            int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
-                                            uint8_t* inside, GgsSampleState* state, void* stream_) {
+namespace {
+// Shared driver of sample_depth (sdf == false) and evaluate_sdf (sdf == true: out_points = median depth [PN],
+// out_sdf = depth difference [PN]).
+int64_t sample_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D, int64_t num_points,
+                      GgsAllocFn alloc, void* user, float* out_points, float* out_sdf, uint8_t* inside,
+                      GgsSampleState* state, bool sdf, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FrameParams fp;
     GaussianInputs in;
@@ -655,7 +658,8 @@ extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaus
     *state = GgsSampleState{};
     if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
     if (fp.P == 0 || num_points == 0) return 0;  // rasterize_points.cu:528
-    if (!points3D || !out_points || !inside || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    if (!points3D || !out_points || !inside || !alloc || (sdf && !out_sdf))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
     const bool debug = frame->debug != 0;
     const int PN = (int)num_points;
     const int tiles = fp.gx * fp.gy;
@@ -720,6 +724,14 @@ extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaus
     state->blocks = blocks;
     GGS_CUDA(cudaMemsetAsync(blocks, 0, (size_t)std::max<uint32_t>(max_blocks, 1) * 4, stream));
     const uint32_t* plist = where ? at<uint32_t>(pbin, QL.vals_b) : at<uint32_t>(pbin, QL.vals_a);
+    if (sdf) {
+        launch_evaluate_sdf(fp, tiles, max_blocks, at<uint32_t>(tile, TL.offsets), at<uint2>(tile, TL.granges),
+                            at<uint2>(tile, TL.pranges), sorted_list(bin, D, tiles), plist,
+                            at<SplatRecord>(geom, GL.records), at<float2>(pts, PL.xy), at<float>(pts, PL.depth),
+                            out_points, out_sdf, inside, stream);
+        GGS_STAGE("evaluate_sdf", debug, stream);
+        return D;
+    }
     launch_sample_depth_forward(fp, tiles, max_blocks, at<uint32_t>(tile, TL.offsets), at<uint2>(tile, TL.granges),
                                 at<uint2>(tile, TL.pranges), sorted_list(bin, D, tiles), plist,
                                 at<SplatRecord>(geom, GL.records), at<float2>(pts, PL.xy),
@@ -727,6 +739,22 @@ extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaus
                                 at<uint32_t>(blocks, 0), out_points, inside, stream);
     GGS_STAGE("sample_depth", debug, stream);
     return D;
+}
+}  // namespace
+
+extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                            int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
+                                            uint8_t* inside, GgsSampleState* state, void* stream) {
+    return sample_points(frame, gaussians, points3D, num_points, alloc, user, out_points, nullptr, inside, state, false,
+                         stream);
+}
+
+extern "C" int64_t ggs_evaluate_sdf(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                    int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
+                                    uint8_t* inside, void* stream) {
+    GgsSampleState state;
+    return sample_points(frame, gaussians, points3D, num_points, alloc, user, out_depth, out_sdf, inside, &state, true,
+                         stream);
 }
 
 extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,

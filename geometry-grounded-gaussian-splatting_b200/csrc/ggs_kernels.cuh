@@ -142,6 +142,11 @@ void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_
                                  const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
                                  uint32_t* n_contrib, float* median_depth, uint32_t* block_max_contributor,
                                  float* output, uint8_t* inside, cudaStream_t stream);
+void launch_evaluate_sdf(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
+                         const uint2* gaussian_ranges, const uint2* point_ranges, const uint32_t* gaussian_list,
+                         const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
+                         const float* point_ts, float* out_depth, float* out_sdf, uint8_t* inside,
+                         cudaStream_t stream);
 void launch_sample_depth_backward(const FrameParams& fp, int tiles, uint32_t max_blocks,
                                   const uint32_t* block_max_contributor, const uint32_t* tile_offsets,
                                   const uint2* gaussian_ranges, const uint2* point_ranges,

@@ -39,14 +39,19 @@ __device__ __forceinline__ void stage3(float4* s_rec, int tid, const SplatRecord
     dst[2] = __ldg(src + 2);
 }
 
+// SDF = false: sample_depth (5 iterations, bracket +-0.4, outputs the camera-space point).
+// SDF = true : evaluate_sdf (sample_forward.cu:171-428: 6 iterations, bracket +-0.8; outputs the median ray depth
+//              and its difference to the query point's own ray depth).
+template <int ITERS, bool SDF>
 __global__ void __launch_bounds__(TILE_PIXELS)
     sample_depth_forward_kernel(int tiles, int W, int H, float focal_x, float focal_y,
                                 const uint32_t* __restrict__ tile_offsets, const uint2* __restrict__ gaussian_ranges,
                                 const uint2* __restrict__ point_ranges, const uint32_t* __restrict__ gaussian_list,
                                 const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
-                                const float2* __restrict__ points2D, uint32_t* __restrict__ n_contrib,
-                                float* __restrict__ median_depth, uint32_t* __restrict__ block_max_contributor,
-                                float* __restrict__ output, uint8_t* __restrict__ inside_output) {
+                                const float2* __restrict__ points2D, const float* __restrict__ point_ts,
+                                uint32_t* __restrict__ n_contrib, float* __restrict__ median_depth,
+                                uint32_t* __restrict__ block_max_contributor, float* __restrict__ output,
+                                uint8_t* __restrict__ inside_output) {
     __shared__ float4 s_rec[TILE_PIXELS * 3];
     __shared__ int s_tile;
     __shared__ uint32_t s_red[TILE_WARPS];
@@ -143,15 +148,16 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     bool inside_range[PB];
 #pragma unroll
     for (int p = 0; p < PB; p++) {
-        depth_min[p] = fmaxf(Depth[p] - SAMPLE_RANGE, 0.f);
-        depth_max[p] = fmaxf(Depth[p] + SAMPLE_RANGE, 0.f);
+        constexpr float RANGE = SDF ? SAMPLE_RANGE * 2.f : SAMPLE_RANGE;
+        depth_min[p] = fmaxf(Depth[p] - RANGE, 0.f);
+        depth_max[p] = fmaxf(Depth[p] + RANGE, 0.f);
         inside_range[p] = p < point_num_round && T[p] <= MIN_TRANSMITTANCE;
 #pragma unroll
         for (int s = 0; s < SPLIT + 1; s++) T_p[p][s] = 1.f;
     }
     const int rounds2 = (max_contributor + TILE_PIXELS - 1) / TILE_PIXELS;
 #pragma unroll 1
-    for (int it = 0; it < SPLIT_ITERATIONS; it++) {
+    for (int it = 0; it < ITERS; it++) {
         const bool first = it == 0;
         constexpr float ONE_OVER_SPLIT = 1.f / static_cast<float>(SPLIT);
         float interval[PB];
@@ -232,19 +238,24 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         const float w_max = __saturatef((T_p[p][0] - 0.5f) / (T_p[p][0] - T_p[p][SPLIT]));
         const float w_min = 1.f - w_max;
         const float mDepth = inside_range[p] ? w_max * depth_max[p] + w_min * depth_min[p] : 0.f;
-        const float2 pixnf = {(point_xy[p].x - static_cast<float>(W - 1) / 2.f) / focal_x,
-                              (point_xy[p].y - static_cast<float>(H - 1) / 2.f) / focal_y};
-        const float rln = rnorm3df(pixnf.x, pixnf.y, 1.f);
-        const float depth = mDepth * rln;
-        float* o = output + 3 * (size_t)point_idx[p];
-        o[0] = pixnf.x * depth;
-        o[1] = pixnf.y * depth;
-        o[2] = depth;
-        median_depth[point_idx[p]] = mDepth;
-        n_contrib[point_idx[p]] = last_contributor[p];
+        if constexpr (SDF) {
+            output[point_idx[p]] = mDepth - point_ts[point_idx[p]];
+            median_depth[point_idx[p]] = mDepth;
+        } else {
+            const float2 pixnf = {(point_xy[p].x - static_cast<float>(W - 1) / 2.f) / focal_x,
+                                  (point_xy[p].y - static_cast<float>(H - 1) / 2.f) / focal_y};
+            const float rln = rnorm3df(pixnf.x, pixnf.y, 1.f);
+            const float depth = mDepth * rln;
+            float* o = output + 3 * (size_t)point_idx[p];
+            o[0] = pixnf.x * depth;
+            o[1] = pixnf.y * depth;
+            o[2] = depth;
+            median_depth[point_idx[p]] = mDepth;
+            n_contrib[point_idx[p]] = last_contributor[p];
+        }
         inside_output[point_idx[p]] = inside_range[p] ? 1 : 0;
     }
-    if (tid == 0) block_max_contributor[block_id] = max_contributor;
+    if (!SDF && tid == 0) block_max_contributor[block_id] = max_contributor;
 }
 
 void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
@@ -253,9 +264,21 @@ void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_
                                  uint32_t* n_contrib, float* median_depth, uint32_t* block_max_contributor,
                                  float* output, uint8_t* inside, cudaStream_t stream) {
     if (max_blocks == 0) return;
-    sample_depth_forward_kernel<<<max_blocks, TILE_PIXELS, 0, stream>>>(
+    sample_depth_forward_kernel<SPLIT_ITERATIONS, false><<<max_blocks, TILE_PIXELS, 0, stream>>>(
         tiles, fp.W, fp.H, fp.focal_x, fp.focal_y, tile_offsets, gaussian_ranges, point_ranges, gaussian_list,
-        point_list, records, points2D, n_contrib, median_depth, block_max_contributor, output, inside);
+        point_list, records, points2D, nullptr, n_contrib, median_depth, block_max_contributor, output, inside);
+}
+
+void launch_evaluate_sdf(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
+                         const uint2* gaussian_ranges, const uint2* point_ranges, const uint32_t* gaussian_list,
+                         const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
+                         const float* point_ts, float* out_depth, float* out_sdf, uint8_t* inside,
+                         cudaStream_t stream) {
+    if (max_blocks == 0) return;
+    // the reference instantiates SPLIT_ITERATIONS + 1 iterations here (sample_forward.cu:792)
+    sample_depth_forward_kernel<SPLIT_ITERATIONS + 1, true><<<max_blocks, TILE_PIXELS, 0, stream>>>(
+        tiles, fp.W, fp.H, fp.focal_x, fp.focal_y, tile_offsets, gaussian_ranges, point_ranges, gaussian_list,
+        point_list, records, points2D, point_ts, nullptr, out_depth, nullptr, out_sdf, inside);
 }
 
 // ---- backward (sample_backward.cu:77-358) ---------------------------------------------------------------------

@@ -440,9 +440,37 @@ class GaussianRasterizer(nn.Module):
 
     def evaluate_sdf(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None,
                      view2gaussian_precomp=None):
-        raise NotImplementedError(
-            "evaluate_sdf is outside the accelerated hot path (no live caller in the reference: "
-            "mesh_extract_tetrahedra.py:90-102 is commented out); see DESIGN.md")
+        """(median ray depth, depth minus the point's own ray depth, inside) per query point (reference :404-468)."""
+        rs = self.raster_settings
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        if cov3D_precomp is not None and cov3D_precomp.numel():
+            raise NotImplementedError("cov3D_precomp is not supported; pass scales and rotations")
+        _check_means(means3D)
+        if points3D.dim() != 2 or points3D.shape[1] != 3:
+            raise RuntimeError("points3D must have dimensions (num_points, 3)")
+        device = means3D.device
+        with torch.no_grad():
+            pts = _dev_f32(points3D, device)
+            m3, op, sc, ro = (_dev_f32(t, device) for t in (means3D, opacities, scales, rotations))
+            PN = pts.shape[0]
+            depth = torch.zeros(PN, dtype=torch.float32, device=device)
+            sdf = torch.zeros(PN, dtype=torch.float32, device=device)
+            inside = torch.zeros(PN, dtype=torch.bool, device=device)
+            keep = []
+            with torch.cuda.device(device):
+                frame = _frame(rs, device, keep, kernel_size=0.0)  # the reference passes 0.0 here (:443)
+                g = _gaussians(m3, op, sc, ro, None, None, None, None, None, 0)
+                arena = _abi.Arena(device)
+                n = _lib.ggs_evaluate_sdf(C.byref(frame), C.byref(g), _abi.ptr(pts), PN, arena.fn, None,
+                                          _abi.ptr(depth), _abi.ptr(sdf), _abi.ptr(inside), _abi.stream_handle(device))
+                arena.done()
+                if n < 0:
+                    if arena.error is not None:
+                        raise arena.error
+                    _abi.check(n, "ggs_evaluate_sdf")
+        return depth, sdf, inside
 
     def sample_depth(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None):
         """Camera-space points at the rendered median depth of arbitrary query points (differentiable; reference

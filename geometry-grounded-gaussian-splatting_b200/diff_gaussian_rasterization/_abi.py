@@ -84,7 +84,7 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
-           "ggs_sample_depth_backward",
+           "ggs_sample_depth_backward", "ggs_evaluate_sdf",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
 
@@ -115,6 +115,9 @@ def _load():
     lib.ggs_sample_depth_forward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                              ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(GgsSampleState),
                                              C.c_void_p]
+    lib.ggs_evaluate_sdf.restype = C.c_int64
+    lib.ggs_evaluate_sdf.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64, ALLOC_FN,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_sample_depth_backward.restype = C.c_int
     lib.ggs_sample_depth_backward.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                               C.POINTER(GgsSampleState), C.c_void_p, C.c_void_p, ALLOC_FN, C.c_void_p,

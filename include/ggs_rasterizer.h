@@ -214,6 +214,14 @@ GGS_API int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussia
                                  int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
                                  uint8_t* inside, GgsSampleState* state, void* stream);
 
+/* Signed distance of query points to the rendered median-depth surface along their rays (evaluate_sdf): replaces
+ * Rasterizer::evaluateSDF (rasterizer.h:140; rasterize_points.cu:368-457; pybind evaluate_sdf_from_signle_view,
+ * ext.cpp:20).  out_depth [PN] = median ray depth at the query's pixel position, out_sdf [PN] = that depth minus the
+ * query's own ray depth, inside [PN] (uint8); all three zero-initialised by the caller. */
+GGS_API int64_t ggs_evaluate_sdf(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                         int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
+                         uint8_t* inside, void* stream);
+
 /* Gradients of ggs_sample_depth_forward: dL_dout_points [PN,3] in; dL_dpoints3D [PN,3] and the Gaussian
  * gradients (means3D, opacity, scales, rotations of `grads`; its other members may be NULL except dL_dmeans2D and
  * dL_dcolors, which are scratch outputs of the shared chain rule) out.  Every row is written. */

@@ -93,3 +93,26 @@ def test_sample_depth_is_deterministic(device):
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
     for k in a[2]:
         assert torch.equal(a[2][k], b[2][k]), k
+
+
+@pytest.mark.parametrize("tag", ["tiny", "c1", "c2_small"])
+def test_evaluate_sdf_vs_reference(tag, device, ref_module):
+    """evaluate_sdf: six bisection iterations over +-0.8 (sample_forward.cu:171-428)."""
+    if ref_module is None:
+        pytest.skip("oracle/_ref not shipped")
+    import diff_gaussian_rasterization as ours
+
+    case = CASES[tag]
+    sc = scenes.make_scene(**case["scene"])
+    pts, _ = _queries(sc, case["n"], case["seed"] + 100, device)
+    x = [getattr(sc, k).to(device) for k in ("means3D", "opacities", "scales", "rotations")]
+    res = {}
+    for name, mod in (("ours", ours), ("ref", ref_module)):
+        rast = mod.GaussianRasterizer(H.settings_for(mod, sc, device))
+        res[name] = rast.evaluate_sdf(pts, *x)
+        torch.cuda.synchronize()
+    (od, os_, oi), (rd, rs_, ri) = res["ours"], res["ref"]
+    assert H.int_mismatch(oi, ri) == 0 and int(ri.sum()) > 0
+    for a, b, what in ((od, rd, "depth"), (os_, rs_, "sdf")):
+        err, bad = H.image_rel_err(a, b)
+        assert err <= H.IMG_TOL, f"{what}: max rel err {err:.3e} ({bad} above tolerance)"
