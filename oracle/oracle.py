@@ -158,6 +158,32 @@ class Oracle:
         return dict(num_rendered=int(D), alpha=1 - T, transmittance=T, inside=inside.bool())
 
 
+    # ---------------------------------------------------------------- sample_depth / evaluate_sdf (forward)
+    def _sample(self, sdf, *, points3D, means3D, opacities, scales, rotations, scale_modifier=1.0, viewmatrix=None,
+                projmatrix=None, campos=None, tanfovx=1.0, tanfovy=1.0, kernel_size=0.0, image_height=0,
+                image_width=0):
+        PN, P = points3D.shape[0], means3D.shape[0]
+        keep = [_f(x) for x in (points3D, means3D, opacities, scales, rotations, viewmatrix, projmatrix, campos)]
+        pts, me, op, sc, ro, vm, pm, cpos = [k[1] for k in keep]
+        out3 = torch.zeros(PN, 3)
+        depth = torch.zeros(PN)
+        sdfv = torch.zeros(PN)
+        inside = torch.zeros(PN, dtype=torch.uint8)
+        self.L.ggs_oracle_sample_depth.restype = C.c_int64
+        D = self.L.ggs_oracle_sample_depth(
+            self.h, C.c_int(PN), C.c_int(P), C.c_int(int(image_width)), C.c_int(int(image_height)), pts, me, op, sc,
+            C.c_float(scale_modifier), ro, vm, pm, cpos, C.c_float(tanfovx), C.c_float(tanfovy),
+            C.c_float(kernel_size), C.c_int(1 if sdf else 0), _ptr(out3), _ptr(depth), _ptr(sdfv), _ptr(inside))
+        return dict(num_rendered=int(D), camera_points=out3, depth=depth, sdf=sdfv, inside=inside.bool())
+
+    def sample_depth(self, **kw):
+        """Forward of GaussianRasterizer.sample_depth for [PN,3] query points (the reference passes kernel_size 0)."""
+        return self._sample(False, **kw)
+
+    def evaluate_sdf(self, **kw):
+        return self._sample(True, **kw)
+
+
 def scene_kwargs(sc):
     """Keyword arguments of Oracle.forward for a scenes.Scene."""
     return dict(bg=sc.bg, means3D=sc.means3D, opacities=sc.opacities, scales=sc.scales, rotations=sc.rotations,
