@@ -409,6 +409,10 @@ def main():
                 acc[k] = acc.get(k, 0.0) + float(v)
             reps += 1
         stages = {k[:-3]: acc[k] / reps for k in acc if k.endswith("_ms")}
+        # the depth pre-sort of the Gaussians and the tile-bit passes over the pairs together replace the
+        # reference's SortPairs: one "sort" stage
+        stages["pair_sort"] = stages["sort"]
+        stages["sort"] = stages["sort"] + stages.pop("depth_order", 0.0)
         sort_passes_run = int(t["sort_passes"])
         _abi.profile_enable(False)
     else:
@@ -468,11 +472,13 @@ def main():
         outs, inter = H.ours_forward_raw(sc, str(device))
         stats = {"P": sc.P, "visible": int((outs["radii"] > 0).sum()), "num_rendered": inter["num_rendered"],
                  "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
-        # launches of OUR kernels per step: preprocess, scan, duplicate, histogram, offsets, the onesweep passes
-        # actually run (5 of the 6 eight-bit digits when the depth keys allow the compact plan), ranges, render fwd,
-        # render bwd, per-Gaussian bwd
+        # launches of OUR kernels per step: preprocess, depth pre-sort (histogram, offsets, 4 onesweep passes), scan,
+        # duplicate, pair sort (histogram, offsets, one onesweep pass per 8 tile bits), ranges, render fwd, render bwd,
+        # per-Gaussian bwd
         stats["sort_passes_run"] = sort_passes_run
-        line["gpu_launches"] = args.steps * (3 + 2 + sort_passes_run + 1 + 1 + 2)
+        stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + 8 * stats["num_rendered"] \
+            + sort_passes_run * 24 * stats["num_rendered"]
+        line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 2 + sort_passes_run + 1 + 1 + 2)
         alg = algorithmic(stats)
         per_stage = {}
         for k, b in alg.items():

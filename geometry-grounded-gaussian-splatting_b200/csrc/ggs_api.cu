@@ -36,7 +36,7 @@ int fail(int code, const std::string& msg) {
     } while (0)
 
 // ---- optional per-stage device timing (ggs_profile_enable / ggs_profile_read) -------------------
-enum { EV_F0, EV_PRE, EV_SCAN, EV_DUP0, EV_DUP, EV_SORT, EV_RANGES, EV_RENDER, EV_B0, EV_RBWD, EV_GBWD, EV_COUNT };
+enum { EV_F0, EV_PRE, EV_ORDER, EV_SCAN, EV_DUP0, EV_DUP, EV_SORT, EV_RANGES, EV_RENDER, EV_B0, EV_RBWD, EV_GBWD, EV_COUNT };
 struct Profiler {
     bool on = false;
     bool have_fwd = false, have_bwd = false;
@@ -129,12 +129,22 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     prof_mark(stream, EV_F0);
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
                       at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
-                      at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.total) + 1, stream);
+                      at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.total) + 1,
+                      at<uint64_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_vals_a), stream);
     GGS_STAGE("preprocess", debug, stream);
     prof_mark(stream, EV_PRE);
+    // Depth pre-sort of the P Gaussians (4 passes over 12 B x P) so that the D pairs only need the tile passes.
+    // ORDER_PASSES is even: the order lands back in order_vals_a.
+    launch_radix_sort(at<uint64_t>(geom, GL.order_keys_a), at<uint64_t>(geom, GL.order_keys_b),
+                      at<uint32_t>(geom, GL.order_vals_a), at<uint32_t>(geom, GL.order_vals_b), (uint32_t)fp.P,
+                      plain_sort_plan(0, 32), at<uint32_t>(geom, GL.order_hist), at<uint32_t>(geom, GL.order_status),
+                      GL.order_status_bytes, at<uint32_t>(geom, GL.order_counters), stream);
+    GGS_STAGE("depth_order", debug, stream);
+    prof_mark(stream, EV_ORDER);
+    const uint32_t* order = at<uint32_t>(geom, GL.order_vals_a);
     launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
                 at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter),
-                at<uint32_t>(geom, GL.total), stream);
+                at<uint32_t>(geom, GL.total), stream, order);
     GGS_STAGE("scan", debug, stream);
     prof_mark(stream, EV_SCAN);
     // one small read-back where the reference blocks too (rasterizer_impl.cu:384): D and the depth-key range
@@ -149,11 +159,14 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
 
     const int tiles = fp.gx * fp.gy;
     const int end_bit = sort_end_bit(tiles);
-    const BinLayout BL = bin_layout(D, sort_passes(0, end_bit), tiles);
+    const BinLayout BL = bin_layout(D, sort_passes(32, end_bit), tiles);
     void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
     if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
     *bin = b;
-    const SortPlan plan = rasterizer_sort_plan(end_bit, depth_min_bits, depth_max_bits);
+    (void)depth_min_bits;
+    (void)depth_max_bits;
+    // the pairs are emitted in depth order: only the tile bits [32, end_bit) are left to sort (stable)
+    const SortPlan plan = plain_sort_plan(32, end_bit);
     // the sorted pairs always end up in keys_a / vals_a: with an odd number of passes the unsorted pairs start in *_b
     const bool odd = plan.passes & 1;
     g_prof.sort_passes = plan.passes;
@@ -162,12 +175,13 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     uint32_t* v_in = at<uint32_t>(b, odd ? BL.vals_b : BL.vals_a);
     uint32_t* v_other = at<uint32_t>(b, odd ? BL.vals_a : BL.vals_b);
     prof_mark(stream, EV_DUP0);
-    launch_duplicate_keys(fp.P, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
+    launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
                           at<float>(geom, GL.depths), fp.gx, k_in, v_in, D, stream);
     GGS_STAGE("duplicate_keys", debug, stream);
     prof_mark(stream, EV_DUP);
     launch_radix_sort(k_in, k_other, v_in, v_other, D, plan, at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status),
-                      BL.status_bytes, at<uint32_t>(b, BL.counters), stream);
+                      (size_t)plan.passes * ((D + SORT_TILE - 1) / SORT_TILE) * RADIX * 4, at<uint32_t>(b, BL.counters),
+                      stream);
     GGS_STAGE("radix_sort", debug, stream);
     prof_mark(stream, EV_SORT);
     const uint64_t* sorted_keys = at<uint64_t>(b, BL.keys_a);
@@ -178,18 +192,18 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
 }
 
 const uint32_t* sorted_list(void* bin, int64_t D, int tiles) {
-    const int passes = sort_passes(0, sort_end_bit(tiles));
+    const int passes = sort_passes(32, sort_end_bit(tiles));
     const BinLayout BL = bin_layout((size_t)D, passes, tiles);
     return at<uint32_t>(bin, BL.vals_a);  // bin_gaussians arranges the ping-pong so that the result lands here
 }
 
 uint32_t* accept_mask(void* bin, int64_t D, int tiles) {
-    const BinLayout BL = bin_layout((size_t)D, sort_passes(0, sort_end_bit(tiles)), tiles);
+    const BinLayout BL = bin_layout((size_t)D, sort_passes(32, sort_end_bit(tiles)), tiles);
     return at<uint32_t>(bin, BL.accept_mask);
 }
 
 uint32_t* near_mask(void* bin, int64_t D, int tiles) {
-    const BinLayout BL = bin_layout((size_t)D, sort_passes(0, sort_end_bit(tiles)), tiles);
+    const BinLayout BL = bin_layout((size_t)D, sort_passes(32, sort_end_bit(tiles)), tiles);
     return at<uint32_t>(bin, BL.near_mask);
 }
 
@@ -494,7 +508,8 @@ int ggs_profile_read(GgsStageTimes* t) {
     int rc = GGS_OK;
     if (g_prof.have_fwd) {
         if ((rc = span(EV_F0, EV_PRE, &t->preprocess_ms))) return rc;
-        if ((rc = span(EV_PRE, EV_SCAN, &t->scan_ms))) return rc;
+        if ((rc = span(EV_PRE, EV_ORDER, &t->depth_order_ms))) return rc;
+        if ((rc = span(EV_ORDER, EV_SCAN, &t->scan_ms))) return rc;
         if ((rc = span(EV_DUP0, EV_DUP, &t->duplicate_ms))) return rc;
         if ((rc = span(EV_DUP, EV_SORT, &t->sort_ms))) return rc;
         if ((rc = span(EV_SORT, EV_RANGES, &t->ranges_ms))) return rc;
@@ -535,8 +550,9 @@ int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_re
     L->point_offsets = GL.point_offsets;
     L->clamped = GL.clamped;
     L->rects = GL.rects;
+    L->depth_order = GL.order_vals_a;
     const int end_bit = sort_end_bit(tiles);
-    const int passes = sort_passes(0, end_bit);
+    const int passes = sort_passes(32, end_bit);
     const BinLayout BL = bin_layout((size_t)num_rendered, passes, tiles);
     L->binning_bytes = BL.bytes;
     const bool in_b = false;  // the ping-pong is arranged so that the sorted pairs land in keys_a / vals_a

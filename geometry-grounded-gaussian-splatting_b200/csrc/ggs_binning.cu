@@ -22,7 +22,9 @@ __device__ __forceinline__ void st_relaxed(uint64_t* p, uint64_t v) {
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+template <bool GATHER>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __restrict__ in,
+                                                            const uint32_t* __restrict__ order,
                                                             uint32_t* __restrict__ out, int n,
                                                             uint64_t* __restrict__ status,
                                                             uint32_t* __restrict__ counter,
@@ -36,14 +38,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __re
     const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
 
     uint32_t v[SCAN_ITEMS];
+    const uint32_t* src = GATHER ? order : in;
     if (base + SCAN_ITEMS <= n) {
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
-        const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(src + base));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(src + base) + 1);
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
         v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
     } else {
 #pragma unroll
-        for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? __ldg(in + base + i) : 0u;
+        for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? __ldg(src + base + i) : 0u;
+    }
+    if constexpr (GATHER) {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? __ldg(in + v[i]) : 0u;
     }
     uint32_t sum = 0;
 #pragma unroll
@@ -106,36 +113,52 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __re
 }
 
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
-                 cudaStream_t stream) {
+                 cudaStream_t stream, const uint32_t* order) {
     const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     cudaMemsetAsync(status, 0, (size_t)(tiles + 1) * 8, stream);
     cudaMemsetAsync(counter, 0, 4, stream);
     cudaMemsetAsync(total, 0, 4, stream);
     if (n == 0) return;
-    scan_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(in, out, n, status, counter, total);
+    if (order)
+        scan_kernel<true><<<tiles, SCAN_THREADS, 0, stream>>>(in, order, out, n, status, counter, total);
+    else
+        scan_kernel<false><<<tiles, SCAN_THREADS, 0, stream>>>(in, order, out, n, status, counter, total);
 }
 
 // ------------------------------------------------------------------------------------------------
-// Key duplication, output-parallel: each block owns 256 consecutive Gaussians and walks the
+// Key duplication, output-parallel: each block owns 256 consecutive Gaussians OF THE DEPTH ORDER and walks the
 // contiguous slice of the key array they expand into; every output slot finds its Gaussian by
 // a binary search over the block's 257 offsets held in shared memory.  Writes are fully
 // coalesced and perfectly balanced (the reference loops over a splat's tiles in one thread).
 // Key = (tile << 32) | f32 bits of depth, value = Gaussian index; slot order inside one
 // Gaussian is y-major then x (rasterizer_impl.cu:96-104).
+// The pairs leave this kernel ordered by (depth, Gaussian index, tile); the stable pair sort on the tile bits alone
+// then yields the reference's order (tile, depth, Gaussian index) -- SortPairs over bits [0, 32 + tile bits) of keys
+// emitted in Gaussian order (rasterizer_impl.cu:406-412) -- without ever moving the pairs for the depth bits.
 // ------------------------------------------------------------------------------------------------
 constexpr int DUP_THREADS = 256;
 
-__global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, const uint32_t* __restrict__ offsets,
+__global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, const uint32_t* __restrict__ order,
+                                                                     const uint32_t* __restrict__ offsets,
                                                                      const uint2* __restrict__ rects,
                                                                      const float* __restrict__ depths, int gx,
                                                                      uint64_t* __restrict__ keys,
                                                                      uint32_t* __restrict__ vals) {
     __shared__ uint32_t s_off[DUP_THREADS + 1];
+    __shared__ uint32_t s_g[DUP_THREADS];
+    __shared__ uint2 s_rect[DUP_THREADS];
+    __shared__ uint32_t s_depth[DUP_THREADS];
     const int g0 = blockIdx.x * DUP_THREADS;
     const int tid = threadIdx.x;
     const int gi = g0 + tid;
     if (tid == 0) s_off[0] = (g0 == 0) ? 0u : __ldg(offsets + g0 - 1);
     s_off[tid + 1] = (gi < P) ? __ldg(offsets + gi) : 0xffffffffu;
+    if (gi < P) {
+        const uint32_t g = __ldg(order + gi);
+        s_g[tid] = g;
+        s_rect[tid] = __ldg(rects + g);  // culled Gaussians own no slots: their (unwritten) rects are never used
+        s_depth[tid] = __float_as_uint(__ldg(depths + g));
+    }
     __syncthreads();
     const uint32_t begin = s_off[0];
     const int last = min(DUP_THREADS, P - g0);
@@ -153,26 +176,26 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
                     hi = mid;
             }
         }
-        const int g = g0 + lo;
         const uint32_t local = o - s_off[lo];
-        const uint2 rc = __ldg(rects + g);
+        const uint2 rc = s_rect[lo];
         const uint32_t minx = rc.x & 0xffffu, miny = rc.x >> 16;
         const uint32_t w = (rc.y & 0xffffu) - minx;
         const uint32_t ty = miny + local / w;
         const uint32_t tx = minx + local % w;
         uint64_t key = (uint64_t)(ty * (uint32_t)gx + tx);
         key <<= 32;
-        key |= (uint64_t)__float_as_uint(__ldg(depths + g));
+        key |= (uint64_t)s_depth[lo];
         keys[o] = key;
-        vals[o] = (uint32_t)g;
+        vals[o] = s_g[lo];
     }
 }
 
-void launch_duplicate_keys(int P, const uint32_t* offsets, const uint2* rects, const float* depths, int gx,
-                           uint64_t* keys, uint32_t* vals, uint32_t D, cudaStream_t stream) {
+void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects,
+                           const float* depths, int gx, uint64_t* keys, uint32_t* vals, uint32_t D,
+                           cudaStream_t stream) {
     if (P == 0 || D == 0) return;
-    duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(P, offsets, rects, depths,
-                                                                                          gx, keys, vals);
+    duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(P, order, offsets, rects,
+                                                                                          depths, gx, keys, vals);
 }
 
 // Points fall into exactly one tile (rasterizer_impl.cu:109-137).

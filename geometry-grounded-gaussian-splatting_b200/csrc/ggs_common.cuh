@@ -75,14 +75,30 @@ struct GeomLayout {
     size_t records;        // SplatRecord[P]
     size_t depths;         // f32[P]
     size_t tiles_touched;  // u32[P]
-    size_t point_offsets;  // u32[P]
+    size_t point_offsets;  // u32[P]: inclusive scan of tiles_touched taken in DEPTH ORDER (see order_vals_a)
     size_t clamped;        // u8[P]  (bit c set when colour channel c was clamped)
     size_t rects;          // uint2[P]: (min.x | min.y<<16, max.x | max.y<<16) tile rectangle
     size_t scan_status;    // u64[scan tiles + 1]
     size_t scan_counter;   // u32
     size_t total;          // u32 D mirror
+    // Depth pre-sort of the Gaussians (stable, by the float bits of the depth; culled Gaussians last): the key
+    // duplication walks the Gaussians in this order, so that the pair sort only has to order the tile bits.
+    size_t order_keys_a, order_keys_b;  // u64[P]  (depth bits in the low word)
+    size_t order_vals_a, order_vals_b;  // u32[P]  (the sorted order lands in order_vals_a)
+    size_t order_hist;                  // u32[MAX_PASSES][RADIX]
+    size_t order_status;                // u32[4][sort tiles][RADIX]
+    size_t order_counters;              // u32[MAX_PASSES]
+    size_t order_status_bytes;
     size_t bytes;
 };
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_PASSES = 8;
+constexpr int ORDER_PASSES = 4;  // 32 depth bits
 
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_THREADS = 256;
@@ -106,16 +122,17 @@ inline GeomLayout geom_layout(size_t P) {
     L.scan_status = take(tiles * 8);
     L.scan_counter = take(256);
     L.total = take(256);
+    L.order_keys_a = take(P * 8);
+    L.order_keys_b = take(P * 8);
+    L.order_vals_a = take(P * 4);
+    L.order_vals_b = take(P * 4);
+    L.order_hist = take(MAX_PASSES * RADIX * 4);
+    L.order_status_bytes = (size_t)ORDER_PASSES * ((P + SORT_TILE - 1) / SORT_TILE) * RADIX * 4;
+    L.order_status = take(L.order_status_bytes);
+    L.order_counters = take(MAX_PASSES * 4);
     L.bytes = o;
     return L;
 }
-
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 12;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int RADIX_BITS = 8;
-constexpr int RADIX = 1 << RADIX_BITS;
-constexpr int MAX_PASSES = 8;
 
 struct BinLayout {
     size_t keys_a, keys_b;  // u64[D]

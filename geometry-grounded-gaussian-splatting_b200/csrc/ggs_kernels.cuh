@@ -31,14 +31,17 @@ struct GaussianInputs {
 // (i.e. ~min); zeroed here.  The host uses them to plan the sort (SortPlan).
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       uint32_t* depth_extremes, cudaStream_t stream);
+                       uint32_t* depth_extremes, uint64_t* order_keys, uint32_t* order_vals, cudaStream_t stream);
 
+// order != null: scans in[order[i]] (the tile counts taken in depth order)
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
-                 cudaStream_t stream);
+                 cudaStream_t stream, const uint32_t* order = nullptr);
 
 // ---- stage 2: key duplication, radix sort, tile ranges ----------------------------------------
-void launch_duplicate_keys(int P, const uint32_t* offsets, const uint2* rects, const float* depths, int gx,
-                           uint64_t* keys, uint32_t* vals, uint32_t D, cudaStream_t stream);
+// order[i] = Gaussian at depth rank i; offsets = inclusive scan of the tile counts in that order
+void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects,
+                           const float* depths, int gx, uint64_t* keys, uint32_t* vals, uint32_t D,
+                           cudaStream_t stream);
 
 // point variant (reference createWithKeys, rasterizer_impl.cu:109-137): key = tile<<32
 void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,

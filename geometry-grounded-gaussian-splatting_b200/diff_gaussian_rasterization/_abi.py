@@ -71,13 +71,13 @@ class GgsLayout(C.Structure):
         "geometry_bytes", "records", "depths", "tiles_touched", "point_offsets", "clamped", "rects",
         "binning_bytes", "sorted_keys", "point_list", "unsorted_keys", "unsorted_list",
         "tile_bytes", "ranges", "max_contributor", "image_bytes", "n_contrib")] + [
-        ("sort_bits", C.c_uint32), ("sort_passes", C.c_uint32)]
+        ("sort_bits", C.c_uint32), ("sort_passes", C.c_uint32), ("depth_order", C.c_uint64)]
 
 
 class GgsStageTimes(C.Structure):
     _fields_ = [("have_forward", C.c_int32), ("have_backward", C.c_int32)] + [(n, C.c_float) for n in (
         "preprocess_ms", "scan_ms", "duplicate_ms", "sort_ms", "ranges_ms", "render_forward_ms",
-        "render_backward_ms", "gaussian_backward_ms")] + [("sort_passes", C.c_int32)]
+        "render_backward_ms", "gaussian_backward_ms")] + [("sort_passes", C.c_int32), ("depth_order_ms", C.c_float)]
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)

@@ -243,7 +243,8 @@ typedef struct GgsStageTimes {
     int32_t have_forward, have_backward;
     float preprocess_ms, scan_ms, duplicate_ms, sort_ms, ranges_ms, render_forward_ms;
     float render_backward_ms, gaussian_backward_ms;
-    int32_t sort_passes; /* radix passes the most recent forward actually ran (5 with the compact digit plan) */
+    int32_t sort_passes; /* radix passes over the (tile, Gaussian) pairs the most recent forward ran */
+    float depth_order_ms; /* depth pre-sort of the Gaussians (between preprocess and scan) */
 } GgsStageTimes;
 GGS_API int ggs_profile_enable(int on);
 GGS_API int ggs_profile_read(GgsStageTimes* times);
@@ -255,6 +256,8 @@ typedef struct GgsLayout {
     uint64_t tile_bytes, ranges, max_contributor;
     uint64_t image_bytes, n_contrib;
     uint32_t sort_bits, sort_passes;
+    uint64_t depth_order; /* u32[P] in the geometry workspace: Gaussian index at each depth rank (culled last);
+                             point_offsets is the inclusive scan of tiles_touched taken in this order */
 } GgsLayout;
 GGS_API int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_rendered, GgsLayout* layout);
 

@@ -122,7 +122,8 @@ def ours_forward_raw(sc, device, require_depth=True):
     inter = dict(
         num_rendered=D,
         tiles_touched=_bytes_view(geom, L.tiles_touched, torch.int32, P).clone(),
-        point_offsets=_bytes_view(geom, L.point_offsets, torch.int32, P).clone(),
+        point_offsets=_bytes_view(geom, L.point_offsets, torch.int32, P).clone(),  # scan in depth order
+        depth_order=_bytes_view(geom, L.depth_order, torch.int32, P).clone(),
         depths=_bytes_view(geom, L.depths, torch.float32, P).clone(),
         clamped=_bytes_view(geom, L.clamped, torch.uint8, P).clone(),
         records=rec.clone(),
@@ -185,6 +186,22 @@ def ref_forward_raw(ref, sc, device, require_depth=True):
                  max_contributor=t["max_contributor"], n_contrib=i["n_contrib"].view(H, W))
     outs = dict(color=color, radii=radii, mdepth=mdepth, alpha=alpha, normal=normal)
     return outs, inter
+
+
+def check_depth_order(it, radii):
+    """Ours only: depth_order is the STABLE ascending order of the visible Gaussians' depth bits (culled ones behind
+    them, any order), and point_offsets is the inclusive scan of tiles_touched taken in that order."""
+    order = it["depth_order"].to(torch.int64)
+    P = order.numel()
+    assert torch.equal(torch.sort(order).values, torch.arange(P, device=order.device)), "not a permutation"
+    vis = radii.to(order.device) > 0
+    V = int(vis.sum())
+    assert bool(vis[order[:V]].all()) and not bool(vis[order[V:]].any()), "culled Gaussians must come last"
+    bits = it["depths"].view(torch.int32).to(torch.int64)[order[:V]]
+    key = bits * P + order[:V]  # stable: ties in depth keep index order
+    assert bool((key[1:] > key[:-1]).all()), "depth order is not the stable sort of the depth bits"
+    tt = it["tiles_touched"].to(torch.int64)[order]
+    assert torch.equal(torch.cumsum(tt, 0).to(torch.int32), it["point_offsets"])
 
 
 # ---- metrics ---------------------------------------------------------------------------------------

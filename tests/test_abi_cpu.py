@@ -43,7 +43,7 @@ def test_layout_query_on_cpu():
     from diff_gaussian_rasterization import _abi
 
     L = _abi.describe_layout(1000, 1237, 822, 12345)
-    assert L.sort_bits == 44 and L.sort_passes == 6          # 4056 tiles -> getHigherMsb = 12
+    assert L.sort_bits == 44 and L.sort_passes == 2          # 4056 tiles -> getHigherMsb = 12; pair passes = tile bits only
     L = _abi.describe_layout(10, 256, 256, 0)
     assert L.sort_bits == 41                                  # 256 tiles -> 9 (NOT ceil(log2))
     L = _abi.describe_layout(10, 800, 600, 5)
