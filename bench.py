@@ -134,6 +134,12 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def _quiet_nccl():
+    """NCCL_DEBUG=VERSION makes NCCL print its version on STDOUT, next to the one JSON line this script owes."""
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -172,6 +178,21 @@ class Step:
         self.flat = None
         # view-parallel runs of our arm: SH gradient summed over views from the all-gathered colour gradients
         self.factored = bool(allreduce) and hasattr(mod, "_SH_FACTORING") and sc.sg_color.shape[1] == 0
+        # ... and all sums through peer memory in one fused launch (PeerGradientExchange) when the node's GPUs can map
+        # each other's memory; GGS_PEER=0 keeps the NCCL collectives (all-gather + bucket all-reduce)
+        self.exchange = None
+        self.exchange_note = "nccl all-gather(dL_drgb) + nccl all-reduce(11 floats/Gaussian)"
+        if self.factored and os.environ.get("GGS_PEER", "1") != "0":
+            try:
+                from diff_gaussian_rasterization.parallel import PeerGradientExchange
+
+                mc = {"0": False, "1": True}.get(os.environ.get("GGS_MULTICAST", ""), None)
+                self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc)
+                self.exchange_note = "fused peer-memory sum (ggs_view_sum_peer, %s)" % (
+                    "NVSwitch multimem" if self.exchange.multicast_ptr else "P2P loads/stores")
+            except Exception as ex:  # noqa: BLE001
+                print(f"[bench] peer exchange unavailable ({type(ex).__name__}: {ex}); using NCCL", file=sys.stderr)
+                self.exchange = None
 
     def _settings(self, cam):
         c = self.sc.cam
@@ -194,12 +215,12 @@ class Step:
         if self.factored:
             from diff_gaussian_rasterization.parallel import factored_sh_gradients
 
-            with factored_sh_gradients():
+            with factored_sh_gradients(exchange=self.exchange):
                 torch.autograd.backward([color, mdepth, alpha, normal],
                                         [g["color"], g["mdepth"], g["alpha"], g["normal"]])
         else:
             torch.autograd.backward([color, mdepth, alpha, normal], [g["color"], g["mdepth"], g["alpha"], g["normal"]])
-        if self.allreduce:
+        if self.allreduce and self.exchange is None:
             # the SH gradient came back already summed over views (factored_sh_gradients: 12 B per Gaussian and view
             # all-gathered instead of 192 B all-reduced); one NCCL all-reduce over the flat bucket of the other
             # parameter gradients (11 floats per Gaussian)
@@ -370,6 +391,7 @@ def main():
     if multi:
         import torch.distributed as dist
 
+        _quiet_nccl()
         dist.init_process_group("nccl", device_id=device)
 
     if args.impl == "ours":
@@ -446,9 +468,8 @@ def main():
         "config": {"workload": f"{args.workload}: {sc.P} Gaussians, {c.W}x{c.H}, SH{sc.sh_degree}, "
                                "require_depth=True, one view per rank",
                    "views_per_step": n_ranks,
-                   "parallelism": (f"view-parallel x{n_ranks}: one view per rank, NCCL all-gather of the per-view colour "
-                                   "gradients (SH gradient rebuilt locally) + all-reduce of the other parameter "
-                                   "gradients, inside the timed region") if multi else "single GPU",
+                   "parallelism": (f"view-parallel x{n_ranks}: one view per rank, parameter gradients summed over views "
+                                   f"inside the timed region: {step.exchange_note}") if multi else "single GPU",
                    "l2": "working set (>700 MB per step) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_value, "unit": "iters/s", "h2d_bytes_per_step": step.h2d_bytes,
                 "d2h_bytes_per_step": step.d2h_bytes},

@@ -284,9 +284,54 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     return D;
 }
 
-int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
-                           const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
-                           void* stream_) {
+}  // extern "C"
+
+namespace {
+
+// side stream + events of the early colour-gradient push (one set per device, created on first use)
+struct PushLane {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ready = nullptr, done = nullptr;
+};
+PushLane* push_lane() {
+    static PushLane lanes[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    PushLane& L = lanes[dev];
+    if (!L.stream) {
+        if (cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        cudaEventCreateWithFlags(&L.ready, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming);
+    }
+    return &L;
+}
+
+int check_exchange(const GgsPeerExchange* px) {
+    if (!px || !px->peer_buffers) return fail(GGS_ERR_INVALID_ARGUMENT, "null peer exchange");
+    if (px->world <= 0 || px->world > MAX_VIEWS || px->rank < 0 || px->rank >= px->world)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad world / rank (at most 16 ranks)");
+    if ((px->send_offset | px->recv_offset | px->reduce_floats | px->rgb_stage_offset | px->rgb_stage_stride |
+         px->reduce_stage_offset | px->reduce_stage_stride | px->campos_stage_offset) & 3)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "exchange offsets must be multiples of 4 floats");
+    for (int r = 0; r < px->world; r++)
+        if (!px->peer_buffers[r] || (px->peer_buffers[r] & 15))
+            return fail(GGS_ERR_INVALID_ARGUMENT, "bad peer buffer");
+    const size_t n4 = (size_t)px->reduce_floats / 4;
+    const size_t longest = (n4 + px->world - 1) / px->world;
+    if ((size_t)px->reduce_stage_stride / 4 < longest)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "reduce stage slots are smaller than a slice");
+    return GGS_OK;
+}
+size_t slice_lo4(const GgsPeerExchange* px, int s) {
+    return (size_t)px->reduce_floats / 4 * (size_t)s / (size_t)px->world;
+}
+float* peer_ptr(const GgsPeerExchange* px, int r, int64_t off) {
+    return reinterpret_cast<float*>(px->peer_buffers[r]) + off;
+}
+
+int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                  const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                  const GgsPeerExchange* px, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FrameParams fp;
     GaussianInputs in;
@@ -299,7 +344,7 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     if (!grads->dL_dmeans3D || !grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity ||
         !grads->dL_dscales || !grads->dL_drotations)
         return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
-    if (in.shs && !grads->dL_dsh && !grads->dL_drgb)
+    if (in.shs && !grads->dL_dsh && !grads->dL_drgb && !px)
         return fail(GGS_ERR_INVALID_ARGUMENT, "dL_dsh (or dL_drgb) required with shs");
     if (in.shs && fp.SGM && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
         return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");
@@ -336,6 +381,27 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     GGS_STAGE("render_backward", debug, stream);
     prof_mark(stream, EV_RBWD);
 
+    PushLane* lane = nullptr;
+    if (px) {
+        // the colour gradient of this view is final here: push it to every rank while the per-Gaussian backward runs
+        lane = push_lane();
+        if (!lane) return fail(GGS_ERR_CUDA, "could not create the push stream");
+        PushTargets t = {};
+        t.world = px->world;
+        for (int r = 0; r < px->world; r++) {
+            t.rgb[r] = peer_ptr(px, r, px->rgb_stage_offset + (int64_t)px->rank * px->rgb_stage_stride);
+            t.campos[r] = peer_ptr(px, r, px->campos_stage_offset + (int64_t)px->rank * 4);
+        }
+        if (px->multicast_base)
+            t.mc_rgb = reinterpret_cast<float*>(px->multicast_base) + px->rgb_stage_offset +
+                       (int64_t)px->rank * px->rgb_stage_stride;
+        GGS_CUDA(cudaEventRecord(lane->ready, stream));
+        GGS_CUDA(cudaStreamWaitEvent(lane->stream, lane->ready, 0));
+        launch_push_rgb(fp.P, acc, at<uint8_t>(state->geometry, GL.clamped), bi->radii, fp.view.campos, t,
+                        lane->stream);
+        GGS_CUDA(cudaEventRecord(lane->done, lane->stream));
+    }
+
     GaussianGrads gg;
     gg.dL_dmeans3D = grads->dL_dmeans3D;
     gg.dL_dmeans2D = grads->dL_dmeans2D;
@@ -353,7 +419,39 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
     GGS_STAGE("gaussian_backward", debug, stream);
     prof_mark(stream, EV_GBWD);
     g_prof.have_bwd = g_prof.on;
+    if (px) {
+        // reduce-scatter by stores: slice s of this rank's gradient region -> slot `rank` of rank s's reduce stage
+        PushSlices ps = {};
+        ps.world = px->world;
+        for (int s = 0; s <= px->world; s++) ps.lo4[s] = slice_lo4(px, s);
+        for (int s = 0; s < px->world; s++)
+            ps.dest[s] = reinterpret_cast<float4*>(
+                peer_ptr(px, s, px->reduce_stage_offset + (int64_t)px->rank * px->reduce_stage_stride));
+        launch_push_slices(reinterpret_cast<const float4*>(peer_ptr(px, px->rank, px->send_offset)), ps, stream);
+        GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
+        GGS_STAGE("peer_push", debug, stream);
+    }
     return GGS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                           const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                           void* stream) {
+    return backward_impl(frame, gaussians, state, bi, alloc, user, grads, nullptr, stream);
+}
+
+int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                                const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                                const GgsPeerExchange* px, void* stream) {
+    const int rc = check_exchange(px);
+    if (rc) return rc;
+    if (!grads || reinterpret_cast<const float*>(grads->dL_drotations) == nullptr)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
+    return backward_impl(frame, gaussians, state, bi, alloc, user, grads, px, stream);
 }
 
 int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
@@ -394,8 +492,9 @@ int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* ga
 
 int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t sh_coeffs, int32_t views, const float* means3D,
                                const float* campos, const float* dL_drgb, float* dL_dsh, void* stream_) {
-    if (count < 0 || count > 0x7fffffffLL || views <= 0) return fail(GGS_ERR_INVALID_ARGUMENT, "bad count / views");
-    if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > sh_coeffs)
+    if (count < 0 || count > 0x7fffffffLL || views <= 0 || views > MAX_VIEWS)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad count / views (at most 16 views)");
+    if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > sh_coeffs || sh_coeffs > 16)
         return fail(GGS_ERR_INVALID_ARGUMENT, "bad sh_degree / sh_coeffs");
     if (count == 0) return GGS_OK;
     if (!means3D || !campos || !dL_drgb || !dL_dsh) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
@@ -489,6 +588,41 @@ int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussian
                      at<float2>(pts, p_xy), at<float>(pts, p_depth), out_transmittance, inside, stream);
     GGS_STAGE("integrate", debug, stream);
     return D;
+}
+
+int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
+                      const GgsPeerExchange* px, float* dL_dsh, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int rc = check_exchange(px);
+    if (rc) return rc;
+    if (count < 0 || count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad count");
+    if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > sh_coeffs || sh_coeffs > 16)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad sh_degree / sh_coeffs");
+    if (count > 0 && (!means3D || !dL_dsh)) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    const int world = px->world, rank = px->rank;
+    ViewSources src = {};
+    PeerJob job = {};
+    job.world = world;
+    job.lo4 = slice_lo4(px, rank);
+    job.hi4 = slice_lo4(px, rank + 1);
+    for (int r = 0; r < world; r++) {
+        // everything this launch READS is local: slot r of this rank's colour / camera / reduce stages
+        src.rgb[r] = peer_ptr(px, rank, px->rgb_stage_offset + (int64_t)r * px->rgb_stage_stride);
+        src.campos[r] = peer_ptr(px, rank, px->campos_stage_offset + (int64_t)r * 4);
+        // indexed by the flat position i of the slice: slot base - lo4
+        job.send[r] = reinterpret_cast<const float4*>(
+                          peer_ptr(px, rank, px->reduce_stage_offset + (int64_t)r * px->reduce_stage_stride)) -
+                      job.lo4;
+        job.recv[r] = reinterpret_cast<float4*>(peer_ptr(px, r, px->recv_offset));
+    }
+    if (px->multicast_base)
+        job.mc_recv = reinterpret_cast<float4*>(reinterpret_cast<float*>(px->multicast_base) + px->recv_offset);
+    const size_t per_block = 256;
+    const size_t want = (job.hi4 - job.lo4 + per_block - 1) / per_block;
+    job.blocks = (int)(want < (size_t)(148 * 4) ? want : (size_t)(148 * 4));
+    launch_view_sum_peer((int)count, sh_degree, sh_coeffs, means3D, src, dL_dsh, job, stream);
+    GGS_STAGE("view_sum_peer", false, stream);
+    return GGS_OK;
 }
 
 int ggs_profile_enable(int on) {

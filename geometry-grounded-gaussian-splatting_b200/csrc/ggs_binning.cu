@@ -74,29 +74,36 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __re
         if (w < warp) warp_off += s_warp[w];
     const uint32_t thread_excl = warp_off + incl - sum;
 
-    if (threadIdx.x == SCAN_THREADS - 1) {
-        const uint32_t aggregate = warp_off + incl;
+    // look-back by the last warp: 32 predecessors per round (one per lane), consumed in order up to the first
+    // inclusive prefix; a serial walk costs ~sqrt(2 x tiles) dependent L2 round trips when a wave starts together
+    if (warp == SCAN_THREADS / 32 - 1) {
+        const uint32_t aggregate = __shfl_sync(0xffffffffu, warp_off + incl, 31);
         uint32_t prefix = 0;
         if (tile == 0) {
-            st_relaxed(status, ST_PREFIX | aggregate);
+            if (lane == 31) st_relaxed(status, ST_PREFIX | aggregate);
         } else {
-            st_relaxed(status + tile, ST_AGG | aggregate);
+            if (lane == 31) st_relaxed(status + tile, ST_AGG | aggregate);
             int look = (int)tile - 1;
             while (true) {
-                const uint64_t d = ld_relaxed(status + look);
-                if (d & ST_PREFIX) {
-                    prefix += (uint32_t)d;
-                    break;
-                }
-                if (d & ST_AGG) {
-                    prefix += (uint32_t)d;
-                    look--;
-                }
+                const int at = look - lane;
+                const uint64_t d = at >= 0 ? ld_relaxed(status + at) : ST_PREFIX;  // before tile 0: prefix 0
+                const uint32_t is_prefix = __ballot_sync(0xffffffffu, (d & ST_PREFIX) != 0);
+                const uint32_t is_invalid = __ballot_sync(0xffffffffu, (d & (ST_PREFIX | ST_AGG)) == 0);
+                const int first_prefix = is_prefix ? __ffs(is_prefix) - 1 : 32;
+                const int first_invalid = is_invalid ? __ffs(is_invalid) - 1 : 32;
+                // usable lanes: [0, take) plus the prefix lane itself when it comes before any invalid word
+                const bool done = first_prefix < first_invalid;
+                const int take = done ? first_prefix + 1 : first_invalid;
+                prefix += __reduce_add_sync(0xffffffffu, lane < take ? (uint32_t)d : 0u);
+                if (done) break;
+                look -= take;
             }
-            st_relaxed(status + tile, ST_PREFIX | (uint64_t)(prefix + aggregate));
+            if (lane == 31) st_relaxed(status + tile, ST_PREFIX | (uint64_t)(prefix + aggregate));
         }
-        s_prefix = prefix;
-        if ((int)(tile + 1) * SCAN_TILE >= n) *total = prefix + aggregate;
+        if (lane == 31) {
+            s_prefix = prefix;
+            if ((int)(tile + 1) * SCAN_TILE >= n) *total = prefix + aggregate;
+        }
     }
     __syncthreads();
     const uint32_t off = s_prefix + thread_excl;

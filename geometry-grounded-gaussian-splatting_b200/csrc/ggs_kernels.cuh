@@ -136,8 +136,43 @@ void launch_integrate(int tiles, uint32_t max_blocks, const uint32_t* tile_offse
                       float* out_transmittance, uint8_t* inside, cudaStream_t stream);
 
 // View-parallel training: dL_dsh[p][k][c] = sum_v basis_k(dir(p, campos[v])) * dL_drgb[v][p][c]  (ggs_multiview.cu)
+constexpr int MAX_VIEWS = 16;
+struct ViewSources {  // where each view's masked colour gradient [P,3] and camera position [3] live
+    const float* rgb[MAX_VIEWS];
+    const float* campos[MAX_VIEWS];
+};
 void launch_sh_gradient_from_views(int P, int SHD, int SHM, int V, const float* means3D, const float* campos,
                                    const float* dL_drgb, float* dL_dsh, cudaStream_t stream);
+
+// Fused form over peer memory (one launch): the first `blocks` blocks sum this rank's slice [lo4, hi4) (float4
+// units) of the flat gradient region over all ranks and store it into every rank's result region; the others form
+// the SH gradient from the peers' colour gradients.  mc_*: NVSwitch multicast addresses of the same regions, or null.
+struct PeerJob {
+    int blocks, world;
+    size_t lo4, hi4;
+    const float4* send[MAX_VIEWS];
+    float4* recv[MAX_VIEWS];
+    const float4* mc_send;
+    float4* mc_recv;
+};
+void launch_view_sum_peer(int P, int SHD, int SHM, const float* means3D, const ViewSources& src, float* dL_dsh,
+                          const PeerJob& job, cudaStream_t stream);
+
+// Push half of the exchange (ggs_peer.cu): every byte crosses the link as a posted store.
+struct PushTargets {  // slot `rank` of every rank's colour stage / camera stage, as this process maps them
+    int world;
+    float* rgb[MAX_VIEWS];
+    float* campos[MAX_VIEWS];
+    float* mc_rgb;  // multicast address of slot `rank` of the colour stage, or null
+};
+struct PushSlices {  // dest[s] = slot `rank` of rank s's reduce stage; slice s = float4 units [lo4[s], lo4[s+1])
+    int world;
+    size_t lo4[MAX_VIEWS + 1];
+    float4* dest[MAX_VIEWS];
+};
+void launch_push_rgb(int P, const double* grad_acc, const uint8_t* clamped, const int* radii, const float* campos,
+                     const PushTargets& t, cudaStream_t stream);
+void launch_push_slices(const float4* send, const PushSlices& t, cudaStream_t stream);
 
 // ---- sampled median depth (sample_depth), ggs_sample_depth.cu ---------------------------------------------------
 void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,

@@ -16,6 +16,7 @@ namespace ggs {
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_PREFIX = 2u << 30;
 constexpr uint32_t VALUE_MASK = (1u << 30) - 1;
+constexpr int LOOK_WINDOW = 8;
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
     uint32_t v;
@@ -239,20 +240,37 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     const uint32_t bin_start = off + incl - cnt;
     s_bin_start[d] = bin_start;
 
-    // ---- decoupled look-back: one thread per digit ----------------------------------------------
+    // ---- decoupled look-back: one thread per digit, LOOK_WINDOW predecessors in flight per round ------------
+    // When the tiles of a wave publish their aggregates at about the same time, a walk that reads one predecessor
+    // per L2 round trip needs ~sqrt(2 x tiles) dependent loads (measured: 23 us of a pass over 326 tiles).  The
+    // window issues its loads together and consumes them in order; it stops at the first word not yet published.
     uint32_t excl = 0;
     if (tile > 0) {
         int look = (int)tile - 1;
-        while (true) {
-            const uint32_t st = ld_relaxed_u32(status + (size_t)look * RADIX + d);
-            if (st & FLAG_PREFIX) {
-                excl += st & VALUE_MASK;
-                break;
+        bool found = false;
+        while (!found) {
+            uint32_t st[LOOK_WINDOW];
+#pragma unroll
+            for (int j = 0; j < LOOK_WINDOW; j++)
+                st[j] = (look - j >= 0) ? ld_relaxed_u32(status + (size_t)(look - j) * RADIX + d) : FLAG_PREFIX;
+            bool stop = false;
+            int adv = 0;
+#pragma unroll
+            for (int j = 0; j < LOOK_WINDOW; j++) {
+                if (!stop) {
+                    if (st[j] & FLAG_PREFIX) {
+                        excl += st[j] & VALUE_MASK;
+                        found = true;
+                        stop = true;
+                    } else if (st[j] & FLAG_AGG) {
+                        excl += st[j] & VALUE_MASK;
+                        adv++;
+                    } else {
+                        stop = true;
+                    }
+                }
             }
-            if (st & FLAG_AGG) {
-                excl += st & VALUE_MASK;
-                look--;
-            }
+            look -= adv;
         }
         st_relaxed_u32(my_status, FLAG_PREFIX | (excl + cnt));
     }

@@ -51,7 +51,8 @@ class GaussianRasterizationSettings(NamedTuple):
 # View-parallel training (parallel.factored_sh_gradients): when set, the backward does not write the per-view SH
 # gradient; it all-gathers the 3-float masked colour gradient of every view and forms the SUM over views locally
 # (ggs_sh_gradient_from_views).  Process-wide on purpose: autograd runs the backward on its own thread.
-_SH_FACTORING = {"on": False, "group": None}
+# "exchange": a parallel.PeerGradientExchange -- the sums then go through peer memory in one fused launch instead of NCCL.
+_SH_FACTORING = {"on": False, "group": None, "exchange": None}
 
 
 def _dev_f32(t, device):
@@ -229,15 +230,22 @@ class _RasterizeGaussians(torch.autograd.Function):
         opts = dict(dtype=torch.float32, device=device)
         SHM = sh_.shape[1] if sh_ is not None else 0
         SGM = sgc.shape[1] if (sgc is not None and sa is not None and ss is not None) else 0
-        d_means3D = torch.empty(P, 3, **opts)
+        factored = bool(_SH_FACTORING["on"]) and sh_ is not None and SGM == 0
+        exchange = _SH_FACTORING["exchange"] if factored else None
         d_means2D = torch.empty(P, 3, **opts)
         d_colors = torch.empty(P, 3, **opts)
-        d_opacity = torch.empty(P, 1, **opts)
-        d_scales = torch.empty(P, 3, **opts)
-        d_rot = torch.empty(P, 4, **opts)
-        factored = bool(_SH_FACTORING["on"]) and sh_ is not None and SGM == 0
+        if exchange is not None:
+            # the per-Gaussian backward writes straight into this rank's region of the peer-mapped exchange buffer
+            exchange.check(P, device)
+            d_means3D, d_opacity, d_scales, d_rot = exchange.send_views()
+            d_rgb = None
+        else:
+            d_means3D = torch.empty(P, 3, **opts)
+            d_opacity = torch.empty(P, 1, **opts)
+            d_scales = torch.empty(P, 3, **opts)
+            d_rot = torch.empty(P, 4, **opts)
+            d_rgb = torch.empty(P, 3, **opts) if factored else None
         d_sh = None if factored else torch.empty(P, SHM, 3, **opts)
-        d_rgb = torch.empty(P, 3, **opts) if factored else None
         d_sg_axis = torch.empty(P, SGM, 3, **opts)
         d_sg_sharp = torch.empty(P, SGM, **opts)
         d_sg_color = torch.empty(P, SGM, 3, **opts)
@@ -254,14 +262,22 @@ class _RasterizeGaussians(torch.autograd.Function):
                                       _abi.ptr(d_opacity), _abi.ptr(d_scales), _abi.ptr(d_rot), _abi.ptr(d_sh),
                                       _abi.ptr(d_sg_axis), _abi.ptr(d_sg_sharp), _abi.ptr(d_sg_color), _abi.ptr(d_rgb))
             arena = _abi.Arena(device)
-            rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn, None,
-                                             C.byref(grads), _abi.stream_handle(device))
+            if exchange is not None:
+                rc = _lib.ggs_rasterize_backward_peer(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn,
+                                                      None, C.byref(grads), C.byref(exchange.px),
+                                                      _abi.stream_handle(device))
+            else:
+                rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn,
+                                                 None, C.byref(grads), _abi.stream_handle(device))
             arena.done()
             if rc < 0:
                 if arena.error is not None:
                     raise arena.error
                 _abi.check(rc, "ggs_rasterize_backward")
-            if factored:
+            if exchange is not None:
+                # sums over the views of all ranks, one fused launch over peer memory (parallel.PeerGradientExchange)
+                d_means3D, d_opacity, d_scales, d_rot, d_sh = exchange.sum_over_views(rs, m3, SHM)
+            elif factored:
                 d_sh = _sum_sh_gradient_over_views(rs, m3, d_rgb, SHM, device)
         had_sh, had_sa, had_ss, had_sgc, had_cp = ctx.had
         if SGM == 0:

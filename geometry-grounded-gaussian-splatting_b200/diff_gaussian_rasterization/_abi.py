@@ -66,6 +66,13 @@ class GgsGradients(C.Structure):
                 ("dL_dsg_sharpness", _f32p), ("dL_dsg_color", _f32p), ("dL_drgb", _f32p)]
 
 
+class GgsPeerExchange(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("peer_buffers", C.POINTER(C.c_uint64)),
+                ("multicast_base", C.c_uint64)] + [(n, C.c_int64) for n in (
+        "send_offset", "recv_offset", "reduce_floats", "rgb_stage_offset", "rgb_stage_stride",
+        "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")]
+
+
 class GgsLayout(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "geometry_bytes", "records", "depths", "tiles_touched", "point_offsets", "clamped", "rects",
@@ -86,7 +93,8 @@ EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_ra
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
-           "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read")
+           "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
+           "ggs_rasterize_backward_peer")
 
 
 def _load():
@@ -136,6 +144,12 @@ def _load():
                                    C.c_void_p, C.c_void_p]
     lib.ggs_profile_enable.restype = C.c_int
     lib.ggs_profile_enable.argtypes = [C.c_int]
+    lib.ggs_view_sum_peer.restype = C.c_int
+    lib.ggs_view_sum_peer.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(GgsPeerExchange),
+                                      C.c_void_p, C.c_void_p]
+    lib.ggs_rasterize_backward_peer.restype = C.c_int
+    lib.ggs_rasterize_backward_peer.argtypes = list(lib.ggs_rasterize_backward.argtypes[:-1]) + [
+        C.POINTER(GgsPeerExchange), C.c_void_p]
     lib.ggs_profile_read.restype = C.c_int
     lib.ggs_profile_read.argtypes = [C.POINTER(GgsStageTimes)]
     if lib.ggs_abi_version() != 1:

@@ -19,19 +19,128 @@ import torch.distributed as dist
 
 
 @contextlib.contextmanager
-def factored_sh_gradients(group=None):
+def factored_sh_gradients(group=None, exchange=None):
     """Inside this context the rasterizer's backward returns the SH-coefficient gradient already SUMMED over the
     views of all ranks of `group`: instead of all-reducing [P, SHM, 3] (81 % of the parameter-gradient bytes at SH3)
     every rank all-gathers the 3-float colour gradient per Gaussian and view and rebuilds the rank-one per-view SH
-    gradients locally.  Reduce the remaining parameters with `GradientBucket` as usual and leave `shs` out of it."""
+    gradients locally.  Reduce the remaining parameters with `GradientBucket` as usual and leave `shs` out of it.
+
+    With `exchange` (a `PeerGradientExchange`) nothing is left to reduce: the backward returns EVERY parameter
+    gradient summed over the views, formed by one fused launch over peer memory (no NCCL call on the data path)."""
     from . import _SH_FACTORING
 
     prev = dict(_SH_FACTORING)
-    _SH_FACTORING.update(on=True, group=group)
+    _SH_FACTORING.update(on=True, group=group, exchange=exchange)
     try:
         yield
     finally:
         _SH_FACTORING.update(prev)
+
+
+def exchange_layout(P: int, world: int) -> dict:
+    """Float offsets of the regions of a `PeerGradientExchange` buffer (`GgsPeerExchange` in the C ABI).  Every
+    region starts on a 256-byte boundary; rotations come first because their rows are stored as float4."""
+    pad = lambda n: (int(n) + 63) // 64 * 64  # noqa: E731
+    L, o = {}, 0
+    for name, width in (("rotations", 4), ("means3D", 3), ("scales", 3), ("opacities", 1)):
+        L[name] = (o, width)
+        o += pad(width * P)
+    L["send"], L["reduce"] = 0, o
+    L["recv"] = o
+    o += L["reduce"]
+    L["rgb_stage"], L["rgb_stride"] = o, pad(3 * P)
+    o += world * L["rgb_stride"]
+    L["campos_stage"] = o
+    o += pad(4 * world)
+    L["reduce_stride"] = pad((L["reduce"] // 4 + world - 1) // world * 4)
+    L["reduce_stage"] = o
+    o += world * L["reduce_stride"]
+    L["total"] = o
+    return L
+
+
+class PeerGradientExchange:
+    """View-parallel gradient sums through peer memory (NVLink / NVSwitch) instead of NCCL collectives.
+
+    Every rank allocates one symmetric buffer (`torch.distributed._symmetric_memory`: cuMem allocations whose handles
+    are exchanged once, here) laid out by `exchange_layout`.  Per step, inside the rasterizer's backward:
+      1. `ggs_rasterize_backward_peer`: the per-Gaussian backward writes this rank's gradients of means3D / opacities /
+         scales / rotations straight into the buffer; the masked colour gradient of the view is pushed into every
+         rank's colour stage while that kernel still runs, and each 1/world slice of the gradient region is pushed to
+         the rank that owns it -- all posted stores, one multimem.st per 16 bytes where the switch can replicate;
+      2. node barrier; `ggs_view_sum_peer` (all reads local): sums the slots of this rank's slice and stores the sum
+         into every rank's result region, and forms the SH gradient summed over views from the staged colour
+         gradients; node barrier.
+    Wire bytes received per rank and step: 12 B x P x (world - 1) colour gradients + 2 x 44 B x P x (world - 1) / world."""
+
+    def __init__(self, P: int, device, group=None, multicast: bool | None = None):
+        import ctypes as C
+
+        import torch.distributed._symmetric_memory as symm
+
+        from . import _abi
+
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("PeerGradientExchange needs an initialised process group")
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        if self.world > 16:
+            raise RuntimeError("at most 16 ranks (one node)")
+        self.P, self.device = int(P), torch.device(device)
+        L = self.layout = exchange_layout(self.P, self.world)
+        self.buf = symm.empty(L["total"], dtype=torch.float32, device=self.device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(ptrs) != self.world or any(p == 0 for p in ptrs):
+            raise RuntimeError("symmetric-memory rendezvous returned no peer pointers")
+        self._ptrs = (C.c_uint64 * self.world)(*ptrs)
+        mc = 0
+        try:
+            if (multicast is None or multicast) and self.hdl.has_multicast_support:
+                mc = int(self.hdl.multicast_ptr)
+        except Exception:  # noqa: BLE001  (no multicast attributes)
+            mc = 0
+        if multicast and not mc:
+            raise RuntimeError("no NVSwitch multicast mapping for the exchange buffer")
+        self.multicast_ptr = mc
+        self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
+                                       L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
+                                       L["reduce_stage"], L["reduce_stride"])
+        torch.cuda.synchronize(self.device)
+        self.hdl.barrier(channel=0)
+
+    def check(self, P, device):
+        if int(P) != self.P or torch.device(device) != self.device:
+            raise RuntimeError("PeerGradientExchange was built for another Gaussian count / device")
+
+    def _view(self, base, name):
+        o, w = self.layout[name]
+        return self.buf[base + o:base + o + w * self.P].view(self.P, w)
+
+    def send_views(self):
+        """(d_means3D, d_opacity, d_scales, d_rotations) of THIS rank's view, inside the exchange buffer."""
+        s = self.layout["send"]
+        return (self._view(s, "means3D"), self._view(s, "opacities"), self._view(s, "scales"),
+                self._view(s, "rotations"))
+
+    def sum_over_views(self, rs, means3D, SHM):
+        """Call after `ggs_rasterize_backward_peer` has been enqueued on the current stream.  Returns the gradients of
+        (means3D, opacities, scales, rotations, shs) summed over the views of all ranks; the first four are views
+        into the exchange buffer, valid until the next backward."""
+        import ctypes as C
+
+        from . import _abi
+
+        d_sh = torch.empty(self.P, SHM, 3, dtype=torch.float32, device=self.device)
+        self.hdl.barrier(channel=0)  # every rank's pushes have landed
+        _abi.check(_abi.lib.ggs_view_sum_peer(self.P, int(rs.sh_degree), int(SHM), _abi.ptr(means3D),
+                                              C.byref(self.px), _abi.ptr(d_sh), _abi.stream_handle(self.device)),
+                   "ggs_view_sum_peer")
+        self.hdl.barrier(channel=1)  # every rank's result region is complete; the stages may be overwritten
+        r = self.layout["recv"]
+        return (self._view(r, "means3D"), self._view(r, "opacities"), self._view(r, "scales"),
+                self._view(r, "rotations"), d_sh)
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:

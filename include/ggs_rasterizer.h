@@ -234,6 +234,42 @@ GGS_API int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians*
 GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
 
+/* ---- view-parallel training over peer memory (NVLink / NVSwitch): no NCCL call on the data path --------------
+ * Every rank of the node owns an exchange buffer of identical layout that all ranks have mapped
+ * (peer_buffers[r] = rank r's buffer as THIS process sees it: torch symmetric memory, or cudaIpcOpenMemHandle).
+ * All offsets are in floats from the buffer's base and multiples of 4:
+ *   [send_offset, +reduce_floats)      this rank's per-view gradients of the non-SH parameters: point
+ *                                      GgsGradients.{dL_drotations, dL_dmeans3D, dL_dscales, dL_dopacity} into it
+ *   rgb_stage_offset + r*rgb_stage_stride       slot r: rank r's masked colour gradient dL/dRGB [count,3]
+ *   campos_stage_offset + r*4                   slot r: rank r's camera position
+ *   reduce_stage_offset + r*reduce_stage_stride slot r: rank r's copy of THIS rank's 1/world slice of the region
+ *   [recv_offset, +reduce_floats)      receives the sum over ranks of the region
+ * multicast_base: address of an NVSwitch multicast mapping of the same buffers (0 if none); broadcasts then take one
+ * multimem.st instead of `world` peer stores.
+ *
+ * ggs_rasterize_backward_peer = ggs_rasterize_backward + the PUSH half: this rank's dL/dRGB goes to slot `rank` of
+ * every rank's colour stage as soon as the tile backward is done (side stream, concurrent with the per-Gaussian
+ * backward), and slice s of the send region goes to slot `rank` of rank s's reduce stage (a reduce-scatter by posted
+ * stores; pulling operands from a peer is bound by NVLink round trips).  GgsGradients.dL_dsh and dL_drgb may be NULL.
+ * Then, after a node barrier on the stream, ggs_view_sum_peer sums the slots of this rank's slice, stores the sum into
+ * every rank's recv region and writes dL_dsh = sum over ranks of the rank-one SH gradients (as
+ * ggs_sh_gradient_from_views) -- all reads local; after a second barrier the recv region holds the gradients summed
+ * over all views.  The reference has no counterpart (no distributed code). */
+typedef struct GgsPeerExchange {
+    int32_t world, rank;
+    const uint64_t* peer_buffers; /* [world], host array */
+    uint64_t multicast_base;
+    int64_t send_offset, recv_offset, reduce_floats;
+    int64_t rgb_stage_offset, rgb_stage_stride;
+    int64_t campos_stage_offset;
+    int64_t reduce_stage_offset, reduce_stage_stride;
+} GgsPeerExchange;
+GGS_API int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussians* gaussians,
+                                const GgsForwardState* state, const GgsBackwardInputs* inputs, GgsAllocFn alloc,
+                                void* user, const GgsGradients* grads, const GgsPeerExchange* exchange, void* stream);
+GGS_API int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
+                      const GgsPeerExchange* exchange, float* dL_dsh, void* stream);
+
 /* ---- optional per-stage device timing ------------------------------------------------------------
  * When enabled (process-wide) the forward / backward record CUDA events on the caller's stream
  * between stages; ggs_profile_read waits for the events of the most recent forward and backward and
