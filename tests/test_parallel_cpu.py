@@ -101,3 +101,35 @@ def test_single_process_paths_need_no_group():
     b = parallel.GradientBucket([p])
     b.allreduce()
     assert torch.equal(p.grad, torch.ones(4))
+
+
+def test_exchange_layout_regions_are_disjoint_and_aligned():
+    """Layout of the peer-memory exchange buffer (GgsPeerExchange): 256-byte aligned regions that do not overlap,
+    reduce-stage slots large enough for the longest 1/world slice."""
+    from diff_gaussian_rasterization.parallel import exchange_layout
+
+    for P in (1, 10, 1000, 200_003, 1_000_000):
+        for world in (1, 2, 3, 8, 16):
+            L = exchange_layout(P, world)
+            spans = []
+            for name, width in (("rotations", 4), ("means3D", 3), ("scales", 3), ("opacities", 1)):
+                o, w = L[name]
+                assert w == width and o % 64 == 0
+                spans.append((L["send"] + o, L["send"] + o + w * P))
+                spans.append((L["recv"] + o, L["recv"] + o + w * P))
+            assert spans[-2][1] <= L["reduce"]
+            for r in range(world):
+                spans.append((L["rgb_stage"] + r * L["rgb_stride"], L["rgb_stage"] + r * L["rgb_stride"] + 3 * P))
+                spans.append((L["campos_stage"] + 4 * r, L["campos_stage"] + 4 * r + 3))
+                spans.append((L["reduce_stage"] + r * L["reduce_stride"],
+                              L["reduce_stage"] + (r + 1) * L["reduce_stride"]))
+            spans.sort()
+            for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+                assert a1 <= b0, (P, world, (a0, a1), (b0, b1))
+            assert spans[-1][1] <= L["total"]
+            for k in ("send", "recv", "reduce", "rgb_stage", "rgb_stride", "campos_stage", "reduce_stage",
+                      "reduce_stride"):
+                assert L[k] % 4 == 0
+            n4 = L["reduce"] // 4
+            longest = max(n4 * (s + 1) // world - n4 * s // world for s in range(world))
+            assert L["reduce_stride"] // 4 >= longest
