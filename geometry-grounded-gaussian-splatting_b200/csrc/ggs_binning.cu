@@ -232,26 +232,46 @@ void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched,
 // ------------------------------------------------------------------------------------------------
 // Tile ranges from the sorted keys (rasterizer_impl.cu:142-161); untouched tiles stay (0,0).
 // ------------------------------------------------------------------------------------------------
-__global__ void tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n, uint2* __restrict__ ranges) {
-    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n) return;
-    const uint32_t cur = (uint32_t)(__ldg(keys + idx) >> 32);
-    if (idx == 0) {
-        ranges[cur].x = 0;
+// Four keys per thread (two 16-byte loads + the predecessor): one 8-byte load per thread left the kernel latency-bound
+// at a third of the HBM rate.
+constexpr int RANGE_ITEMS = 4;
+__global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n,
+                                                          uint2* __restrict__ ranges) {
+    const uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) * RANGE_ITEMS;
+    if (base >= n) return;
+    uint32_t t[RANGE_ITEMS + 1];
+    if (base + RANGE_ITEMS <= n) {
+        const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2*>(keys + base));
+        const ulonglong2 b = __ldg(reinterpret_cast<const ulonglong2*>(keys + base) + 1);
+        t[1] = (uint32_t)(a.x >> 32);
+        t[2] = (uint32_t)(a.y >> 32);
+        t[3] = (uint32_t)(b.x >> 32);
+        t[4] = (uint32_t)(b.y >> 32);
     } else {
-        const uint32_t prev = (uint32_t)(__ldg(keys + idx - 1) >> 32);
-        if (cur != prev) {
-            ranges[prev].y = idx;
+#pragma unroll
+        for (int i = 0; i < RANGE_ITEMS; i++) t[i + 1] = base + i < n ? (uint32_t)(__ldg(keys + base + i) >> 32) : 0u;
+    }
+    t[0] = base ? (uint32_t)(__ldg(keys + base - 1) >> 32) : 0u;
+#pragma unroll
+    for (int i = 0; i < RANGE_ITEMS; i++) {
+        const uint32_t idx = base + i;
+        if (idx >= n) break;
+        const uint32_t cur = t[i + 1];
+        if (idx == 0) {
+            ranges[cur].x = 0;
+        } else if (cur != t[i]) {
+            ranges[t[i]].y = idx;
             ranges[cur].x = idx;
         }
+        if (idx == n - 1) ranges[cur].y = n;
     }
-    if (idx == n - 1) ranges[cur].y = n;
 }
 
 void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream) {
     cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
     if (n == 0) return;
-    tile_ranges_kernel<<<(n + 255) / 256, 256, 0, stream>>>(sorted_keys, n, ranges);
+    const uint32_t per_block = 256 * RANGE_ITEMS;
+    tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_keys, n, ranges);
 }
 
 }  // namespace ggs

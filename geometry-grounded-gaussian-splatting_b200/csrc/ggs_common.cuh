@@ -198,4 +198,47 @@ inline ImgLayout img_layout(size_t npix) {
     return L;
 }
 
+#ifdef __CUDACC__
+// A warp's 32 rows of F = 4 Q floats ([32][F], contiguous in global memory) -> shared-memory rows of stride RS
+// (odd: conflict-free when every lane later walks its own row).  Rows whose bit in `rows` is clear are skipped.
+// The loads of a batch are issued together before any is stored: with the dependent one-load-per-iteration form
+// half of the stall samples of the per-Gaussian kernels sat on this copy (one DRAM round trip per 512 bytes per warp).
+__device__ __forceinline__ void load_rows_to_shared(const float4* __restrict__ src, int Q, int ng, uint32_t rows,
+                                                    float* __restrict__ swarp, int RS, int lane) {
+    constexpr int BATCH = 6;
+    const int total = ng * Q;
+    int gi = 0, rem = lane;
+    for (int e0 = lane; e0 < total; e0 += 32 * BATCH) {
+        float4 v[BATCH];
+        int gi_l = gi, rem_l = rem;
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            const int e = e0 + 32 * j;
+            while (rem_l >= Q) {
+                rem_l -= Q;
+                gi_l++;
+            }
+            if (e < total && ((rows >> gi_l) & 1u)) v[j] = __ldg(src + e);
+            rem_l += 32;
+        }
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            const int e = e0 + 32 * j;
+            while (rem >= Q) {
+                rem -= Q;
+                gi++;
+            }
+            if (e < total && ((rows >> gi) & 1u)) {
+                float* d = swarp + gi * RS + rem * 4;
+                d[0] = v[j].x;
+                d[1] = v[j].y;
+                d[2] = v[j].z;
+                d[3] = v[j].w;
+            }
+            rem += 32;
+        }
+    }
+}
+#endif
+
 }  // namespace ggs

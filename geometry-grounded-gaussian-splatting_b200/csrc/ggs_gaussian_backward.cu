@@ -61,21 +61,7 @@ __global__ void __launch_bounds__(GB_THREADS)
         if (vec4) {
             const int Q = F >> 2;
             const float4* src = reinterpret_cast<const float4*>(in.shs + g0 * F);
-            int gi = 0, rem = lane;
-            for (int e = lane; e < ng * Q; e += 32, rem += 32) {
-                while (rem >= Q) {
-                    rem -= Q;
-                    gi++;
-                }
-                if ((vm >> gi) & 1u) {
-                    const float4 v = __ldg(src + e);
-                    float* d = swarp + gi * RS + rem * 4;
-                    d[0] = v.x;
-                    d[1] = v.y;
-                    d[2] = v.z;
-                    d[3] = v.w;
-                }
-            }
+            load_rows_to_shared(src, Q, ng, vm, swarp, RS, lane);
         } else {
             const float* src = in.shs + g0 * F;
             int gi = 0, rem = lane;

@@ -18,3 +18,9 @@ if [ "${NCU:-0}" = "1" ]; then
       python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
   echo "ncu rc=$?"
 fi
+if [ "${FULL:-0}" = "1" ]; then
+  # one step's worth of our kernels with the full metric set (DRAM traffic, pipe utilisation, source pages)
+  timeout 1200 ncu --set full --import-source on --clock-control none --kernel-name-base demangled -k regex:ggs:: --launch-skip ${FULL_SKIP:-120} -c ${FULL_COUNT:-24} \
+      -f -o gpurun_out/full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+  echo "ncu full rc=$?"
+fi
