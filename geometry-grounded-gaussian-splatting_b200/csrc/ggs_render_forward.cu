@@ -35,8 +35,13 @@ struct RenderParams {
     const float* bg;  // device [3]
 };
 
-constexpr int BATCH = TILE_BATCH;
-constexpr int WARPS = TILE_WARPS;
+// A CTA renders HALF a tile (16x8 pixels, 4 warps; blockIdx.z = half): the barrier that hands over a staged batch
+// then couples 4 warps instead of 8 (warps of a tile have unequal work per batch: 23 % of the stall samples of the
+// full-tile kernel were block barriers) and twice as many CTAs per SM progress independently.  Warp ids stay those of
+// the full tile (half * 4 + warp), so the masks handed to the backward keep their layout.
+constexpr int WARPS = TILE_WARPS / 2;
+constexpr int THREADS = WARPS * 32;
+constexpr int BATCH = THREADS;  // list entries per staged batch (one per thread)
 constexpr uint32_t FULL = 0xffffffffu;
 constexpr uint32_t NEVER = 0xffffffffu;
 constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0 (it does from 13.3 sigma on)
@@ -86,7 +91,7 @@ __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsi
 }
 
 template <bool GEOMETRY>
-__global__ void __launch_bounds__(TILE_PIXELS, 4)
+__global__ void __launch_bounds__(THREADS, 8)
     render_forward_kernel(const RenderParams rp, const uint2* __restrict__ ranges,
                           const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
                           float* __restrict__ out_color, float* __restrict__ out_alpha,
@@ -104,9 +109,10 @@ __global__ void __launch_bounds__(TILE_PIXELS, 4)
     const int W = rp.W, H = rp.H;
     const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
     const uint32_t tid = threadIdx.x;
-    const uint32_t warp = tid >> 5, lane = tid & 31;
-    // warp w owns the 8x4 pixel block (w & 1, w >> 1) of the tile
-    const uint2 pix0 = {blockIdx.x * TILE_X + (warp & 1) * 8, blockIdx.y * TILE_Y + (warp >> 1) * 4};
+    const uint32_t warp = tid >> 5, lane = tid & 31;  // warp: within this CTA (staging, shared arrays)
+    const uint32_t twarp = blockIdx.z * WARPS + warp;  // within the tile (pixels, masks)
+    // warp w of the tile owns its 8x4 pixel block (w & 1, w >> 1)
+    const uint2 pix0 = {blockIdx.x * TILE_X + (twarp & 1) * 8, blockIdx.y * TILE_Y + (twarp >> 1) * 4};
     const uint2 pix = {pix0.x + (lane & 7), pix0.y + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
@@ -197,7 +203,7 @@ __global__ void __launch_bounds__(TILE_PIXELS, 4)
                 const uint32_t gw = i * (BATCH / 32) + w;
                 if (lane == 0) {
                     if (GEOMETRY && gw < MASK_WORDS) s_mask[warp][gw] = bits;
-                    accept_mask[(size_t)(mask_base + gw) * 8 + warp] = bits;  // kept for the backward
+                    accept_mask[(size_t)(mask_base + gw) * 8 + twarp] = bits;  // kept for the backward
                 }
                 mask_words = gw + 1;
             }
@@ -231,8 +237,8 @@ __global__ void __launch_bounds__(TILE_PIXELS, 4)
         for (int w = 0; w < WARPS; w++) m = max(m, s_red[w]);
         max_contributor = m;
     }
-    if (tid == 0) max_contributors[tile_id] = max_contributor;
-    if (lane == 0) warp_words[tile_id * WARPS + warp] = mask_words;
+    if (tid == 0) atomicMax(max_contributors + tile_id, max_contributor);  // over the two halves (zeroed at launch)
+    if (lane == 0) warp_words[tile_id * TILE_WARPS + twarp] = mask_words;
     if constexpr (!GEOMETRY) return;
 
     // ---- passes 2-6: median depth by 8-way bisection ---------------------------------------------------
@@ -415,10 +421,10 @@ __global__ void __launch_bounds__(TILE_PIXELS, 4)
 
     // what the backward's dT/dt pass has to visit: (near_first, ...] restricted to the thinned mask
     const uint32_t nf = __reduce_min_sync(FULL, in_range ? pre_pos : NEVER);
-    if (lane == 0) near_first[tile_id * WARPS + warp] = nf;
+    if (lane == 0) near_first[tile_id * TILE_WARPS + twarp] = nf;
     __syncwarp();
     for (uint32_t gw = lane; gw < min(mask_words, (uint32_t)MASK_WORDS); gw += 32)
-        near_mask[(size_t)(mask_base + gw) * 8 + warp] = s_mask[warp][gw];
+        near_mask[(size_t)(mask_base + gw) * 8 + twarp] = s_mask[warp][gw];
 }
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
@@ -431,8 +437,9 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     rp.focal_x = fp.focal_x;
     rp.focal_y = fp.focal_y;
     rp.bg = fp.view.bg;
-    const dim3 grid(fp.gx, fp.gy, 1);
-    const dim3 block(TILE_PIXELS, 1, 1);
+    const dim3 grid(fp.gx, fp.gy, TILE_WARPS / WARPS);
+    const dim3 block(THREADS, 1, 1);
+    cudaMemsetAsync(out.max_contributor, 0, (size_t)fp.gx * fp.gy * sizeof(uint32_t), stream);
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(render_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
