@@ -29,6 +29,7 @@ from __future__ import annotations
 
 import argparse
 import gc
+import glob
 import json
 import os
 import sys
@@ -493,23 +494,39 @@ def main():
         outs, inter = H.ours_forward_raw(sc, str(device))
         stats = {"P": sc.P, "visible": int((outs["radii"] > 0).sum()), "num_rendered": inter["num_rendered"],
                  "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
-        # launches of OUR kernels per step: preprocess, depth pre-sort (histogram, offsets, 4 onesweep passes), scan,
-        # duplicate, pair sort (histogram, offsets, one onesweep pass per 8 tile bits), ranges, render fwd, render bwd,
-        # per-Gaussian bwd
         stats["sort_passes_run"] = sort_passes_run
-        stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + 8 * stats["num_rendered"] \
-            + sort_passes_run * 24 * stats["num_rendered"]
-        line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 2 + sort_passes_run + 1 + 1 + 2)
+        # depth pre-sort: histogram read + 4 passes of (8 + 4) B in and out per Gaussian; tile sort: 32-bit keys + values
+        # in and out per pass, the last pass writes the 64-bit keys (and gathers 4 B of depth per pair)
+        stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + (sort_passes_run - 1) * 16 * stats["num_rendered"] \
+            + 24 * stats["num_rendered"]
+        # preprocess, depth pre-sort (histogram, offsets, 4 passes), scan, duplicate (+ tile histograms), tile sort
+        # (offsets, passes), ranges, render fwd, render bwd, per-Gaussian bwd
+        line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 1 + sort_passes_run + 1 + 1 + 2)
         alg = algorithmic(stats)
         per_stage = {}
         for k, b in alg.items():
             t = stages.get(k)
             if t:
                 per_stage[k] = {"ms": t, "alg_bytes": b, "gbs": b / t / 1e6, "frac_hbm": b / t / 1e6 / hbm}
+        # measured DRAM traffic per launch (ncu --set full of this same command, summarised under profiles/)
+        traffic, traffic_src = {}, None
+        cands = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic_*.json")))
+        if cands and args.workload == "c3":
+            with open(cands[-1]) as fh:
+                tj = json.load(fh)
+            traffic_src = os.path.relpath(cands[-1], ROOT)
+            kmap = {"preprocess": "preprocess_kernel", "scan": "scan_kernel", "duplicate": "duplicate_keys_kernel",
+                    "ranges": "tile_ranges_kernel", "render_forward": "render_forward_kernel",
+                    "render_backward": "render_backward_kernel", "gaussian_backward": "gaussian_backward_kernel"}
+            for st, kn in kmap.items():
+                if kn in tj["kernels"]:
+                    traffic[st] = tj["kernels"][kn]["dram_bytes"]
+                    if st in per_stage:
+                        per_stage[st]["dram_bytes_ncu"] = traffic[st]
         dom = max(per_stage, key=lambda k: per_stage[k]["ms"])
         line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": per_stage[dom]["gbs"], "peak": hbm,
-                            "unit": "GB/s", "frac": per_stage[dom]["frac_hbm"], "traffic": None,
-                            "peak_source": how,
+                            "unit": "GB/s", "frac": per_stage[dom]["frac_hbm"], "traffic": traffic.get(dom),
+                            "traffic_source": traffic_src, "peak_source": how,
                             "note": "render kernels are issue-bound (MUFU/FP32), not HBM-bound; see DESIGN.md "
                                     "and profiles/ for pipe utilisation"}
         line["stages"] = per_stage

@@ -165,23 +165,24 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     *bin = b;
     (void)depth_min_bits;
     (void)depth_max_bits;
-    // the pairs are emitted in depth order: only the tile bits [32, end_bit) are left to sort (stable)
-    const SortPlan plan = plain_sort_plan(32, end_bit);
-    // the sorted pairs always end up in keys_a / vals_a: with an odd number of passes the unsorted pairs start in *_b
-    const bool odd = plan.passes & 1;
-    g_prof.sort_passes = plan.passes;
-    uint64_t* k_in = at<uint64_t>(b, odd ? BL.keys_b : BL.keys_a);
-    uint64_t* k_other = at<uint64_t>(b, odd ? BL.keys_a : BL.keys_b);
-    uint32_t* v_in = at<uint32_t>(b, odd ? BL.vals_b : BL.vals_a);
-    uint32_t* v_other = at<uint32_t>(b, odd ? BL.vals_a : BL.vals_b);
+    // The pairs are emitted in depth order, so only the tile bits [32, end_bit) are left to sort (stable), and only
+    // the 32-bit tile halves of the keys move through the passes: two u32[D] ping-pong arrays inside keys_b; the
+    // last pass writes the reference's 64-bit keys into keys_a.  Sorted values always land in vals_a.
+    const int tile_bits = end_bit - 32;
+    const int passes = tile_sort_passes(tile_bits);
+    g_prof.sort_passes = passes;
+    uint32_t* tk_a = at<uint32_t>(b, BL.keys_b);
+    uint32_t* tk_b = tk_a + D;
+    uint32_t* v_a = at<uint32_t>(b, BL.vals_a);
+    uint32_t* v_b = at<uint32_t>(b, BL.vals_b);
+    const bool odd = passes & 1;
     prof_mark(stream, EV_DUP0);
-    launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects),
-                          at<float>(geom, GL.depths), fp.gx, k_in, v_in, D, stream);
+    launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects), fp.gx,
+                          odd ? tk_b : tk_a, odd ? v_b : v_a, D, passes, at<uint32_t>(b, BL.hist), stream);
     GGS_STAGE("duplicate_keys", debug, stream);
     prof_mark(stream, EV_DUP);
-    launch_radix_sort(k_in, k_other, v_in, v_other, D, plan, at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status),
-                      (size_t)plan.passes * ((D + SORT_TILE - 1) / SORT_TILE) * RADIX * 4, at<uint32_t>(b, BL.counters),
-                      stream);
+    launch_tile_sort(tk_a, tk_b, v_a, v_b, D, tile_bits, at<uint32_t>(geom, GL.depths), at<uint64_t>(b, BL.keys_a),
+                     at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), at<uint32_t>(b, BL.counters), stream);
     GGS_STAGE("radix_sort", debug, stream);
     prof_mark(stream, EV_SORT);
     const uint64_t* sorted_keys = at<uint64_t>(b, BL.keys_a);

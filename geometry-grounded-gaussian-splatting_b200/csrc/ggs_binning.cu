@@ -137,8 +137,9 @@ void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uin
 // contiguous slice of the key array they expand into; every output slot finds its Gaussian by
 // a binary search over the block's 257 offsets held in shared memory.  Writes are fully
 // coalesced and perfectly balanced (the reference loops over a splat's tiles in one thread).
-// Key = (tile << 32) | f32 bits of depth, value = Gaussian index; slot order inside one
-// Gaussian is y-major then x (rasterizer_impl.cu:96-104).
+// Reference key = (tile << 32) | f32 bits of depth, value = Gaussian index; slot order inside one
+// Gaussian is y-major then x (rasterizer_impl.cu:96-104).  Only the 32-bit tile half is materialised here: the
+// last pass of the tile sort writes the full 64-bit keys (launch_tile_sort).
 // The pairs leave this kernel ordered by (depth, Gaussian index, tile); the stable pair sort on the tile bits alone
 // then yields the reference's order (tile, depth, Gaussian index) -- SortPairs over bits [0, 32 + tile bits) of keys
 // emitted in Gaussian order (rasterizer_impl.cu:406-412) -- without ever moving the pairs for the depth bits.
@@ -147,62 +148,88 @@ constexpr int DUP_THREADS = 256;
 
 __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, const uint32_t* __restrict__ order,
                                                                      const uint32_t* __restrict__ offsets,
-                                                                     const uint2* __restrict__ rects,
-                                                                     const float* __restrict__ depths, int gx,
-                                                                     uint64_t* __restrict__ keys,
-                                                                     uint32_t* __restrict__ vals) {
+                                                                     const uint2* __restrict__ rects, int gx,
+                                                                     uint32_t* __restrict__ tile_keys,
+                                                                     uint32_t* __restrict__ vals, int passes,
+                                                                     uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_off[DUP_THREADS + 1];
     __shared__ uint32_t s_g[DUP_THREADS];
     __shared__ uint2 s_rect[DUP_THREADS];
-    __shared__ uint32_t s_depth[DUP_THREADS];
+    __shared__ uint32_t s_hist[4][RADIX];  // digit histograms of this block's keys (tile ids < 2^32: <= 4 digits)
     const int g0 = blockIdx.x * DUP_THREADS;
     const int tid = threadIdx.x;
     const int gi = g0 + tid;
+    for (int i = tid; i < passes * RADIX; i += DUP_THREADS) (&s_hist[0][0])[i] = 0;
     if (tid == 0) s_off[0] = (g0 == 0) ? 0u : __ldg(offsets + g0 - 1);
     s_off[tid + 1] = (gi < P) ? __ldg(offsets + gi) : 0xffffffffu;
     if (gi < P) {
         const uint32_t g = __ldg(order + gi);
         s_g[tid] = g;
         s_rect[tid] = __ldg(rects + g);  // culled Gaussians own no slots: their (unwritten) rects are never used
-        s_depth[tid] = __float_as_uint(__ldg(depths + g));
     }
     __syncthreads();
     const uint32_t begin = s_off[0];
     const int last = min(DUP_THREADS, P - g0);
     const uint32_t end = s_off[last];
-    for (uint32_t o = begin + tid; o < end; o += DUP_THREADS) {
-        // largest j in [0,last) with s_off[j] <= o
-        int lo = 0, hi = last;
+    const uint32_t span = end - begin;
+    // whole warps walk the slice together (the histogram votes below need every lane)
+    for (uint32_t ob = (tid & ~31u); ob < span; ob += DUP_THREADS) {
+        const uint32_t o = begin + ob + (tid & 31u);
+        const bool live = o < end;
+        uint32_t tile = 0;
+        if (live) {
+            // largest j in [0,last) with s_off[j] <= o
+            int lo = 0, hi = last;
 #pragma unroll
-        for (int s = 0; s < 9; s++) {
-            const int mid = (lo + hi) >> 1;
-            if (lo + 1 < hi) {
-                if (s_off[mid] <= o)
-                    lo = mid;
-                else
-                    hi = mid;
+            for (int s = 0; s < 9; s++) {
+                const int mid = (lo + hi) >> 1;
+                if (lo + 1 < hi) {
+                    if (s_off[mid] <= o)
+                        lo = mid;
+                    else
+                        hi = mid;
+                }
+            }
+            const uint32_t local = o - s_off[lo];
+            const uint2 rc = s_rect[lo];
+            const uint32_t minx = rc.x & 0xffffu, miny = rc.x >> 16;
+            const uint32_t w = (rc.y & 0xffffu) - minx;
+            const uint32_t ty = miny + local / w;
+            const uint32_t tx = minx + local % w;
+            tile = ty * (uint32_t)gx + tx;
+            tile_keys[o] = tile;
+            vals[o] = s_g[lo];
+        }
+        // digit histograms: the low digit of neighbouring slots differs (consecutive tiles), the higher ones are
+        // mostly warp-uniform -- one add for the warp then, per-lane atomics otherwise
+        if (live) atomicAdd(&s_hist[0][tile & (RADIX - 1)], 1u);
+        for (int p = 1; p < passes; p++) {
+            const uint32_t d = (tile >> (RADIX_BITS * p)) & (RADIX - 1);
+            const uint32_t lives = __ballot_sync(0xffffffffu, live);
+            if (lives == 0) break;
+            const int leader = __ffs(lives) - 1;
+            const uint32_t d0 = __shfl_sync(0xffffffffu, d, leader);
+            if (__all_sync(0xffffffffu, !live || d == d0)) {
+                if ((tid & 31) == leader) atomicAdd(&s_hist[p][d0], (uint32_t)__popc(lives));
+            } else if (live) {
+                atomicAdd(&s_hist[p][d], 1u);
             }
         }
-        const uint32_t local = o - s_off[lo];
-        const uint2 rc = s_rect[lo];
-        const uint32_t minx = rc.x & 0xffffu, miny = rc.x >> 16;
-        const uint32_t w = (rc.y & 0xffffu) - minx;
-        const uint32_t ty = miny + local / w;
-        const uint32_t tx = minx + local % w;
-        uint64_t key = (uint64_t)(ty * (uint32_t)gx + tx);
-        key <<= 32;
-        key |= (uint64_t)s_depth[lo];
-        keys[o] = key;
-        vals[o] = s_g[lo];
+    }
+    __syncthreads();
+    for (int i = tid; i < passes * RADIX; i += DUP_THREADS) {
+        const uint32_t c = (&s_hist[0][0])[i];
+        if (c) atomicAdd(hist + i, c);
     }
 }
 
-void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects,
-                           const float* depths, int gx, uint64_t* keys, uint32_t* vals, uint32_t D,
+void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
+                           uint32_t* tile_keys, uint32_t* vals, uint32_t D, int passes, uint32_t* hist,
                            cudaStream_t stream) {
+    cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
     if (P == 0 || D == 0) return;
-    duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(P, order, offsets, rects,
-                                                                                          depths, gx, keys, vals);
+    duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(
+        P, order, offsets, rects, gx, tile_keys, vals, passes > 4 ? 4 : passes, hist);
 }
 
 // Points fall into exactly one tile (rasterizer_impl.cu:109-137).

@@ -38,9 +38,11 @@ void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uin
                  cudaStream_t stream, const uint32_t* order = nullptr);
 
 // ---- stage 2: key duplication, radix sort, tile ranges ----------------------------------------
-// order[i] = Gaussian at depth rank i; offsets = inclusive scan of the tile counts in that order
-void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects,
-                           const float* depths, int gx, uint64_t* keys, uint32_t* vals, uint32_t D,
+// order[i] = Gaussian at depth rank i; offsets = inclusive scan of the tile counts in that order.  Emits 32-bit TILE
+// keys (the depth half of the reference's 64-bit key is implied by the emission order) and accumulates the 8-bit
+// digit histograms of the `passes` tile-sort passes into hist[passes][256] (zeroed here).
+void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
+                           uint32_t* tile_keys, uint32_t* vals, uint32_t D, int passes, uint32_t* hist,
                            cudaStream_t stream);
 
 // point variant (reference createWithKeys, rasterizer_impl.cu:109-137): key = tile<<32
@@ -69,6 +71,15 @@ SortPlan rasterizer_sort_plan(int end_bit, uint32_t depth_min_bits, uint32_t dep
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
                       const SortPlan& plan, uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
                       cudaStream_t stream);
+
+// Stable sort of depth-ordered pairs on their 32-bit tile keys (bits [0, tile_bits)); the histograms are those of
+// launch_duplicate_keys.  Input in (tk_a, vals_a) when tile_sort_passes() is even, in (tk_b, vals_b) when odd; the
+// sorted values land in vals_a and the last pass writes the reference's 64-bit keys (tile << 32 | depth bits of the
+// pair's Gaussian) to keys64_out.
+int tile_sort_passes(int tile_bits);
+void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int tile_bits,
+                      const uint32_t* depth_bits, uint64_t* keys64_out, uint32_t* hist, uint32_t* status,
+                      uint32_t* counters, cudaStream_t stream);
 
 void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream);
 

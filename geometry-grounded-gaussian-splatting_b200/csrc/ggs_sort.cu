@@ -40,6 +40,9 @@ __device__ __forceinline__ uint32_t digit_of(const uint64_t key, const DigitSpec
     const uint32_t v = ((((uint32_t)(key >> 32)) & s.tile_mask) << s.nb) | ((((uint32_t)key) >> 24) - s.emin);
     return (v >> s.vshift) & s.mask;
 }
+__device__ __forceinline__ uint32_t digit_of(const uint32_t key, const DigitSpec& s) {
+    return (key >> s.shift) & s.mask;  // 32-bit tile keys: plain digits only
+}
 struct PassSpecs {
     DigitSpec d[MAX_PASSES];
 };
@@ -139,22 +142,27 @@ __global__ void __launch_bounds__(RADIX) offsets_kernel(uint32_t* __restrict__ h
 // MATCH: rank with match.any (one instruction, ~10 cycles when most lanes hold different digits, as for depth
 // mantissa bits -- but measured ~65 cycles when lanes share digits in runs, as for tile bits of depth-sorted
 // pairs: the ADU pipe became the bottleneck of those passes).  !MATCH: eight ballots, constant cost.
-template <bool MATCH>
-__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* __restrict__ keys_in,
-                                                                uint64_t* __restrict__ keys_out,
+// KeyT = uint64_t: the general sort.  KeyT = uint32_t: tile keys of pairs that were emitted in depth order; with EMIT64
+// the pass is the last one and writes the full reference key (tile << 32 | depth bits of the pair's Gaussian) to
+// keys64_out instead of the 32-bit key -- the 64-bit keys never move through the passes.
+template <bool MATCH, typename KeyT, bool EMIT64>
+__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __restrict__ keys_in,
+                                                                KeyT* __restrict__ keys_out,
                                                                 const uint32_t* __restrict__ vals_in,
                                                                 uint32_t* __restrict__ vals_out, uint32_t n,
                                                                 const DigitSpec spec,
                                                                 const uint32_t* __restrict__ bin_offsets,
                                                                 uint32_t* __restrict__ status,
-                                                                uint32_t* __restrict__ counter) {
+                                                                uint32_t* __restrict__ counter,
+                                                                uint64_t* __restrict__ keys64_out,
+                                                                const uint32_t* __restrict__ depth_bits) {
     constexpr int WARPS = SORT_THREADS / 32;
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_warp_hist[WARPS][RADIX];
     __shared__ uint32_t s_bin_start[RADIX];
     __shared__ uint32_t s_global_base[RADIX];
     __shared__ uint32_t s_scan[WARPS];
-    __shared__ uint64_t s_keys[SORT_TILE];
+    __shared__ KeyT s_keys[SORT_TILE];
     __shared__ uint32_t s_vals[SORT_TILE];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -166,7 +174,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     const uint32_t count = min((uint32_t)SORT_TILE, n - base);
 
     // ---- load (warp-striped) and rank --------------------------------------------------------
-    uint64_t key[SORT_ITEMS];
+    KeyT key[SORT_ITEMS];
     uint32_t val[SORT_ITEMS];
     uint32_t rank[SORT_ITEMS];
     const uint32_t warp_base = warp * 32 * SORT_ITEMS;
@@ -177,7 +185,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
             key[i] = __ldg(keys_in + base + li);
             val[i] = __ldg(vals_in + base + li);
         } else {
-            key[i] = ~0ull;
+            key[i] = ~KeyT(0);
             val[i] = 0;
         }
     }
@@ -287,11 +295,15 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const uint64_t* 
     }
     __syncthreads();
     for (uint32_t p = tid; p < count; p += SORT_THREADS) {
-        const uint64_t k = s_keys[p];
+        const KeyT k = s_keys[p];
         const uint32_t dg = digit_of(k, spec);
         const uint32_t out = s_global_base[dg] + p;
-        keys_out[out] = k;
-        vals_out[out] = s_vals[p];
+        const uint32_t v = s_vals[p];
+        if constexpr (EMIT64)
+            keys64_out[out] = ((uint64_t)k << 32) | (uint64_t)__ldg(depth_bits + v);
+        else
+            keys_out[out] = k;
+        vals_out[out] = v;
     }
 }
 
@@ -317,13 +329,13 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
         // tile-bit digits (virtual key, or plain digits above bit 32) come in runs: rank them with ballots
         const bool tile_digit = specs.d[p].vshift >= 0 || specs.d[p].shift >= 32;
         if (tile_digit)
-            onesweep_kernel<false><<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p],
-                                                                       hist + p * RADIX,
-                                                                       status + (size_t)p * tiles * RADIX, counters + p);
+            onesweep_kernel<false, uint64_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
+                kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
+                nullptr, nullptr);
         else
-            onesweep_kernel<true><<<tiles, SORT_THREADS, 0, stream>>>(kin, kout, vin, vout, n, specs.d[p],
-                                                                      hist + p * RADIX,
-                                                                      status + (size_t)p * tiles * RADIX, counters + p);
+            onesweep_kernel<true, uint64_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
+                kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
+                nullptr, nullptr);
         uint64_t* tk = kin;
         kin = kout;
         kout = tk;
@@ -332,6 +344,45 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
         vout = tv;
     }
     return passes & 1;
+}
+
+int tile_sort_passes(int tile_bits) { return (tile_bits + RADIX_BITS - 1) / RADIX_BITS; }
+
+void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int tile_bits,
+                      const uint32_t* depth_bits, uint64_t* keys64_out, uint32_t* hist, uint32_t* status,
+                      uint32_t* counters, cudaStream_t stream) {
+    if (n == 0) return;
+    const int passes = tile_sort_passes(tile_bits);
+    const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    cudaMemsetAsync(status, 0, (size_t)passes * tiles * RADIX * 4, stream);
+    cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
+    offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);  // the histograms come from the key duplication
+    // final values must land in vals_a: an even number of passes starts in *_a, an odd one in *_b
+    uint32_t* kin = (passes & 1) ? tk_b : tk_a;
+    uint32_t* kout = (passes & 1) ? tk_a : tk_b;
+    uint32_t* vin = (passes & 1) ? vals_b : vals_a;
+    uint32_t* vout = (passes & 1) ? vals_a : vals_b;
+    for (int p = 0; p < passes; p++) {
+        DigitSpec spec = {};
+        spec.shift = RADIX_BITS * p;
+        const int width = tile_bits - spec.shift < RADIX_BITS ? tile_bits - spec.shift : RADIX_BITS;
+        spec.mask = (1u << width) - 1u;
+        spec.vshift = -1;
+        uint32_t* st = status + (size_t)p * tiles * RADIX;
+        // tile digits of depth-ordered pairs come in runs: rank with ballots (see onesweep_kernel)
+        if (p + 1 == passes)
+            onesweep_kernel<false, uint32_t, true><<<tiles, SORT_THREADS, 0, stream>>>(
+                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, keys64_out, depth_bits);
+        else
+            onesweep_kernel<false, uint32_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
+                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, nullptr, nullptr);
+        uint32_t* tk = kin;
+        kin = kout;
+        kout = tk;
+        uint32_t* tv = vin;
+        vin = vout;
+        vout = tv;
+    }
 }
 
 }  // namespace ggs
