@@ -626,6 +626,35 @@ int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const
     return GGS_OK;
 }
 
+int ggs_activate_forward(int64_t count, const float* raw_scaling, const float* raw_opacity, const float* raw_rotation,
+                         const float* filter_3D, float* scales, float* opacities, float* rotations, void* stream_) {
+    if (count < 0 || count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad Gaussian count");
+    if (count == 0) return GGS_OK;
+    if (!raw_scaling || !raw_opacity || !raw_rotation || !filter_3D || !scales || !opacities || !rotations)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_activate_forward((int)count, raw_scaling, raw_opacity, raw_rotation, filter_3D, scales, opacities,
+                            rotations, stream);
+    GGS_STAGE("activate_forward", false, stream);
+    return GGS_OK;
+}
+
+int ggs_activate_backward(int64_t count, const float* raw_scaling, const float* raw_opacity, const float* raw_rotation,
+                          const float* filter_3D, const float* dL_dscales, const float* dL_dopacities,
+                          const float* dL_drotations, float* dL_draw_scaling, float* dL_draw_opacity,
+                          float* dL_draw_rotation, void* stream_) {
+    if (count < 0 || count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad Gaussian count");
+    if (count == 0) return GGS_OK;
+    if (!raw_scaling || !raw_opacity || !raw_rotation || !filter_3D || !dL_dscales || !dL_dopacities ||
+        !dL_drotations || !dL_draw_scaling || !dL_draw_opacity || !dL_draw_rotation)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_activate_backward((int)count, raw_scaling, raw_opacity, raw_rotation, filter_3D, dL_dscales, dL_dopacities,
+                             dL_drotations, dL_draw_scaling, dL_draw_opacity, dL_draw_rotation, stream);
+    GGS_STAGE("activate_backward", false, stream);
+    return GGS_OK;
+}
+
 int ggs_profile_enable(int on) {
     g_prof.on = on != 0;
     g_prof.have_fwd = g_prof.have_bwd = false;

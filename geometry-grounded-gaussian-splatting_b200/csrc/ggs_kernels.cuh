@@ -206,6 +206,15 @@ void launch_sample_depth_backward(const FrameParams& fp, int tiles, uint32_t max
 void launch_points_backward(const FrameParams& fp, int PN, const float* points3D, const uint32_t* touched,
                             const float2* dL_dpoints2D, float* dL_dpoints3D, cudaStream_t stream);
 
+// Fused caller-side activations (ggs_activations.cu; scene/gaussian_model.py:158-160,203-212)
+void launch_activate_forward(int P, const float* raw_scaling, const float* raw_opacity, const float* raw_rotation,
+                             const float* filter_3D, float* scales, float* opacities, float* rotations,
+                             cudaStream_t stream);
+void launch_activate_backward(int P, const float* raw_scaling, const float* raw_opacity, const float* raw_rotation,
+                              const float* filter_3D, const float* dL_dscales, const float* dL_dopacities,
+                              const float* dL_drotations, float* dL_draw_scaling, float* dL_draw_opacity,
+                              float* dL_draw_rotation, cudaStream_t stream);
+
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 
 }  // namespace ggs

@@ -27,7 +27,7 @@ import torch.nn as nn
 from . import _abi
 from ._abi import lib as _lib
 
-__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "activate_gaussians"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -378,6 +378,57 @@ class _SampleDepth(torch.autograd.Function):
                     raise arena.error
                 _abi.check(rc, "ggs_sample_depth_backward")
         return d_pts.reshape(ctx.pts_shape), d_means3D, d_opacity, d_scales, d_rot, None
+
+
+class _ActivateGaussians(torch.autograd.Function):
+    """One kernel each way for the activations the reference applies in torch before every rasterizer call
+    (scene/gaussian_model.py:203-212 get_scaling_n_opacity_with_3D_filter, :158-160 get_rotation)."""
+
+    @staticmethod
+    def forward(ctx, raw_scaling, raw_opacity, raw_rotation, filter_3D):
+        if not raw_scaling.is_cuda:
+            raise RuntimeError("activate_gaussians needs CUDA tensors: this library has no CPU path")
+        device = raw_scaling.device
+        rs, ro, rq, f = (_dev_f32(t, device) for t in (raw_scaling, raw_opacity, raw_rotation, filter_3D))
+        P = rs.shape[0]
+        if rs.shape != (P, 3) or ro.numel() != P or rq.shape != (P, 4) or f.numel() != P:
+            raise RuntimeError("expected raw_scaling [P,3], raw_opacity [P,1], raw_rotation [P,4], filter_3D [P,1]")
+        scales = torch.empty(P, 3, dtype=torch.float32, device=device)
+        opac = torch.empty(P, 1, dtype=torch.float32, device=device)
+        rot = torch.empty(P, 4, dtype=torch.float32, device=device)
+        with torch.cuda.device(device):
+            _abi.check(_lib.ggs_activate_forward(P, _abi.ptr(rs), _abi.ptr(ro), _abi.ptr(rq), _abi.ptr(f),
+                                                 _abi.ptr(scales), _abi.ptr(opac), _abi.ptr(rot),
+                                                 _abi.stream_handle(device)), "ggs_activate_forward")
+        ctx.save_for_backward(rs, ro, rq, f)
+        ctx.shapes = (raw_scaling.shape, raw_opacity.shape, raw_rotation.shape)
+        return scales, opac, rot
+
+    @staticmethod
+    def backward(ctx, g_scales, g_opac, g_rot):
+        rs, ro, rq, f = ctx.saved_tensors
+        device = rs.device
+        P = rs.shape[0]
+        z = lambda g, w: torch.zeros(P, w, dtype=torch.float32, device=device) if g is None else _dev_f32(g, device)  # noqa: E731
+        gs, go, gq = z(g_scales, 3), z(g_opac, 1), z(g_rot, 4)
+        d_rs = torch.empty(P, 3, dtype=torch.float32, device=device)
+        d_ro = torch.empty(P, 1, dtype=torch.float32, device=device)
+        d_rq = torch.empty(P, 4, dtype=torch.float32, device=device)
+        with torch.cuda.device(device):
+            _abi.check(_lib.ggs_activate_backward(P, _abi.ptr(rs), _abi.ptr(ro), _abi.ptr(rq), _abi.ptr(f), _abi.ptr(gs),
+                                                  _abi.ptr(go), _abi.ptr(gq), _abi.ptr(d_rs), _abi.ptr(d_ro),
+                                                  _abi.ptr(d_rq), _abi.stream_handle(device)),
+                       "ggs_activate_backward")
+        s0, s1, s2 = ctx.shapes
+        return d_rs.view(s0), d_ro.view(s1), d_rq.view(s2), None
+
+
+def activate_gaussians(raw_scaling, raw_opacity, raw_rotation, filter_3D):
+    """(scales [P,3], opacities [P,1], rotations [P,4]) exactly as gaussian_renderer/__init__.py:62-63 obtains them from
+    `pc.get_scaling_n_opacity_with_3D_filter` and `pc.get_rotation`, differentiable w.r.t. the three raw parameters
+    (filter_3D is a buffer): one fused kernel forward and one backward instead of ~30 elementwise launches.
+    Opt-in: the drop-in surface does not need it."""
+    return _ActivateGaussians.apply(raw_scaling, raw_opacity, raw_rotation, filter_3D)
 
 
 class GaussianRasterizer(nn.Module):

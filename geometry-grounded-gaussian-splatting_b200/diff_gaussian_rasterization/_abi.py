@@ -94,7 +94,7 @@ EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_ra
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
            "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
-           "ggs_rasterize_backward_peer")
+           "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
 
 def _load():
@@ -150,6 +150,10 @@ def _load():
     lib.ggs_rasterize_backward_peer.restype = C.c_int
     lib.ggs_rasterize_backward_peer.argtypes = list(lib.ggs_rasterize_backward.argtypes[:-1]) + [
         C.POINTER(GgsPeerExchange), C.c_void_p]
+    lib.ggs_activate_forward.restype = C.c_int
+    lib.ggs_activate_forward.argtypes = [C.c_int64] + [C.c_void_p] * 8
+    lib.ggs_activate_backward.restype = C.c_int
+    lib.ggs_activate_backward.argtypes = [C.c_int64] + [C.c_void_p] * 11
     lib.ggs_profile_read.restype = C.c_int
     lib.ggs_profile_read.argtypes = [C.POINTER(GgsStageTimes)]
     if lib.ggs_abi_version() != 1:

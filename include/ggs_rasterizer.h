@@ -270,6 +270,21 @@ GGS_API int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussian
 GGS_API int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
                       const GgsPeerExchange* exchange, float* dL_dsh, void* stream);
 
+/* ---- fused caller-side activations (opt-in, the reference does this in torch) -------------
+ * One pass each way over what gaussian_renderer/__init__.py:62-63 obtains from
+ * GaussianModel.get_scaling_n_opacity_with_3D_filter (scene/gaussian_model.py:203-212) and GaussianModel.get_rotation
+ * (:158-160):  scales = sqrt(exp(raw_scaling)^2 + filter_3D^2) [P,3],
+ * opacities = sigmoid(raw_opacity) * sqrt(prod exp(raw_scaling)^2 / prod (exp(raw_scaling)^2 + filter_3D^2)) [P,1],
+ * rotations = raw_rotation / max(|raw_rotation|, 1e-12) [P,4].  filter_3D [P,1] carries no gradient (it is a buffer
+ * in the reference).  IEEE arithmetic (no fast-math): results within an ulp or two of the torch expressions. */
+GGS_API int ggs_activate_forward(int64_t count, const float* raw_scaling, const float* raw_opacity,
+                         const float* raw_rotation, const float* filter_3D, float* scales, float* opacities,
+                         float* rotations, void* stream);
+GGS_API int ggs_activate_backward(int64_t count, const float* raw_scaling, const float* raw_opacity,
+                          const float* raw_rotation, const float* filter_3D, const float* dL_dscales,
+                          const float* dL_dopacities, const float* dL_drotations, float* dL_draw_scaling,
+                          float* dL_draw_opacity, float* dL_draw_rotation, void* stream);
+
 /* ---- optional per-stage device timing ------------------------------------------------------------
  * When enabled (process-wide) the forward / backward record CUDA events on the caller's stream
  * between stages; ggs_profile_read waits for the events of the most recent forward and backward and

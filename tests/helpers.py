@@ -78,6 +78,19 @@ def run_module(mod, sc, device, require_depth=True, backward=True, mask_depth_gr
     return out, grads
 
 
+def rasterize_with(mod, sc, device, scales, opacities, rotations, require_depth=True):
+    """Rasterizer forward with caller-provided (differentiable) scales / opacities / rotations; the other inputs are
+    the scene's.  Returns (color, mdepth, alpha, normal) attached to the graph."""
+    rs = settings_for(mod, sc, device, require_depth)
+    x = leaf_inputs(sc, device)
+    rast = mod.GaussianRasterizer(rs)
+    color, _radii, mdepth, alpha, normal = rast(
+        means3D=x["means3D"], means2D=x["means2D"], opacities=opacities, shs=x["shs"], sg_axis=x["sg_axis"],
+        sg_sharpness=x["sg_sharpness"], sg_color=x["sg_color"], colors_precomp=None, scales=scales,
+        rotations=rotations, cov3D_precomp=None)
+    return color, mdepth, alpha, normal
+
+
 # ---- intermediates -------------------------------------------------------------------------------
 
 def _bytes_view(buf, offset, dtype, count):
