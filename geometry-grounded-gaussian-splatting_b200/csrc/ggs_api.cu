@@ -332,7 +332,7 @@ float* peer_ptr(const GgsPeerExchange* px, int r, int64_t off) {
 
 int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
                   const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
-                  const GgsPeerExchange* px, void* stream_) {
+                  const GgsPeerExchange* px, void* stream_, void* side_stream_ = nullptr) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FrameParams fp;
     GaussianInputs in;
@@ -396,11 +396,13 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
         if (px->multicast_base)
             t.mc_rgb = reinterpret_cast<float*>(px->multicast_base) + px->rgb_stage_offset +
                        (int64_t)px->rank * px->rgb_stage_stride;
+        // the caller's side stream if it gave one (it then chains the view-sum of the colour gradients behind the
+        // push on that stream, concurrent with the per-Gaussian backward), else the library's own
+        cudaStream_t side = side_stream_ ? static_cast<cudaStream_t>(side_stream_) : lane->stream;
         GGS_CUDA(cudaEventRecord(lane->ready, stream));
-        GGS_CUDA(cudaStreamWaitEvent(lane->stream, lane->ready, 0));
-        launch_push_rgb(fp.P, acc, at<uint8_t>(state->geometry, GL.clamped), bi->radii, fp.view.campos, t,
-                        lane->stream);
-        GGS_CUDA(cudaEventRecord(lane->done, lane->stream));
+        GGS_CUDA(cudaStreamWaitEvent(side, lane->ready, 0));
+        launch_push_rgb(fp.P, acc, at<uint8_t>(state->geometry, GL.clamped), bi->radii, fp.view.campos, t, side);
+        GGS_CUDA(cudaEventRecord(lane->done, side));
     }
 
     GaussianGrads gg;
@@ -447,12 +449,12 @@ int ggs_rasterize_backward(const GgsFrame* frame, const GgsGaussians* gaussians,
 
 int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
                                 const GgsBackwardInputs* bi, GgsAllocFn alloc, void* user, const GgsGradients* grads,
-                                const GgsPeerExchange* px, void* stream) {
+                                const GgsPeerExchange* px, void* stream, void* side_stream) {
     const int rc = check_exchange(px);
     if (rc) return rc;
     if (!grads || reinterpret_cast<const float*>(grads->dL_drotations) == nullptr)
         return fail(GGS_ERR_INVALID_ARGUMENT, "null gradient tensor");
-    return backward_impl(frame, gaussians, state, bi, alloc, user, grads, px, stream);
+    return backward_impl(frame, gaussians, state, bi, alloc, user, grads, px, stream, side_stream);
 }
 
 int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
@@ -592,7 +594,7 @@ int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussian
 }
 
 int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
-                      const GgsPeerExchange* px, float* dL_dsh, void* stream_) {
+                      const GgsPeerExchange* px, float* dL_dsh, int32_t parts, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int rc = check_exchange(px);
     if (rc) return rc;
@@ -621,7 +623,9 @@ int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const
     const size_t per_block = 256;
     const size_t want = (job.hi4 - job.lo4 + per_block - 1) / per_block;
     job.blocks = (int)(want < (size_t)(148 * 4) ? want : (size_t)(148 * 4));
-    launch_view_sum_peer((int)count, sh_degree, sh_coeffs, means3D, src, dL_dsh, job, stream);
+    if (!(parts & GGS_VIEW_SUM_SLICE)) job.blocks = 0;
+    launch_view_sum_peer((parts & GGS_VIEW_SUM_SH) ? (int)count : 0, sh_degree, sh_coeffs, means3D, src, dL_dsh, job,
+                         stream);
     GGS_STAGE("view_sum_peer", false, stream);
     return GGS_OK;
 }

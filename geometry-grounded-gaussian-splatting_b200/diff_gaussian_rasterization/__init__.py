@@ -265,7 +265,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             if exchange is not None:
                 rc = _lib.ggs_rasterize_backward_peer(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn,
                                                       None, C.byref(grads), C.byref(exchange.px),
-                                                      _abi.stream_handle(device))
+                                                      _abi.stream_handle(device),
+                                                      C.c_void_p(exchange.side.cuda_stream))
             else:
                 rc = _lib.ggs_rasterize_backward(C.byref(frame), C.byref(g), C.byref(state), C.byref(bi), arena.fn,
                                                  None, C.byref(grads), _abi.stream_handle(device))

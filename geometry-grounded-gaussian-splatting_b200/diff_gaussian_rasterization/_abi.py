@@ -146,10 +146,10 @@ def _load():
     lib.ggs_profile_enable.argtypes = [C.c_int]
     lib.ggs_view_sum_peer.restype = C.c_int
     lib.ggs_view_sum_peer.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(GgsPeerExchange),
-                                      C.c_void_p, C.c_void_p]
+                                      C.c_void_p, C.c_int32, C.c_void_p]
     lib.ggs_rasterize_backward_peer.restype = C.c_int
     lib.ggs_rasterize_backward_peer.argtypes = list(lib.ggs_rasterize_backward.argtypes[:-1]) + [
-        C.POINTER(GgsPeerExchange), C.c_void_p]
+        C.POINTER(GgsPeerExchange), C.c_void_p, C.c_void_p]
     lib.ggs_activate_forward.restype = C.c_int
     lib.ggs_activate_forward.argtypes = [C.c_int64] + [C.c_void_p] * 8
     lib.ggs_activate_backward.restype = C.c_int

@@ -107,6 +107,9 @@ class PeerGradientExchange:
         self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
                                        L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
                                        L["reduce_stage"], L["reduce_stride"])
+        # the colour push and the SH half of the sum run on this stream, concurrent with the per-Gaussian backward
+        self.side = torch.cuda.Stream(self.device)
+        self._d_sh = None  # persistent: written on the side stream, so it must not come from the caching allocator
         torch.cuda.synchronize(self.device)
         self.hdl.barrier(channel=0)
 
@@ -125,22 +128,39 @@ class PeerGradientExchange:
                 self._view(s, "rotations"))
 
     def sum_over_views(self, rs, means3D, SHM):
-        """Call after `ggs_rasterize_backward_peer` has been enqueued on the current stream.  Returns the gradients of
-        (means3D, opacities, scales, rotations, shs) summed over the views of all ranks; the first four are views
-        into the exchange buffer, valid until the next backward."""
+        """Call after `ggs_rasterize_backward_peer(..., side_stream=self.side)` has been enqueued on the current stream.
+        Returns the gradients of (means3D, opacities, scales, rotations, shs) summed over the views of all ranks; all
+        five live in buffers of this object and are valid until the next backward."""
         import ctypes as C
 
         from . import _abi
 
-        d_sh = torch.empty(self.P, SHM, 3, dtype=torch.float32, device=self.device)
-        self.hdl.barrier(channel=0)  # every rank's pushes have landed
-        _abi.check(_abi.lib.ggs_view_sum_peer(self.P, int(rs.sh_degree), int(SHM), _abi.ptr(means3D),
-                                              C.byref(self.px), _abi.ptr(d_sh), _abi.stream_handle(self.device)),
-                   "ggs_view_sum_peer")
-        self.hdl.barrier(channel=1)  # every rank's result region is complete; the stages may be overwritten
+        if self._d_sh is None or self._d_sh.shape[1] != SHM:
+            self._d_sh = torch.empty(self.P, SHM, 3, dtype=torch.float32, device=self.device)
+        d_sh = self._d_sh
+        main = torch.cuda.current_stream(self.device)
+
+        def launch(parts, stream):
+            _abi.check(_abi.lib.ggs_view_sum_peer(self.P, int(rs.sh_degree), int(SHM), _abi.ptr(means3D),
+                                                  C.byref(self.px), _abi.ptr(d_sh), parts,
+                                                  C.c_void_p(stream.cuda_stream)), "ggs_view_sum_peer")
+
+        # side stream, behind the colour push and concurrent with the per-Gaussian backward: once every rank's colour
+        # gradients have landed, the SH gradient summed over views (all reads local)
+        with torch.cuda.stream(self.side):
+            self.hdl.barrier(channel=2)
+            launch(2, self.side)  # GGS_VIEW_SUM_SH
+            sh_done = self.side.record_event()
+        # main stream, behind the per-Gaussian backward and the slice push
+        self.hdl.barrier(channel=0)  # every rank's slices have landed
+        launch(1, main)  # GGS_VIEW_SUM_SLICE
+        main.wait_event(sh_done)
+        self.hdl.barrier(channel=1)  # result regions complete everywhere; every stage may be overwritten
         r = self.layout["recv"]
+        # fresh view objects: autograd's AccumulateGrad adopts a gradient it holds the only reference to, and clones
+        # (192 MB for the SH gradient) one that something else still references
         return (self._view(r, "means3D"), self._view(r, "opacities"), self._view(r, "scales"),
-                self._view(r, "rotations"), d_sh)
+                self._view(r, "rotations"), d_sh.view(self.P, SHM, 3))
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:

@@ -264,11 +264,18 @@ typedef struct GgsPeerExchange {
     int64_t campos_stage_offset;
     int64_t reduce_stage_offset, reduce_stage_stride;
 } GgsPeerExchange;
+/* side_stream (may be NULL: the library then uses a stream of its own): the stream the colour push is enqueued on.
+ * A caller that passes one can chain, on that stream, a barrier and ggs_view_sum_peer(GGS_VIEW_SUM_SH) behind the
+ * push: the SH half of the sum then runs concurrently with the per-Gaussian backward on `stream`, and only
+ * ggs_view_sum_peer(GGS_VIEW_SUM_SLICE) is left for after it.  `parts` selects the halves of the launch. */
+#define GGS_VIEW_SUM_SLICE 1 /* sum this rank's slice of the gradient region and store it to every rank */
+#define GGS_VIEW_SUM_SH 2    /* SH gradient summed over views from the staged colour gradients */
 GGS_API int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussians* gaussians,
                                 const GgsForwardState* state, const GgsBackwardInputs* inputs, GgsAllocFn alloc,
-                                void* user, const GgsGradients* grads, const GgsPeerExchange* exchange, void* stream);
+                                void* user, const GgsGradients* grads, const GgsPeerExchange* exchange, void* stream,
+                                void* side_stream);
 GGS_API int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
-                      const GgsPeerExchange* exchange, float* dL_dsh, void* stream);
+                      const GgsPeerExchange* exchange, float* dL_dsh, int32_t parts, void* stream);
 
 /* ---- fused caller-side activations (opt-in, the reference does this in torch) -------------
  * One pass each way over what gaussian_renderer/__init__.py:62-63 obtains from
