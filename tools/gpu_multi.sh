@@ -19,3 +19,7 @@ python -c "import json,sys; d=json.loads(open('gpurun_out/bench_n${N}_nccl.json'
 [ "${N1:-1}" = "1" ] && timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench n1 rc=$?"
 python -c "import json,sys; d=json.load(open('gpurun_out/bench_n1.json')); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'])"
 fi
+if [ "${C4:-0}" = "1" ]; then
+timeout 400 $TR bench.py --gpus $N --workload c4 --steps 30 --warmup 5 > gpurun_out/bench_n${N}_c4_peer.json 2> gpurun_out/bench_n${N}_c4_peer.err; echo "bench c4 peer rc=$?"
+python -c "import json,sys; d=json.loads(open('gpurun_out/bench_n${N}_c4_peer.json').read().strip().splitlines()[-1]); print('c4', d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'], d['config']['parallelism'][-60:])"
+fi

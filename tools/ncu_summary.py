@@ -8,6 +8,7 @@ ranked by executed warp instructions and stall samples.
 import argparse
 import csv
 import io
+import re
 import subprocess
 
 WANT = [
@@ -46,7 +47,8 @@ def main():
     seen = set()
     for r in rows[2:]:
         name = r[H.index("Kernel Name")]
-        short = name.split("(")[0].split()[-1]
+        m = re.search(r"(\w+)\s*(<[^()]*>)?\s*\(", name)  # "void ggs::k<0, unsigned int, 1>(args)" -> k<0,unsigned int,1>
+        short = (m.group(1) + (m.group(2) or "").replace(", ", ",")) if m else name.split("(")[0].split()[-1]
         grid = r[H.index("Grid Size")] if "Grid Size" in H else ""
         print(f"===== {short}  grid {grid}")
         for key, label in WANT:
