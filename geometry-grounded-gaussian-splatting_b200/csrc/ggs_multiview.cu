@@ -181,17 +181,7 @@ __global__ void __launch_bounds__(MV_THREADS, 5)
     }
     __syncwarp();
     if ((F & 3) == 0) {
-        const int Q = F >> 2;
-        float4* dst = reinterpret_cast<float4*>(dL_dsh + g0 * F);
-        int gi = 0, rem = lane;
-        for (int e = lane; e < ng * Q; e += 32, rem += 32) {
-            while (rem >= Q) {
-                rem -= Q;
-                gi++;
-            }
-            const float* sr = swarp + gi * RS + rem * 4;
-            dst[e] = float4{sr[0], sr[1], sr[2], sr[3]};
-        }
+        store_rows_from_shared(reinterpret_cast<float4*>(dL_dsh + g0 * F), F >> 2, ng, swarp, RS, lane);
     } else {
         float* dst = dL_dsh + g0 * F;
         int gi = 0, rem = lane;
