@@ -188,9 +188,12 @@ class Step:
                 from diff_gaussian_rasterization.parallel import PeerGradientExchange
 
                 mc = {"0": False, "1": True}.get(os.environ.get("GGS_MULTICAST", ""), None)
-                self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc)
-                self.exchange_note = "fused peer-memory sum (ggs_view_sum_peer, %s)" % (
-                    "NVSwitch multimem" if self.exchange.multicast_ptr else "P2P loads/stores")
+                pull = os.environ.get("GGS_PEER_PULL", "0") == "1"
+                self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc, pull_reduce=pull)
+                self.exchange_note = "fused peer-memory sum (ggs_view_sum_peer, %s%s)" % (
+                    "NVSwitch multimem" if self.exchange.multicast_ptr else "P2P loads/stores",
+                    ", slices reduced in the switch" if pull and self.exchange.multicast_ptr else
+                    (", slices pulled" if pull else ""))
             except Exception as ex:  # noqa: BLE001
                 print(f"[bench] peer exchange unavailable ({type(ex).__name__}: {ex}); using NCCL", file=sys.stderr)
                 self.exchange = None
@@ -419,13 +422,25 @@ def main():
     # steps start ----
     stages = None
     t_pre = time.perf_counter()
+
+    def keep_going(done, at_least):
+        """Time-based stop of the untimed pre-run.  Every step of a view-parallel run contains node barriers, so all
+        ranks must run the SAME number of steps: the decision is agreed on with a MAX all-reduce (a rank that launched
+        one step more than its peers would wait in that step's barrier for ever)."""
+        go = done < at_least or time.perf_counter() - t_pre < 1.0
+        if multi:
+            flag = torch.tensor([1 if go else 0], dtype=torch.int32, device=device)
+            torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MAX)
+            go = bool(int(flag.item()))
+        return go
+
     if _abi is not None:
         for _ in range(3):
             step.resident()
         _abi.profile_enable(True)
         acc = {}
         reps = 0
-        while reps < 8 or time.perf_counter() - t_pre < 1.0:
+        while keep_going(reps, 8):
             step.resident()
             t = _abi.profile_read()
             for k, v in t.items():
@@ -440,7 +455,7 @@ def main():
         _abi.profile_enable(False)
     else:
         reps = 0
-        while reps < 11 or time.perf_counter() - t_pre < 1.0:
+        while keep_going(reps, 11):
             step.resident()
             torch.cuda.synchronize()
             reps += 1

@@ -422,7 +422,9 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     GGS_STAGE("gaussian_backward", debug, stream);
     prof_mark(stream, EV_GBWD);
     g_prof.have_bwd = g_prof.on;
-    if (px) {
+    if (px && px->pull_reduce) {
+        GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
+    } else if (px) {
         // reduce-scatter by stores: slice s of this rank's gradient region -> slot `rank` of rank s's reduce stage
         PushSlices ps = {};
         ps.world = px->world;
@@ -612,14 +614,19 @@ int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const
         // everything this launch READS is local: slot r of this rank's colour / camera / reduce stages
         src.rgb[r] = peer_ptr(px, rank, px->rgb_stage_offset + (int64_t)r * px->rgb_stage_stride);
         src.campos[r] = peer_ptr(px, rank, px->campos_stage_offset + (int64_t)r * 4);
-        // indexed by the flat position i of the slice: slot base - lo4
-        job.send[r] = reinterpret_cast<const float4*>(
-                          peer_ptr(px, rank, px->reduce_stage_offset + (int64_t)r * px->reduce_stage_stride)) -
-                      job.lo4;
+        // indexed by the flat position i of the slice: local slot base - lo4, or (pull) rank r's send region itself
+        job.send[r] = px->pull_reduce
+                          ? reinterpret_cast<const float4*>(peer_ptr(px, r, px->send_offset))
+                          : reinterpret_cast<const float4*>(peer_ptr(
+                                px, rank, px->reduce_stage_offset + (int64_t)r * px->reduce_stage_stride)) -
+                                job.lo4;
         job.recv[r] = reinterpret_cast<float4*>(peer_ptr(px, r, px->recv_offset));
     }
-    if (px->multicast_base)
+    if (px->multicast_base) {
         job.mc_recv = reinterpret_cast<float4*>(reinterpret_cast<float*>(px->multicast_base) + px->recv_offset);
+        if (px->pull_reduce)
+            job.mc_send = reinterpret_cast<const float4*>(reinterpret_cast<float*>(px->multicast_base) + px->send_offset);
+    }
     const size_t per_block = 256;
     const size_t want = (job.hi4 - job.lo4 + per_block - 1) / per_block;
     job.blocks = (int)(want < (size_t)(148 * 4) ? want : (size_t)(148 * 4));

@@ -70,7 +70,7 @@ class GgsPeerExchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("peer_buffers", C.POINTER(C.c_uint64)),
                 ("multicast_base", C.c_uint64)] + [(n, C.c_int64) for n in (
         "send_offset", "recv_offset", "reduce_floats", "rgb_stage_offset", "rgb_stage_stride",
-        "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")]
+        "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")] + [("pull_reduce", C.c_int32)]
 
 
 class GgsLayout(C.Structure):

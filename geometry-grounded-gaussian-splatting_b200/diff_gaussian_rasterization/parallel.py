@@ -73,7 +73,7 @@ class PeerGradientExchange:
          gradients; node barrier.
     Wire bytes received per rank and step: 12 B x P x (world - 1) colour gradients + 2 x 44 B x P x (world - 1) / world."""
 
-    def __init__(self, P: int, device, group=None, multicast: bool | None = None):
+    def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool = False):
         import ctypes as C
 
         import torch.distributed._symmetric_memory as symm
@@ -106,7 +106,7 @@ class PeerGradientExchange:
         self.multicast_ptr = mc
         self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
                                        L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
-                                       L["reduce_stage"], L["reduce_stride"])
+                                       L["reduce_stage"], L["reduce_stride"], int(bool(pull_reduce)))
         # the colour push and the SH half of the sum run on this stream, concurrent with the per-Gaussian backward
         self.side = torch.cuda.Stream(self.device)
         self._d_sh = None  # persistent: written on the side stream, so it must not come from the caching allocator

@@ -263,6 +263,10 @@ typedef struct GgsPeerExchange {
     int64_t rgb_stage_offset, rgb_stage_stride;
     int64_t campos_stage_offset;
     int64_t reduce_stage_offset, reduce_stage_stride;
+    /* 0: slices are pushed into the owners' reduce stages and summed from local memory (default).
+     * 1: no slice push; the owner of a slice sums it straight out of every rank's send region -- one
+     *    multimem.ld_reduce per 16 bytes when multicast_base is set (the switch adds), peer loads otherwise. */
+    int32_t pull_reduce;
 } GgsPeerExchange;
 /* side_stream (may be NULL: the library then uses a stream of its own): the stream the colour push is enqueued on.
  * A caller that passes one can chain, on that stream, a barrier and ggs_view_sum_peer(GGS_VIEW_SUM_SH) behind the

@@ -24,8 +24,9 @@ def main():
     sc = bench.make_view(workload, rank, world)
     names = ("means3D", "opacities", "scales", "rotations", "shs")
 
-    def run(peer, multicast=None, reps=1):
+    def run(peer, multicast=None, reps=1, pull=False):
         os.environ["GGS_PEER"] = "1" if peer else "0"
+        os.environ["GGS_PEER_PULL"] = "1" if pull else "0"
         os.environ["GGS_MULTICAST"] = "" if multicast is None else ("1" if multicast else "0")
         step = bench.Step(dgr, sc, dev, allreduce=True)
         for _ in range(reps):
@@ -38,9 +39,9 @@ def main():
     if rank == 0:
         print(f"nccl reference done ({workload}, P={sc.P}, world={world})", flush=True)
     rc = 0
-    for mc in (False, True):
+    for mc, pull in ((False, False), (True, False), (True, True)):
         try:
-            step, got = run(True, mc, reps=3)
+            step, got = run(True, mc, reps=3, pull=pull)
         except Exception as e:  # noqa: BLE001
             print(f"rank {rank}: exchange(multicast={mc}) failed: {type(e).__name__}: {e}", flush=True)
             if mc:
