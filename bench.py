@@ -136,9 +136,14 @@ class ClockSampler:
 
 
 def _quiet_nccl():
-    """NCCL_DEBUG=VERSION makes NCCL print its version on STDOUT, next to the one JSON line this script owes."""
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    """With NCCL_DEBUG=VERSION (and above) NCCL prints its version on STDOUT, next to the one JSON line this script
+    owes.  VERSION carries nothing else, so it is switched off; WARN / INFO are a user's explicit choice and go to
+    stderr through NCCL_DEBUG_FILE."""
+    level = os.environ.get("NCCL_DEBUG", "").upper()
+    if level == "VERSION":
+        os.environ["NCCL_DEBUG"] = "NONE"
+    elif level and level != "NONE":
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 
 def dist_env():
