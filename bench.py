@@ -202,6 +202,16 @@ class Step:
             except Exception as ex:  # noqa: BLE001
                 print(f"[bench] peer exchange unavailable ({type(ex).__name__}: {ex}); using NCCL", file=sys.stderr)
                 self.exchange = None
+            # every rank must take the same path: if the set-up failed anywhere, all ranks fall back to NCCL
+            import torch.distributed as dist
+
+            ok = torch.tensor([1 if self.exchange is not None else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0 and self.exchange is not None:
+                print("[bench] peer exchange set-up failed on another rank; using NCCL", file=sys.stderr)
+                self.exchange = None
+            if self.exchange is None:
+                self.exchange_note = "nccl all-gather(dL_drgb) + nccl all-reduce(11 floats/Gaussian)"
 
     def _settings(self, cam):
         c = self.sc.cam
