@@ -183,6 +183,26 @@ class Oracle:
     def evaluate_sdf(self, **kw):
         return self._sample(True, **kw)
 
+    def sample_depth_backward(self, dL_dcamera_points, *, points3D, means3D, opacities, scales, rotations,
+                              scale_modifier=1.0, viewmatrix=None, projmatrix=None, campos=None, tanfovx=1.0,
+                              tanfovy=1.0, kernel_size=0.0, image_height=0, image_width=0):
+        """Backward of GaussianRasterizer.sample_depth: gradients of sum(camera_points * dL_dcamera_points).  The
+        forward is recomputed with kernel size 0 and the per-Gaussian chain uses `kernel_size`, as the reference's
+        autograd node does (__init__.py:513,606)."""
+        PN, P = points3D.shape[0], means3D.shape[0]
+        keep = [_f(x) for x in (points3D, means3D, opacities, scales, rotations, viewmatrix, projmatrix, campos,
+                                dL_dcamera_points)]
+        pts, me, op, sc, ro, vm, pm, cpos, up = [k[1] for k in keep]
+        g = dict(points3D=torch.zeros(PN, 3), means3D=torch.zeros(P, 3), opacities=torch.zeros(P, 1),
+                 scales=torch.zeros(P, 3), rotations=torch.zeros(P, 4))
+        self.L.ggs_oracle_sample_depth_backward.restype = None
+        self.L.ggs_oracle_sample_depth_backward(
+            self.h, C.c_int(PN), C.c_int(P), C.c_int(int(image_width)), C.c_int(int(image_height)), pts, me, op, sc,
+            C.c_float(scale_modifier), ro, vm, pm, cpos, C.c_float(tanfovx), C.c_float(tanfovy), C.c_float(0.0),
+            C.c_float(kernel_size), up, _ptr(g["points3D"]), _ptr(g["means3D"]), _ptr(g["opacities"]),
+            _ptr(g["scales"]), _ptr(g["rotations"]))
+        return g
+
 
 def scene_kwargs(sc):
     """Keyword arguments of Oracle.forward for a scenes.Scene."""
