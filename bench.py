@@ -146,6 +146,22 @@ def _quiet_nccl():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 
+def watchdog(seconds, rank):
+    """View-parallel runs only: every step holds node-wide barriers, so one stuck rank stalls all of them for good.
+    Fail fast instead of hanging the box: after `seconds` without a result every rank says so and exits non-zero
+    (process exit tears the CUDA context down, which also ends kernels spinning in a barrier)."""
+    def fire():
+        print(f"[bench] rank {rank}: no result after {seconds:.0f} s, a rank is stuck in a collective or a node "
+              "barrier; aborting (GGS_PEER=0 selects the NCCL exchange, GGS_BENCH_WATCHDOG_S changes the limit)",
+              file=sys.stderr, flush=True)
+        os._exit(3)
+
+    t = threading.Timer(seconds, fire)
+    t.daemon = True
+    t.start()
+    return t
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -412,6 +428,7 @@ def main():
 
         _quiet_nccl()
         dist.init_process_group("nccl", device_id=device)
+        guard = watchdog(float(os.environ.get("GGS_BENCH_WATCHDOG_S", "600")), rank)
 
     if args.impl == "ours":
         import diff_gaussian_rasterization as mod
@@ -488,6 +505,7 @@ def main():
 
     if rank != 0:
         if multi:
+            guard.cancel()
             torch.distributed.destroy_process_group()
         return 0
 
@@ -563,8 +581,9 @@ def main():
         line["scene"] = stats
         if not args.no_cpu_baseline and not multi:
             line["cpu_baseline"] = cpu_baseline()
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if multi:
+        guard.cancel()
         torch.distributed.destroy_process_group()
     return 0
 

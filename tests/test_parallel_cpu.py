@@ -133,3 +133,19 @@ def test_exchange_layout_regions_are_disjoint_and_aligned():
             n4 = L["reduce"] // 4
             longest = max(n4 * (s + 1) // world - n4 * s // world for s in range(world))
             assert L["reduce_stride"] // 4 >= longest
+
+
+def test_bench_watchdog_fails_fast_instead_of_hanging():
+    """bench.py's view-parallel runs hold node barriers in every step; a stuck rank must end the run, not hang it."""
+    import subprocess
+    import sys
+
+    code = ("import sys, time; sys.argv=['bench.py']; import bench; bench.watchdog(0.3, 0); time.sleep(30); "
+            "print('still here')")
+    r = subprocess.run([sys.executable, "-c", code], cwd=helpers.ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3, (r.returncode, r.stderr[-400:])
+    assert "still here" not in r.stdout and "stuck" in r.stderr
+    # a cancelled guard does nothing
+    code = "import sys, time; sys.argv=['bench.py']; import bench; g = bench.watchdog(0.2, 0); g.cancel(); time.sleep(0.6)"
+    r = subprocess.run([sys.executable, "-c", code], cwd=helpers.ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-400:]
