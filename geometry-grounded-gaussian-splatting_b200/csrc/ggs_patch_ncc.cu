@@ -1,0 +1,96 @@
+// libggs_patch_ncc.so: patch NCC under the plane-induced homography (include/ggs_patch_ncc.h).
+// One thread per pixel, sums in the reference's order (see ggs_patch_ncc_point.cuh for what differs from
+// warp_patch_ncc_impl.cu).  The intrinsics travel as a kernel parameter (constant bank); the pose stays a device
+// pointer, as in the reference, so that the caller needs no host synchronisation; [P,3] rows go through shared memory
+// so that global traffic is coalesced; invalid patches stop early.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ggs_patch_ncc.h"
+#include "ggs_patch_ncc_point.cuh"
+
+#define GGS_NCC_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace ggs {
+namespace ncc {
+
+constexpr int THREADS = 128;
+
+__global__ void __launch_bounds__(THREADS)
+warp_patch_kernel(Pair pair, const float* __restrict__ R, const float* __restrict__ T, const long long P,
+                  const float* __restrict__ depths,
+                  const float* __restrict__ normals, const int2* __restrict__ uvs,
+                  const float* __restrict__ image_r, const float* __restrict__ image_n, float* __restrict__ ncc,
+                  float* __restrict__ grad_depths, float* __restrict__ grad_normals, uint8_t* __restrict__ valid) {
+    __shared__ float rows[THREADS * 3];
+    __shared__ float samples[SAMPLES * THREADS];  // [sample][thread]: conflict-free columns
+    const long long first = static_cast<long long>(blockIdx.x) * THREADS;
+    const int here = static_cast<int>(min(static_cast<long long>(THREADS), P - first));
+    const int t = threadIdx.x;
+    for (int i = t; i < here * 3; i += THREADS) rows[i] = __ldg(normals + first * 3 + i);
+    __syncthreads();
+    PointResult r = {0.f, 0.f, 0.f, 0.f, 0.f, false};
+    for (int i = 0; i < 9; i++) pair.R[i] = __ldg(R + i);  // uniform addresses: one broadcast transaction each
+    for (int i = 0; i < 3; i++) pair.T[i] = __ldg(T + i);
+    if (t < here) {
+        const int2 uv = __ldg(uvs + first + t);
+        const V3 n = v3(rows[3 * t], rows[3 * t + 1], rows[3 * t + 2]);
+        r = evaluate_point<THREADS>(pair, uv.x, uv.y, __ldg(depths + first + t), n, image_r, image_n, samples + t);
+        ncc[first + t] = r.ncc;
+        grad_depths[first + t] = r.d_depth;
+        valid[first + t] = r.valid ? 1 : 0;
+    }
+    __syncthreads();
+    if (t < here) {
+        rows[3 * t] = r.d_nx;
+        rows[3 * t + 1] = r.d_ny;
+        rows[3 * t + 2] = r.d_nz;
+    }
+    __syncthreads();
+    for (int i = t; i < here * 3; i += THREADS) grad_normals[first * 3 + i] = rows[i];
+}
+
+}  // namespace ncc
+}  // namespace ggs
+
+static thread_local char g_error[256] = "";
+
+static int fail(int code, const char* what) {
+    snprintf(g_error, sizeof(g_error), "%s", what);
+    return code;
+}
+
+GGS_NCC_EXPORT int ggs_ncc_abi_version(void) { return GGS_NCC_ABI_VERSION; }
+GGS_NCC_EXPORT const char* ggs_ncc_last_error(void) { return g_error; }
+
+GGS_NCC_EXPORT int ggs_ncc_warp_patch(const GgsNccPair* pair, int64_t P, const float* depths, const float* normals,
+                                      const int32_t* uvs, const float* image_r, const float* image_n, float* ncc,
+                                      float* grad_depths, float* grad_normals, uint8_t* valid, void* stream) {
+    if (!pair) return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: pair is null");
+    if (!pair->R || !pair->T) return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: null pose");
+    if (P < 0) return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: negative point count");
+    if (P == 0) return 0;
+    if (!depths || !normals || !uvs || !image_r || !image_n || !ncc || !grad_depths || !grad_normals || !valid)
+        return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: null buffer");
+    if (pair->height_r <= 0 || pair->width_r <= 0 || pair->height_n <= 0 || pair->width_n <= 0)
+        return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: empty image");
+    ggs::ncc::Pair k;
+    for (int i = 0; i < 9; i++) k.R[i] = 0.f;  // read on the device
+    for (int i = 0; i < 3; i++) k.T[i] = 0.f;
+    k.fx_r = pair->fx_r; k.fy_r = pair->fy_r; k.cx_r = pair->cx_r; k.cy_r = pair->cy_r;
+    k.fx_n = pair->fx_n; k.fy_n = pair->fy_n; k.cx_n = pair->cx_n; k.cy_n = pair->cy_n;
+    k.h_r = pair->height_r; k.w_r = pair->width_r; k.h_n = pair->height_n; k.w_n = pair->width_n;
+    const long long blocks = (P + ggs::ncc::THREADS - 1) / ggs::ncc::THREADS;
+    if (blocks > 0x7fffffffLL) return fail(GGS_NCC_EINVAL, "ggs_ncc_warp_patch: too many points for one launch");
+    ggs::ncc::warp_patch_kernel<<<static_cast<unsigned>(blocks), ggs::ncc::THREADS, 0,
+                                  static_cast<cudaStream_t>(stream)>>>(
+        k, pair->R, pair->T, P, depths, normals, reinterpret_cast<const int2*>(uvs), image_r, image_n, ncc, grad_depths,
+        grad_normals, valid);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(g_error, sizeof(g_error), "ggs_ncc_warp_patch: launch failed: %s", cudaGetErrorString(e));
+        return GGS_NCC_ECUDA;
+    }
+    return 0;
+}

@@ -11,6 +11,9 @@ land in the repo, under the git-ignored oracle/_ref/:
     oracle/_ref/ref_dgr/__init__.py  the reference's Python wrapper (an install
                                      artefact, like `pip install --target`)
 
+    oracle/_ref/ref_wpn/_C.so        the reference's warp-patch-ncc extension (submodules/warp-patch-ncc,
+    oracle/_ref/ref_wpn/__init__.py  setup.py:6-20: -O3 --use_fast_math), importable as `ref_wpn`
+
 The package is importable as `ref_dgr` (see oracle/ref_loader.py) so it can
 live beside the drop-in `diff_gaussian_rasterization` in one process.
 Needs /root/reference; on the GPU box only the prebuilt files are used.
@@ -70,5 +73,32 @@ def build(force: bool = False) -> str:
     return so
 
 
+REF_NCC = "/root/reference/submodules/warp-patch-ncc"
+OUT_NCC = os.path.join(HERE, "_ref", "ref_wpn")
+
+
+def build_ncc(force: bool = False) -> str:
+    """The reference's patch-NCC extension, same recipe: its three sources, its two nvcc flags."""
+    so = os.path.join(OUT_NCC, "_C.so")
+    if os.path.exists(so) and not force:
+        return so
+    if not os.path.isdir(REF_NCC):
+        raise RuntimeError("reference sources not present at " + REF_NCC)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0")
+    os.environ.setdefault("MAX_JOBS", str(os.cpu_count() or 4))
+    from torch.utils.cpp_extension import load
+
+    bdir = BUILD + "_ncc"
+    os.makedirs(bdir, exist_ok=True)
+    srcs = ["cuda_warp_patch_ncc/warp_patch_ncc_impl.cu", "warp_patch_ncc.cu", "ext.cpp"]
+    load(name="_C", sources=[os.path.join(REF_NCC, s) for s in srcs], extra_cuda_cflags=["-O3", "--use_fast_math"],
+         extra_include_paths=[REF_NCC], build_directory=bdir, is_python_module=False, verbose=True)
+    os.makedirs(OUT_NCC, exist_ok=True)
+    shutil.copyfile(os.path.join(bdir, "_C.so"), so)
+    shutil.copyfile(os.path.join(REF_NCC, "warp_patch_ncc", "__init__.py"), os.path.join(OUT_NCC, "__init__.py"))
+    return so
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(build_ncc(force="--force" in sys.argv))

@@ -582,3 +582,4 @@ int64_t ggs_oracle_num_rendered(void* h) { return ((Oracle*)h)->D; }
 
 #include "ggs_oracle_backward.inc"
 #include "ggs_oracle_points.inc"
+#include "ggs_oracle_ncc.inc"

@@ -19,7 +19,8 @@ _lib = None
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_HERE, f) for f in ("ggs_oracle.c", "ggs_oracle_backward.inc", "ggs_oracle_points.inc")]
+    srcs = [os.path.join(_HERE, f) for f in ("ggs_oracle.c", "ggs_oracle_backward.inc", "ggs_oracle_points.inc",
+                                             "ggs_oracle_ncc.inc")]
     stale = (not os.path.exists(_SO)) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
@@ -202,6 +203,28 @@ class Oracle:
             C.c_float(kernel_size), up, _ptr(g["points3D"]), _ptr(g["means3D"]), _ptr(g["opacities"]),
             _ptr(g["scales"]), _ptr(g["rotations"]))
         return g
+
+
+def warp_patch_ncc(depths, normals, uvs, R, T, image_r, image_n, fx_r, fy_r, cx_r, cy_r, fx_n, fy_n, cx_n, cy_n,
+                   debug=False):
+    """The reference's `_C.warp_patch_ncc` (submodules/warp-patch-ncc/warp_patch_ncc.cu:5-57) on CPU tensors:
+    (ncc [P], grad_depths [P], grad_normals [P,3], valid [P] bool).  R is read as the reference reads it: 9 floats
+    in memory order, columns of the rotation."""
+    L = lib()
+    P = int(depths.shape[0])
+    keep = [_f(x) for x in (depths, normals, R, T, image_r, image_n)]
+    d, n, r, t, ir, im = [k[1] for k in keep]
+    uv = uvs.detach().to("cpu", torch.int32).contiguous()
+    ncc, gd, gn = torch.zeros(P), torch.zeros(P), torch.zeros(P, 3)
+    valid = torch.zeros(P, dtype=torch.uint8)
+    L.ggs_oracle_warp_patch_ncc.restype = None
+    if P:
+        L.ggs_oracle_warp_patch_ncc(
+            C.c_int(P), d, n, _ptr(uv), r, t, ir, im, *[C.c_float(float(v)) for v in (fx_r, fy_r, cx_r, cy_r, fx_n, fy_n,
+                                                                                    cx_n, cy_n)],
+            C.c_int(int(image_r.shape[0])), C.c_int(int(image_r.shape[1])), C.c_int(int(image_n.shape[0])),
+            C.c_int(int(image_n.shape[1])), _ptr(ncc), _ptr(gd), _ptr(gn), _ptr(valid))
+    return ncc, gd, gn, valid.bool()
 
 
 def scene_kwargs(sc):

@@ -25,3 +25,19 @@ def load():
     if _REF_DIR not in sys.path:
         sys.path.insert(0, _REF_DIR)
     return importlib.import_module("ref_dgr")
+
+
+def ncc_available() -> bool:
+    return os.path.exists(os.path.join(_REF_DIR, "ref_wpn", "_C.so"))
+
+
+def load_ncc():
+    """The compiled reference `warp_patch_ncc` module (submodules/warp-patch-ncc) as `ref_wpn`."""
+    if not ncc_available():
+        raise ImportError("oracle/_ref/ref_wpn/_C.so not built; run `python oracle/build_ref.py` where "
+                          "/root/reference exists")
+    import torch  # noqa: F401
+
+    if _REF_DIR not in sys.path:
+        sys.path.insert(0, _REF_DIR)
+    return importlib.import_module("ref_wpn")

@@ -1,0 +1,149 @@
+"""Patch NCC on the GPU: the CUDA kernel behind `warp_patch_ncc.warp_patch_ncc` against the
+compiled reference (oracle/_ref/ref_wpn, when shipped) and against the IEEE C oracle, on seeded synthetic view pairs.
+
+First hardware run of this kernel happens after it was written (no GPU time was left), so the bounds below are the
+ones arithmetic can guarantee, not measured ones: `valid` may flip only on knife-edge patches, values may differ by
+what float32 cancellation in the variance amplifies (tests/test_patch_ncc_cpu.py measures 5.6e-4 worst, 9e-6 median,
+between float32 and float64).  The measured differences are written to gpurun_out/ncc_parity.json to tighten them."""
+import json
+import os
+
+import pytest
+import torch
+
+import helpers as H
+import ncc_scenes
+
+pytestmark = pytest.mark.gpu
+
+SCENES = {
+    "same_size": dict(n=20000),
+    "other_size": dict(height=96, width=128, neighbour_size=(110, 150), seed=11, shift=(12.0, 6.0), n=20000),
+    "large": dict(height=545, width=980, seed=17, n=200000),
+}
+
+
+def _ours(sc, device):
+    import warp_patch_ncc as ours
+
+    a = ncc_scenes.args_of(sc, device)
+    return ours._run(a[0], a[1], a[2], a[5], a[6], ours.WarpParams(a[3], a[4], *a[7:], False))
+
+
+def _report(tag, arm, stats):
+    out = os.path.join(H.ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    path = os.path.join(out, "ncc_parity.json")
+    data = {}
+    if os.path.exists(path):
+        with open(path) as fh:
+            data = json.load(fh)
+    data[f"{tag}/{arm}"] = stats
+    with open(path, "w") as fh:
+        json.dump(data, fh, indent=1, sort_keys=True)
+
+
+def _compare(got, want, tag, arm, flip_frac, value_abs, grad_rel):
+    g = [t.cpu() for t in got]
+    w = [t.cpu() for t in want]
+    n = len(w[3])
+    flips = int((g[3] != w[3]).sum())
+    both = g[3] & w[3]
+    stats = {"points": n, "valid": int(w[3].sum()), "valid_flips": flips}
+    dv = (g[0] - w[0]).abs()[both]
+    stats["ncc_max_abs"] = float(dv.max())
+    stats["ncc_median_abs"] = float(dv.median())
+    stats["bit_equal"] = bool(all(torch.equal(a, b) for a, b in zip(g, w)))
+    for a, b, name in ((g[1], w[1], "grad_depths"), (g[2], w[2], "grad_normals")):
+        scale = float(b[both].abs().max())
+        d = (a - b).abs()[both] / scale
+        stats[name + "_max_rel"] = float(d.max())
+        stats[name + "_median_rel"] = float(d.median())
+    _report(tag, arm, stats)
+    print(tag, arm, stats)
+    assert stats["valid"] > n // 2, "scene does not exercise the kernel"
+    assert flips <= max(2, int(flip_frac * n)), stats
+    assert stats["ncc_max_abs"] <= value_abs and stats["ncc_median_abs"] <= value_abs / 20, stats
+    for name in ("grad_depths", "grad_normals"):
+        assert stats[name + "_max_rel"] <= grad_rel and stats[name + "_median_rel"] <= grad_rel / 20, (name, stats)
+    # invalid patches are exactly zero in every output
+    for t in g[:3]:
+        assert float(t[~g[3]].abs().max() if (~g[3]).any() else 0.0) == 0.0
+
+
+@pytest.mark.parametrize("tag", sorted(SCENES))
+def test_patch_ncc_vs_c_oracle(tag, device):
+    from oracle import oracle as O
+
+    sc = ncc_scenes.make_pair(**SCENES[tag])
+    got = _ours(sc, device)
+    torch.cuda.synchronize()
+    want = O.warp_patch_ncc(*ncc_scenes.args_of(sc))
+    _compare(got, want, tag, "c_oracle", flip_frac=2e-3, value_abs=5e-3, grad_rel=2e-2)
+
+
+@pytest.mark.parametrize("tag", sorted(SCENES))
+def test_patch_ncc_vs_reference(tag, device):
+    from oracle import ref_loader
+
+    if not ref_loader.ncc_available():
+        pytest.skip("oracle/_ref/ref_wpn not shipped")
+    ref = ref_loader.load_ncc()
+    sc = ncc_scenes.make_pair(**SCENES[tag])
+    a = ncc_scenes.args_of(sc, device)
+    want = ref._C.warp_patch_ncc(*a, False)  # (ncc, grad_depths, grad_normals, valid)
+    torch.cuda.synchronize()
+    got = _ours(sc, device)
+    torch.cuda.synchronize()
+    _compare(got, want, tag, "reference", flip_frac=1e-3, value_abs=2e-3, grad_rel=1e-2)
+
+
+def test_patch_ncc_autograd_surface(device):
+    """Same call and autograd behaviour as the reference module (warp_patch_ncc/__init__.py:20-84): gradients are the
+    saved forward-mode derivatives times the incoming gradient; uvs, images and the pose get none."""
+    import warp_patch_ncc as ours
+
+    sc = ncc_scenes.make_pair(n=5000, seed=23)
+    a = ncc_scenes.args_of(sc, device)
+    depths = a[0].clone().requires_grad_(True)
+    normals = a[1].clone().requires_grad_(True)
+    R_view = a[3].t().contiguous().t()  # what the trainer passes: a transposed, non-contiguous view
+    assert not R_view.is_contiguous()
+    ncc, valid = ours.warp_patch_ncc(depths, normals, a[2], R_view, *a[4:], False)
+    assert ncc.shape == (5000,) and valid.shape == (5000,) and valid.dtype == torch.bool
+    assert not valid.requires_grad
+    w = torch.randn(5000, device=device, generator=torch.Generator(device=device).manual_seed(1))
+    (ncc * w).sum().backward()
+    raw = ours._run(a[0], a[1], a[2], a[5], a[6], ours.WarpParams(a[3], a[4], *a[7:], False))
+    assert torch.equal(ncc.detach(), raw[0]) and torch.equal(valid, raw[3])
+    assert torch.equal(depths.grad, w * raw[1])
+    assert torch.equal(normals.grad, w.unsqueeze(-1) * raw[2])
+    # the loss of utils/loss_utils.py:257-264 runs on top of it
+    loss = torch.clamp(1 - ncc.detach(), 0.0, 2.0)[valid].mean()
+    assert bool(torch.isfinite(loss))
+
+
+def test_patch_ncc_edge_cases(device):
+    import warp_patch_ncc as ours
+
+    sc = ncc_scenes.make_pair(n=3000, seed=29)
+    a = ncc_scenes.args_of(sc, device)
+    one = ours.warp_patch_ncc(*a, True)  # debug: synchronises, as the reference's CHECK_CUDA does
+    two = ours.warp_patch_ncc(*a, False)
+    assert torch.equal(one[0], two[0]) and torch.equal(one[1], two[1])  # deterministic
+    # no points
+    e = ours.warp_patch_ncc(a[0][:0], a[1][:0], a[2][:0], *a[3:], False)
+    assert e[0].shape == (0,) and e[1].shape == (0,)
+    # a count that is not a multiple of the block size, and a single point
+    for n in (1, 127, 129):
+        part = ours.warp_patch_ncc(a[0][:n], a[1][:n], a[2][:n], *a[3:], False)
+        assert torch.equal(part[0], two[0][:n]) and torch.equal(part[1], two[1][:n])
+    # a degenerate plane (normal orthogonal to the ray: distance 0) must not poison its neighbours
+    d = a[0].clone()
+    d[10] = 0.0
+    bad = ours.warp_patch_ncc(d, *a[1:], False)
+    keep = torch.ones(3000, dtype=torch.bool, device=device)
+    keep[10] = False
+    assert torch.equal(bad[0][keep], two[0][keep]) and not bool(bad[1][10]) and float(bad[0][10]) == 0.0
+    with pytest.raises(RuntimeError, match="normals must have dimensions"):
+        ours.warp_patch_ncc(a[0], a[1].reshape(-1), *a[2:], False)
