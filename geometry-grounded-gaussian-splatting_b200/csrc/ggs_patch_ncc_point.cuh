@@ -9,7 +9,7 @@
 // warped outside the image instead of sampling all 49 positions and discarding them.  The accumulation order of
 // every sum is the reference's (dv outer, du inner, one accumulator each), so results round alike.
 //
-// The routine is host/device so that the very code the kernel runs can be checked on a CPU against the C oracle
+// The routine is host/device so that the very code the kernel runs can be checked on a CPU by the test suite
 // (tests/test_patch_ncc_cpu.py builds it with g++); the product only ever calls it from the kernel.
 #pragma once
 #include <math.h>

@@ -106,11 +106,12 @@ def test_either_or_argument_rules():
 
 def test_product_never_imports_oracle():
     """The product package must not reference the oracle (test infrastructure) or any CPU fallback."""
-    pkg = os.path.join(H.PKG, "diff_gaussian_rasterization")
-    for fn in os.listdir(pkg):
-        if fn.endswith(".py"):
-            src = open(os.path.join(pkg, fn)).read()
-            assert "oracle" not in src.replace("Oracle A", ""), fn
+    for name in ("diff_gaussian_rasterization", "warp_patch_ncc"):
+        pkg = os.path.join(H.PKG, name)
+        for fn in os.listdir(pkg):
+            if fn.endswith(".py"):
+                src = open(os.path.join(pkg, fn)).read()
+                assert "oracle" not in src.replace("Oracle A", ""), fn
     for fn in os.listdir(os.path.join(H.PKG, "csrc")):
         if fn.endswith((".cu", ".cuh")):
             assert "oracle" not in open(os.path.join(H.PKG, "csrc", fn)).read(), fn
