@@ -160,3 +160,29 @@ def test_library_exports_what_the_header_declares():
         ours.warp_patch_ncc(*ncc_scenes.args_of(sc), False)
     with pytest.raises(RuntimeError, match="normals must have dimensions"):
         ours.warp_patch_ncc(sc["depths"], sc["normals"].reshape(-1), *ncc_scenes.args_of(sc)[2:], False)
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 700])
+def test_kernel_source_under_emulation_matches_oracle(n, tmp_path_factory):
+    """warp_patch_kernel's SOURCE run on the host (tests/native/cuda_emu.h: one OS thread per CUDA thread, real
+    barriers), launched as ggs_ncc_warp_patch launches it: shared-memory staging of the [P,3] rows, partial last
+    block, every output element written."""
+    from oracle import oracle as O
+
+    so = str(tmp_path_factory.mktemp("ncc_emu") / "patch_ncc_emulated.so")
+    native = os.path.join(H.ROOT, "tests", "native")
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-pthread", "-shared", "-fPIC", "-I" + CSRC, "-I" + native,
+                           "-o", so, os.path.join(native, "patch_ncc_emulated.cpp")])
+    lib = C.CDLL(so)
+    sc = ncc_scenes.make_pair(n=n, seed=31)
+    want = O.warp_patch_ncc(*ncc_scenes.args_of(sc))
+    out = [torch.full((n,), 7.0), torch.full((n,), 7.0), torch.full((n, 3), 7.0), torch.full((n,), 9, dtype=torch.uint8)]
+    intr = torch.tensor([sc[k] for k in INTR], dtype=torch.float32)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    lib.ggs_test_ncc_kernel(C.c_longlong(n), p(sc["depths"]), p(sc["normals"]), p(sc["uvs"]), p(sc["R"]), p(sc["T"]),
+                            p(sc["image_r"]), p(sc["image_n"]), p(intr), *[int(v) for v in sc["image_r"].shape],
+                            *[int(v) for v in sc["image_n"].shape], p(out[0]), p(out[1]), p(out[2]), p(out[3]))
+    assert int(out[3].max()) <= 1
+    assert torch.equal(out[3].bool(), want[3])
+    for a, b, name in zip(out[:3], want[:3], ("ncc", "grad_depths", "grad_normals")):
+        assert torch.equal(a, b), name
