@@ -106,7 +106,7 @@ def test_either_or_argument_rules():
 
 def test_product_never_imports_oracle():
     """The product package must not reference the oracle (test infrastructure) or any CPU fallback."""
-    for name in ("diff_gaussian_rasterization", "warp_patch_ncc"):
+    for name in ("diff_gaussian_rasterization", "warp_patch_ncc", "fused_ssim"):
         pkg = os.path.join(H.PKG, name)
         for fn in os.listdir(pkg):
             if fn.endswith(".py"):

@@ -1,0 +1,86 @@
+"""Fused SSIM without a GPU: the kernels' SOURCE run on the host under tests/native/cuda_emu.h
+against the reference's torch statement of SSIM in float64, and the C ABI of libggs_ssim.so (symbols and host-side
+queries only: no compute without a GPU)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+import helpers as H
+import ssim_reference as R
+
+CSRC = os.path.join(H.ROOT, "geometry-grounded-gaussian-splatting_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def emulated(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("ssim_emu") / "ssim_emulated.so")
+    native = os.path.join(H.ROOT, "tests", "native")
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-pthread", "-shared", "-fPIC", "-I" + CSRC, "-I" + native,
+                           "-o", so, os.path.join(native, "ssim_emulated.cpp")])
+    return C.CDLL(so)
+
+
+CASES = [  # (B, C, H, W, padding): several tiles, partial tiles, several planes, the smallest valid image
+    (1, 3, 40, 50, "valid"), (1, 3, 40, 50, "same"), (2, 1, 33, 64, "valid"), (1, 1, 75, 70, "same"),
+    (1, 2, 12, 11, "valid"), (1, 1, 5, 7, "same"),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "x".join(map(str, c)))
+def test_kernel_sources_under_emulation_match_torch_float64(case, emulated):
+    B, Ch, Hh, W, padding = case
+    img1, img2 = R.image_pair((B, Ch, Hh, W), seed=3 + Hh)
+    want, want_grad = R.value_and_grad(img1, img2, padding, upstream=0.7)
+    planes, valid = B * Ch, 1 if padding == "valid" else 0
+    rh, rw = (Hh - 10, W - 10) if valid else (Hh, W)
+    tiles = ((rh + 31) // 32) * ((rw + 31) // 32) * planes
+    maps = [torch.full((planes, Hh, W), float("nan")) for _ in range(3)]
+    partials, mean = torch.zeros(tiles), torch.zeros(1)
+    window = R.gaussian().float()
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    emulated.ggs_test_ssim_forward(planes, Hh, W, valid, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]),
+                                   p(maps[2]), p(partials), p(mean))
+    assert abs(float(mean) - float(want)) <= 1e-6 * abs(float(want))
+    inside = torch.zeros(Hh, W, dtype=torch.bool)
+    inside[(5 if valid else 0):(Hh - 5 if valid else Hh), (5 if valid else 0):(W - 5 if valid else W)] = True
+    for m in maps:  # written exactly on the map region
+        assert not bool(torch.isnan(m[:, inside]).any()) and bool(torch.isnan(m[:, ~inside]).all())
+    grad = torch.full((planes, Hh, W), float("nan"))
+    upstream = torch.tensor([0.7])
+    emulated.ggs_test_ssim_backward(planes, Hh, W, valid, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]),
+                                    p(maps[2]), p(upstream), p(grad))
+    assert not bool(torch.isnan(grad).any())
+    err = float((grad.reshape(B, Ch, Hh, W).double() - want_grad).abs().max() / want_grad.abs().max())
+    assert err <= 1e-5, err
+
+
+def test_library_exports_what_the_header_declares():
+    import fused_ssim as ours
+
+    with open(os.path.join(H.ROOT, "include", "ggs_ssim.h")) as fh:
+        text = re.sub(r"/\*.*?\*/", "", fh.read(), flags=re.S)
+    declared = set(re.findall(r"\b(ggs_ssim_\w+)\s*\(", text))
+    assert declared == set(ours.EXPORTS), declared ^ set(ours.EXPORTS)
+    lib = C.CDLL(ours.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.ggs_ssim_abi_version() == ours.ABI_VERSION
+    assert C.sizeof(ours.GgsSsimPlan) == 4 * 4 + 2 * 4 + 11 * 4
+    # host-side query: tiles of the map region times planes
+    plan = ours.make_plan((1, 3, 822, 1237), "valid", 0.01 ** 2, 0.03 ** 2)
+    assert ours._lib.ggs_ssim_partials(C.byref(plan)) == 3 * ((812 + 31) // 32) * ((1227 + 31) // 32)
+    plan = ours.make_plan((2, 3, 64, 64), "same", 0.01 ** 2, 0.03 ** 2)
+    assert ours._lib.ggs_ssim_partials(C.byref(plan)) == 6 * 2 * 2
+    plan = ours.make_plan((1, 1, 10, 64), "valid", 0.01 ** 2, 0.03 ** 2)  # no map left
+    assert ours._lib.ggs_ssim_partials(C.byref(plan)) < 0
+    assert torch.equal(ours.gaussian_window(), R.gaussian().float())
+    assert abs(float(sum(plan.window)) - 1.0) < 1e-6
+    img1, img2 = R.image_pair((1, 3, 20, 20), seed=1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ours.fused_ssim(img1, img2, padding="valid")
+    with pytest.raises(AssertionError):
+        ours.fused_ssim(img1, img2, padding="reflect")
