@@ -12,6 +12,16 @@ for p in (ROOT, PKG, os.path.dirname(os.path.abspath(__file__))):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "first_hardware_run: GPU test of code that has not run on hardware yet; such "
+                            "tests are collected last so that a surprise in them cannot hide the measured ones")
+
+
+def pytest_collection_modifyitems(config, items):
+    def rank(item):  # stable sort: unmarked tests keep their order and run first; marked ones by their `order`
+        m = item.get_closest_marker("first_hardware_run")
+        return 0 if m is None else 1 + int(m.kwargs.get("order", 0))
+
+    items.sort(key=rank)
 
 
 def _lib_built():

@@ -14,7 +14,7 @@ import torch
 import helpers as H
 import ncc_scenes
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.first_hardware_run(order=3)]
 
 SCENES = {
     "same_size": dict(n=20000),

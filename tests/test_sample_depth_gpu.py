@@ -118,6 +118,7 @@ def test_evaluate_sdf_vs_reference(tag, device, ref_module):
         assert err <= H.IMG_TOL, f"{what}: max rel err {err:.3e} ({bad} above tolerance)"
 
 
+@pytest.mark.first_hardware_run(order=2)
 @pytest.mark.parametrize("tag", ["tiny", "c1_k01"])
 def test_sample_depth_backward_vs_c_oracle(tag, device):
     """CUDA sample_depth backward against the IEEE C restatement (oracle/ggs_oracle_points.inc), including a scene

@@ -7,7 +7,7 @@ import torch
 import helpers as H  # noqa: F401  (sys.path)
 import ssim_reference as R
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.first_hardware_run(order=1)]
 
 CASES = [
     (1, 3, 822, 1237, "valid"),  # what train.py:189 passes at the headline resolution
