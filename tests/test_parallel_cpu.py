@@ -149,3 +149,20 @@ def test_bench_watchdog_fails_fast_instead_of_hanging():
     code = "import sys, time; sys.argv=['bench.py']; import bench; g = bench.watchdog(0.2, 0); g.cancel(); time.sleep(0.6)"
     r = subprocess.run([sys.executable, "-c", code], cwd=helpers.ROOT, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr[-400:]
+
+
+def test_bench_reference_arm_runs_on_rank_zero_only_and_needs_a_gpu():
+    """Contract of `bench.py --impl reference` under torchrun: ranks other than 0 exit 0 without work; and no arm
+    pretends to run without a CUDA device."""
+    import subprocess
+    import sys
+
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    r = subprocess.run([sys.executable, "bench.py", "--impl", "reference", "--gpus", "2", "--steps", "1"],
+                       cwd=helpers.ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip() == "", (r.returncode, r.stdout[-200:], r.stderr[-200:])
+    if not torch.cuda.is_available():
+        env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+        r = subprocess.run([sys.executable, "bench.py", "--steps", "1"], cwd=helpers.ROOT, env=env,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode != 0 and "no CPU path" in (r.stderr + r.stdout)
