@@ -25,6 +25,7 @@ constexpr int HALO = TAPS / 2;           // 5
 constexpr int TILE = 32;                 // output tile edge
 constexpr int SPAN = TILE + 2 * HALO;    // 42: input tile edge
 constexpr int THREADS = 256;
+constexpr int ROWS = TILE * TILE / THREADS;  // 4: rows of one column a thread owns in the vertical pass
 
 struct Plan {
     int planes, height, width;  // planes = batch * channels
@@ -102,32 +103,42 @@ forward_kernel(const Plan plan, const float* __restrict__ img1, const float* __r
     }
     __syncthreads();
 
+    // vertical pass: each thread owns ROWS consecutive rows of one column, so the ROWS + 10 inputs of a moment are
+    // read from shared memory once and reused by the ROWS windows (sums still run k = 0..10, so nothing rounds anew)
     float local = 0.f;
-    for (int i = tid; i < TILE * TILE; i += THREADS) {
-        const int y = i / TILE, x = i - y * TILE;
-        const int cy = oy0 + y, cx = ox0 + x;
-        if (cy >= r.y1 || cx >= r.x1) continue;
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    {
+        const int x = tid % TILE, y0 = (tid / TILE) * ROWS;
+        float m[5][ROWS];
 #pragma unroll
-        for (int k = 0; k < TAPS; k++) {
-            const float w = plan.window[k];
-            mu1 += w * h[0][y + k][x];
-            mu2 += w * h[1][y + k][x];
-            e11 += w * h[2][y + k][x];
-            e22 += w * h[3][y + k][x];
-            e12 += w * h[4][y + k][x];
+        for (int q = 0; q < 5; q++) {
+            float v[ROWS + TAPS - 1];
+#pragma unroll
+            for (int j = 0; j < ROWS + TAPS - 1; j++) v[j] = h[q][y0 + j][x];
+#pragma unroll
+            for (int r2 = 0; r2 < ROWS; r2++) {
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < TAPS; k++) acc += plan.window[k] * v[r2 + k];
+                m[q][r2] = acc;
+            }
         }
-        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2;
-        const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1 * mu2;
-        const float A = mu1_sq + mu2_sq + plan.c1, B = sigma1_sq + sigma2_sq + plan.c2;
-        const float C = 2.f * mu1 * mu2 + plan.c1, D = 2.f * sigma12 + plan.c2;
-        local += (C * D) / (A * B);
-        if (dm_dmu1) {
-            const size_t at = base + static_cast<size_t>(cy) * W + cx;
-            dm_dmu1[at] = (mu2 * 2.f * D) / (A * B) - (mu2 * 2.f * C) / (A * B) - (mu1 * 2.f * C * D) / (A * A * B) +
-                          (mu1 * 2.f * C * D) / (A * B * B);
-            dm_dsigma1_sq[at] = (-C * D) / (A * B * B);
-            dm_dsigma12[at] = (2.f * C) / (A * B);
+#pragma unroll
+        for (int r2 = 0; r2 < ROWS; r2++) {
+            const int cy = oy0 + y0 + r2, cx = ox0 + x;
+            if (cy >= r.y1 || cx >= r.x1) continue;
+            const float mu1 = m[0][r2], mu2 = m[1][r2], e11 = m[2][r2], e22 = m[3][r2], e12 = m[4][r2];
+            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2;
+            const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1 * mu2;
+            const float A = mu1_sq + mu2_sq + plan.c1, B = sigma1_sq + sigma2_sq + plan.c2;
+            const float C = 2.f * mu1 * mu2 + plan.c1, D = 2.f * sigma12 + plan.c2;
+            local += (C * D) / (A * B);
+            if (dm_dmu1) {
+                const size_t at = base + static_cast<size_t>(cy) * W + cx;
+                dm_dmu1[at] = (mu2 * 2.f * D) / (A * B) - (mu2 * 2.f * C) / (A * B) - (mu1 * 2.f * C * D) / (A * A * B) +
+                              (mu1 * 2.f * C * D) / (A * B * B);
+                dm_dsigma1_sq[at] = (-C * D) / (A * B * B);
+                dm_dsigma12[at] = (2.f * C) / (A * B);
+            }
         }
     }
     const float total = block_sum(local, red);
@@ -185,20 +196,30 @@ backward_kernel(const Plan plan, const float* __restrict__ img1, const float* __
     }
     __syncthreads();
 
-    for (int i = tid; i < TILE * TILE; i += THREADS) {
-        const int y = i / TILE, x = i - y * TILE;
-        const int py = oy0 + y, px = ox0 + x;
-        if (py >= H || px >= W) continue;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+    {
+        const int x = tid % TILE, y0 = (tid / TILE) * ROWS;
+        float m[3][ROWS];
 #pragma unroll
-        for (int k = 0; k < TAPS; k++) {
-            const float w = plan.window[k];
-            v0 += w * h[0][y + k][x];
-            v1 += w * h[1][y + k][x];
-            v2 += w * h[2][y + k][x];
+        for (int q = 0; q < 3; q++) {
+            float v[ROWS + TAPS - 1];
+#pragma unroll
+            for (int j = 0; j < ROWS + TAPS - 1; j++) v[j] = h[q][y0 + j][x];
+#pragma unroll
+            for (int r2 = 0; r2 < ROWS; r2++) {
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < TAPS; k++) acc += plan.window[k] * v[r2 + k];
+                m[q][r2] = acc;
+            }
         }
-        const size_t at = base + static_cast<size_t>(py) * W + px;
-        dL_dimg1[at] = v0 + 2.f * __ldg(img1 + at) * v1 + __ldg(img2 + at) * v2;
+#pragma unroll
+        for (int r2 = 0; r2 < ROWS; r2++) {
+            const int py = oy0 + y0 + r2, px = ox0 + x;
+            if (py >= H || px >= W) continue;
+            const float v0 = m[0][r2], v1 = m[1][r2], v2 = m[2][r2];
+            const size_t at = base + static_cast<size_t>(py) * W + px;
+            dL_dimg1[at] = v0 + 2.f * __ldg(img1 + at) * v1 + __ldg(img2 + at) * v2;
+        }
     }
 }
 }  // namespace ssim
