@@ -2,9 +2,10 @@
 compiled reference (oracle/_ref/ref_wpn, when shipped) and against the IEEE C oracle, on seeded synthetic view pairs.
 
 First hardware run of this kernel happens after it was written (no GPU time was left), so the bounds below are the
-ones arithmetic can guarantee, not measured ones: `valid` may flip only on knife-edge patches, values may differ by
-what float32 cancellation in the variance amplifies (tests/test_patch_ncc_cpu.py measures 5.6e-4 worst, 9e-6 median,
-between float32 and float64).  The measured differences are written to gpurun_out/ncc_parity.json to tighten them."""
+ones arithmetic allows, not measured ones: `valid` may flip only on knife-edge patches, and values may differ by what
+float32 cancellation in the variance amplifies, which is heavy-tailed (see the bounds below: quantiles, calibrated on
+the CPU with and without multiply-add contraction).  The measured differences, and whether the outputs are bit-equal
+to the reference's, are written to gpurun_out/ncc_parity.json so that the bounds can be tightened."""
 import json
 import os
 
@@ -43,29 +44,43 @@ def _report(tag, arm, stats):
         json.dump(data, fh, indent=1, sort_keys=True)
 
 
-def _compare(got, want, tag, arm, flip_frac, value_abs, grad_rel):
+def _quantiles(d):
+    d = d.flatten().double()
+    if d.numel() > 4_000_000:
+        d = d[:: d.numel() // 4_000_000 + 1]
+    q = torch.quantile(d, torch.tensor([0.5, 0.99, 0.999], dtype=torch.double))
+    return [float(v) for v in q] + [float(d.max())]
+
+
+# Bounds on (median, 99 %, 99.9 %) of the differences.  Calibrated on the CPU: the kernel's routine compiled with
+# multiply-add contraction against the same routine without it differs by (6e-6, 1.3e-4, 3.1e-4) in the value and by
+# (9e-7, 5e-5, 3.9e-4) of the largest element in the depth derivative, with single patches off by 40 % (variance
+# = sum of squares - square of sum / 49 cancels), so the worst element is reported but not bounded.
+VALUE_BOUNDS = (5e-5, 1e-3, 3e-3)
+GRAD_BOUNDS = (1e-5, 5e-4, 4e-3)
+
+
+def _compare(got, want, tag, arm, flip_frac):
     g = [t.cpu() for t in got]
     w = [t.cpu() for t in want]
     n = len(w[3])
     flips = int((g[3] != w[3]).sum())
     both = g[3] & w[3]
     stats = {"points": n, "valid": int(w[3].sum()), "valid_flips": flips}
-    dv = (g[0] - w[0]).abs()[both]
-    stats["ncc_max_abs"] = float(dv.max())
-    stats["ncc_median_abs"] = float(dv.median())
     stats["bit_equal"] = bool(all(torch.equal(a, b) for a, b in zip(g, w)))
+    stats["ncc"] = _quantiles((g[0] - w[0]).abs()[both])
     for a, b, name in ((g[1], w[1], "grad_depths"), (g[2], w[2], "grad_normals")):
         scale = float(b[both].abs().max())
-        d = (a - b).abs()[both] / scale
-        stats[name + "_max_rel"] = float(d.max())
-        stats[name + "_median_rel"] = float(d.median())
+        stats[name] = _quantiles((a - b).abs()[both] / scale)
     _report(tag, arm, stats)
     print(tag, arm, stats)
     assert stats["valid"] > n // 2, "scene does not exercise the kernel"
     assert flips <= max(2, int(flip_frac * n)), stats
-    assert stats["ncc_max_abs"] <= value_abs and stats["ncc_median_abs"] <= value_abs / 20, stats
+    for got_q, bound in zip(stats["ncc"][:3], VALUE_BOUNDS):
+        assert got_q <= bound, ("ncc", stats)
     for name in ("grad_depths", "grad_normals"):
-        assert stats[name + "_max_rel"] <= grad_rel and stats[name + "_median_rel"] <= grad_rel / 20, (name, stats)
+        for got_q, bound in zip(stats[name][:3], GRAD_BOUNDS):
+            assert got_q <= bound, (name, stats)
     # invalid patches are exactly zero in every output
     for t in g[:3]:
         assert float(t[~g[3]].abs().max() if (~g[3]).any() else 0.0) == 0.0
@@ -79,7 +94,7 @@ def test_patch_ncc_vs_c_oracle(tag, device):
     got = _ours(sc, device)
     torch.cuda.synchronize()
     want = O.warp_patch_ncc(*ncc_scenes.args_of(sc))
-    _compare(got, want, tag, "c_oracle", flip_frac=2e-3, value_abs=5e-3, grad_rel=2e-2)
+    _compare(got, want, tag, "c_oracle", flip_frac=2e-3)
 
 
 @pytest.mark.parametrize("tag", sorted(SCENES))
@@ -95,7 +110,7 @@ def test_patch_ncc_vs_reference(tag, device):
     torch.cuda.synchronize()
     got = _ours(sc, device)
     torch.cuda.synchronize()
-    _compare(got, want, tag, "reference", flip_frac=1e-3, value_abs=2e-3, grad_rel=1e-2)
+    _compare(got, want, tag, "reference", flip_frac=1e-3)
 
 
 def test_patch_ncc_autograd_surface(device):
