@@ -141,7 +141,11 @@ def test_sample_depth_backward_vs_c_oracle(tag, device):
     for k, w in want.items():
         got = g[k].cpu().reshape(w.shape).double()
         w = w.double()
-        assert H.grad_rel_err(got, w) < 1e-2, k
+        # the oracle against the fast-math reference on the golden scenes: worst element 1.9e-3 of the largest; the
+        # median depth divides by dT/dt, so single queries can be touchier than that: bound the 99 % point tightly
+        # and the worst element loosely
+        d = ((got - w).abs() / w.abs().max()).flatten()
+        assert float(torch.quantile(d, 0.99)) < 2e-3 and float(d.max()) < 5e-2, (k, float(d.max()))
         big = w.abs() > 1e-3 * w.abs().max()
         rel = ((got - w).abs() / w.abs())[big]
         assert float(rel.median()) < 1e-3, (k, float(rel.median()))
