@@ -84,3 +84,32 @@ def test_library_exports_what_the_header_declares():
         ours.fused_ssim(img1, img2, padding="valid")
     with pytest.raises(AssertionError):
         ours.fused_ssim(img1, img2, padding="reflect")
+
+
+def test_smooth_images_with_flat_regions_are_as_accurate_as_torch_float32(emulated):
+    """Rendered images are smooth and have flat areas, where sigma^2 = E[x^2] - mu^2 cancels and the map divides by
+    ~C2: the fused kernels must not lose more there than the reference's own float32 formulation does."""
+    import ncc_scenes
+
+    tex = ncc_scenes.make_pair(height=120, width=160, n=4)["image_r"]
+    img1 = tex[None, None].repeat(1, 3, 1, 1).contiguous()
+    img1[:, :, :40, :60] = 0.3
+    img2 = (img1 + 0.01 * torch.randn(img1.shape, generator=torch.Generator().manual_seed(0))).clamp(0, 1).contiguous()
+    img2[:, :, :40, :60] = 0.31
+    B, Ch, Hh, W = img1.shape
+    want, want_grad = R.value_and_grad(img1, img2, "valid")
+    v32, g32 = R.value_and_grad(img1, img2, "valid", dtype=torch.float32)
+    torch_err = float((g32.double() - want_grad).abs().max() / want_grad.abs().max())
+    planes = B * Ch
+    tiles = (((Hh - 10) + 31) // 32) * (((W - 10) + 31) // 32) * planes
+    maps = [torch.zeros(planes, Hh, W) for _ in range(3)]
+    partials, mean, grad = torch.zeros(tiles), torch.zeros(1), torch.zeros(planes, Hh, W)
+    window, one = R.gaussian().float(), torch.tensor([1.0])
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    emulated.ggs_test_ssim_forward(planes, Hh, W, 1, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]), p(maps[2]),
+                                   p(partials), p(mean))
+    emulated.ggs_test_ssim_backward(planes, Hh, W, 1, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]), p(maps[2]),
+                                    p(one), p(grad))
+    ours_err = float((grad.reshape(B, Ch, Hh, W).double() - want_grad).abs().max() / want_grad.abs().max())
+    assert abs(float(mean) - float(want)) <= 1e-5 * abs(float(want))
+    assert ours_err <= 1e-4 and ours_err <= 2.0 * torch_err, (ours_err, torch_err)
