@@ -131,13 +131,16 @@ forward_kernel(const Plan plan, const float* __restrict__ img1, const float* __r
             const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1 * mu2;
             const float A = mu1_sq + mu2_sq + plan.c1, B = sigma1_sq + sigma2_sq + plan.c2;
             const float C = 2.f * mu1 * mu2 + plan.c1, D = 2.f * sigma12 + plan.c2;
-            local += (C * D) / (A * B);
+            // two reciprocals per pixel instead of seven divisions:
+            //   m = C D / (A B);  dm/dmu1 = 2 [mu2 (D - C) + mu1 C D (1/B - 1/A)] / (A B);
+            //   dm/dsigma1^2 = -C D / (A B^2);  dm/dsigma12 = 2 C / (A B)
+            const float inv_a = 1.f / A, inv_b = 1.f / B, inv_ab = inv_a * inv_b, cd = C * D;
+            local += cd * inv_ab;
             if (dm_dmu1) {
                 const size_t at = base + static_cast<size_t>(cy) * W + cx;
-                dm_dmu1[at] = (mu2 * 2.f * D) / (A * B) - (mu2 * 2.f * C) / (A * B) - (mu1 * 2.f * C * D) / (A * A * B) +
-                              (mu1 * 2.f * C * D) / (A * B * B);
-                dm_dsigma1_sq[at] = (-C * D) / (A * B * B);
-                dm_dsigma12[at] = (2.f * C) / (A * B);
+                dm_dmu1[at] = 2.f * inv_ab * (mu2 * (D - C) + mu1 * cd * (inv_b - inv_a));
+                dm_dsigma1_sq[at] = -cd * inv_ab * inv_b;
+                dm_dsigma12[at] = 2.f * C * inv_ab;
             }
         }
     }
