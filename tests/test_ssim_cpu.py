@@ -113,3 +113,14 @@ def test_smooth_images_with_flat_regions_are_as_accurate_as_torch_float32(emulat
     ours_err = float((grad.reshape(B, Ch, Hh, W).double() - want_grad).abs().max() / want_grad.abs().max())
     assert abs(float(mean) - float(want)) <= 1e-5 * abs(float(want))
     assert ours_err <= 1e-4 and ours_err <= 2.0 * torch_err, (ours_err, torch_err)
+
+
+def test_emulated_kernels_have_no_out_of_bounds_access():
+    """tools/emu_asan.sh: the NCC and SSIM kernel sources under the host shim, built with AddressSanitizer, on
+    exactly-sized buffers (global memory and the static "shared" arrays get redzones)."""
+    asan = subprocess.run(["gcc", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
+    if not os.path.isabs(asan) or not os.path.exists(asan):
+        pytest.skip("libasan not installed")
+    r = subprocess.run(["bash", os.path.join(H.ROOT, "tools", "emu_asan.sh")], capture_output=True, text=True,
+                       timeout=900)
+    assert r.returncode == 0 and "no out-of-bounds access" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])
