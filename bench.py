@@ -162,6 +162,16 @@ def watchdog(seconds, rank):
     return t
 
 
+def agreed(go, device):
+    """True on every rank if any rank wants to go on (MAX all-reduce): loops whose steps contain node-wide barriers
+    must run the same number of steps everywhere."""
+    import torch.distributed as dist
+
+    flag = torch.tensor([1 if go else 0], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+    return bool(int(flag.item()))
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -460,11 +470,7 @@ def main():
         ranks must run the SAME number of steps: the decision is agreed on with a MAX all-reduce (a rank that launched
         one step more than its peers would wait in that step's barrier for ever)."""
         go = done < at_least or time.perf_counter() - t_pre < 1.0
-        if multi:
-            flag = torch.tensor([1 if go else 0], dtype=torch.int32, device=device)
-            torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MAX)
-            go = bool(int(flag.item()))
-        return go
+        return agreed(go, device) if multi else go
 
     if _abi is not None:
         for _ in range(3):

@@ -166,3 +166,39 @@ def test_bench_reference_arm_runs_on_rank_zero_only_and_needs_a_gpu():
         r = subprocess.run([sys.executable, "bench.py", "--steps", "1"], cwd=helpers.ROOT, env=env,
                            capture_output=True, text=True, timeout=300)
         assert r.returncode != 0 and "no CPU path" in (r.stderr + r.stdout)
+
+
+def _agree_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import sys
+
+    sys.argv = ["bench.py"]
+    sys.path.insert(0, helpers.ROOT)
+    import bench
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # rank r alone would stop after 3 + 2 r steps; every step holds a barrier, as a view-parallel step does
+        steps = 0
+        while bench.agreed(steps < 3 + 2 * rank, "cpu"):
+            dist.barrier()
+            steps += 1
+        ret[rank] = steps
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_ranks_agree_on_the_number_of_pre_run_steps():
+    """bench.py's untimed pre-run is time-based; with a node barrier inside every step the ranks must stop after the
+    same step (a rank that went one step further hung two 8-GPU runs): the decision is a MAX all-reduce."""
+    world = 2
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_agree_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+        assert p.exitcode == 0
+    assert dict(ret) == {0: 5, 1: 5}
