@@ -26,6 +26,8 @@ constexpr int TILE = 32;                 // output tile edge
 constexpr int SPAN = TILE + 2 * HALO;    // 42: input tile edge
 constexpr int THREADS = 256;
 constexpr int ROWS = TILE * TILE / THREADS;  // 4: rows of one column a thread owns in the vertical pass
+static_assert(ROWS * THREADS == TILE * TILE && THREADS % TILE == 0, "one column strip per thread");
+static_assert(sizeof(float) * (2 * SPAN * SPAN + 5 * SPAN * TILE + THREADS) <= 48 * 1024, "static shared memory");
 
 struct Plan {
     int planes, height, width;  // planes = batch * channels
