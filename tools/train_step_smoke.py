@@ -57,7 +57,7 @@ def main():
     import warp_patch_ncc
 
     dev = "cuda:0"
-    views = [scenes.make_scene(args.workload, view=v, n_views=2) for v in (0, 1)]
+    views = [scenes.make_scene(args.workload, view=v, n_views=24) for v in (0, 1)]  # neighbours 15 degrees apart
     sc = views[0]
     P = sc.P
     gt = {k: getattr(sc, k).to(dev) for k in ("means3D", "opacities", "scales", "rotations", "shs")}
