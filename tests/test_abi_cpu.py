@@ -115,3 +115,16 @@ def test_product_never_imports_oracle():
     for fn in os.listdir(os.path.join(H.PKG, "csrc")):
         if fn.endswith((".cu", ".cuh")):
             assert "oracle" not in open(os.path.join(H.PKG, "csrc", fn)).read(), fn
+
+
+def test_public_headers_are_plain_c99():
+    """The boundary is a C ABI: every header under include/ must compile as C99 with no C++ or CUDA in it."""
+    import glob
+    import subprocess
+
+    headers = sorted(glob.glob(os.path.join(H.ROOT, "include", "*.h")))
+    assert len(headers) >= 3
+    for h in headers:
+        r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", "-"],
+                           input=f'#include "{h}"\n', capture_output=True, text=True)
+        assert r.returncode == 0, (h, r.stderr[-800:])
