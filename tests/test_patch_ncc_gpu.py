@@ -86,6 +86,7 @@ def _compare(got, want, tag, arm, flip_frac):
         assert float(t[~g[3]].abs().max() if (~g[3]).any() else 0.0) == 0.0
 
 
+@pytest.mark.first_hardware_run(order=4)  # after the self-consistency tests of this file
 @pytest.mark.parametrize("tag", sorted(SCENES))
 def test_patch_ncc_vs_c_oracle(tag, device):
     from oracle import oracle as O
@@ -97,6 +98,7 @@ def test_patch_ncc_vs_c_oracle(tag, device):
     _compare(got, want, tag, "c_oracle", flip_frac=2e-3)
 
 
+@pytest.mark.first_hardware_run(order=4)  # after the self-consistency tests of this file
 @pytest.mark.parametrize("tag", sorted(SCENES))
 def test_patch_ncc_vs_reference(tag, device):
     from oracle import ref_loader
