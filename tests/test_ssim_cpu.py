@@ -124,3 +124,35 @@ def test_emulated_kernels_have_no_out_of_bounds_access():
     r = subprocess.run(["bash", os.path.join(H.ROOT, "tools", "emu_asan.sh")], capture_output=True, text=True,
                        timeout=900)
     assert r.returncode == 0 and "no out-of-bounds access" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])
+
+
+def test_reference_golden_pins_the_checker_and_the_kernels(emulated):
+    """tests/golden/ssim/same.npz was produced by executing the reference's own `_ssim` (utils/loss_utils.py:52-73,
+    tests/golden/make_ssim_golden.py): it pins tests/ssim_reference.py, the checker of every SSIM test, and the
+    kernels (run from source on the host) for the padding the reference's torch code has."""
+    import numpy as np
+
+    gold = np.load(os.path.join(H.ROOT, "tests", "golden", "ssim", "same.npz"))
+    img1, img2 = torch.from_numpy(gold["img1"]), torch.from_numpy(gold["img2"])
+    val, grad = R.value_and_grad(img1, img2, "same")
+    # the reference rounds the 2-D window's products to float32 (create_window, :41-43); the checker and the separable
+    # kernels use the products of the float32 taps unrounded: agreement to 1e-8, not to the last bit
+    assert abs(float(val) - float(gold["value_f64"])) < 1e-8
+    want64 = torch.from_numpy(gold["grad_f64"])
+    assert float((grad - want64).abs().max()) < 1e-7 * float(want64.abs().max())
+    B, Ch, Hh, W = img1.shape
+    planes = B * Ch
+    tiles = ((Hh + 31) // 32) * ((W + 31) // 32) * planes
+    maps = [torch.zeros(planes, Hh, W) for _ in range(3)]
+    partials, mean, out = torch.zeros(tiles), torch.zeros(1), torch.zeros(planes, Hh, W)
+    window, one = R.gaussian().float(), torch.tensor([1.0])
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    emulated.ggs_test_ssim_forward(planes, Hh, W, 0, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]), p(maps[2]),
+                                   p(partials), p(mean))
+    emulated.ggs_test_ssim_backward(planes, Hh, W, 0, p(window), p(img1), p(img2), p(maps[0]), p(maps[1]), p(maps[2]),
+                                    p(one), p(out))
+    want_grad = torch.from_numpy(gold["grad_f64"])
+    assert abs(float(mean) - float(gold["value_f64"])) <= 1e-6 * float(gold["value_f64"])
+    err = float((out.reshape(B, Ch, Hh, W).double() - want_grad).abs().max() / want_grad.abs().max())
+    ref32 = float((torch.from_numpy(gold["grad_f32"]).double() - want_grad).abs().max() / want_grad.abs().max())
+    assert err <= 1e-5 and err <= 4.0 * max(ref32, 1e-7), (err, ref32)
