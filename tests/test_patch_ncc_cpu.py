@@ -186,3 +186,27 @@ def test_kernel_source_under_emulation_matches_oracle(n, tmp_path_factory):
     assert torch.equal(out[3].bool(), want[3])
     for a, b, name in zip(out[:3], want[:3], ("ncc", "grad_depths", "grad_normals")):
         assert torch.equal(a, b), name
+
+
+NCC_GOLDEN = {
+    "same_size": dict(n=4000),
+    "other_size": dict(height=96, width=128, neighbour_size=(110, 150), seed=11, shift=(12.0, 6.0), n=4000),
+    "big_shift": dict(seed=13, shift=(-40.0, 25.0), n=3000),
+}
+
+
+@pytest.mark.parametrize("tag", sorted(NCC_GOLDEN))
+def test_oracle_and_kernel_routine_match_the_reference_kernel_source_bit_for_bit(tag, host_routine):
+    """tests/golden/ncc/*.npz are outputs of the reference's OWN kernel source executed on the host under the CUDA
+    shim (tests/golden/make_ncc_golden.py; IEEE arithmetic, i.e. the reference's algorithm without fast-math).  The C
+    oracle and the kernel's routine, both IEEE on the host, must reproduce them exactly: this is what pins them."""
+    from oracle import oracle as O
+
+    gold = np.load(os.path.join(H.ROOT, "tests", "golden", "ncc", tag + ".npz"))
+    assert str(gold["scene"]) == repr(sorted(NCC_GOLDEN[tag].items()))
+    sc = ncc_scenes.make_pair(**NCC_GOLDEN[tag])
+    for arm, got in (("oracle", O.warp_patch_ncc(*ncc_scenes.args_of(sc))), ("kernel routine", host_routine(sc))):
+        assert np.array_equal(got[3].numpy(), gold["valid"]), arm
+        assert int(gold["valid"].sum()) > len(gold["valid"]) // 2
+        for t, key in zip(got[:3], ("ncc", "grad_depths", "grad_normals")):
+            assert np.array_equal(t.numpy(), gold[key]), (arm, key)
