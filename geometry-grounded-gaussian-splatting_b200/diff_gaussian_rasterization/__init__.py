@@ -72,7 +72,12 @@ def _frame(rs: GaussianRasterizationSettings, device, keep: list, kernel_size=No
     view = _dev_f32(rs.viewmatrix, device)
     proj = _dev_f32(rs.projmatrix, device)
     campos = _dev_f32(rs.campos, device)
-    bg = _dev_f32(rs.bg, device)
+    bg = rs.bg
+    if not isinstance(bg, torch.Tensor):
+        # the reference's point-query callers pass bg=None (gaussian_renderer/__init__.py:117,178) or bg=0 (:238);
+        # those paths never read it
+        bg = torch.full((3,), 0.0 if bg is None else float(bg), dtype=torch.float32, device=device)
+    bg = _dev_f32(bg, device)
     keep += [view, proj, campos, bg]
     f = _abi.GgsFrame()
     f.image_width = int(rs.image_width)

@@ -118,7 +118,7 @@ def make_scene(name: str = "c1", *, seed: Optional[int] = None, view: int = 0, n
                P: Optional[int] = None, W: Optional[int] = None, H: Optional[int] = None,
                kernel_size: float = 0.0, random_bg: bool = False, sh_degree: Optional[int] = None,
                sg_degree: Optional[int] = None, scale_mult: float = 1.0,
-               mask_depth_grad: bool = False) -> Scene:
+               mask_depth_grad: bool = False, opacity_range: Optional[tuple] = None) -> Scene:
     cP, cW, cH, focal, csh, csg = CONFIGS[name]
     P = cP if P is None else P
     if W is not None and W != cW:
@@ -150,6 +150,10 @@ def make_scene(name: str = "c1", *, seed: Optional[int] = None, view: int = 0, n
     rot = randn(P, 4)
     rot = (rot / rot.norm(dim=1, keepdim=True).clamp_min(1e-8)).contiguous()
     opac = torch.sigmoid(2.0 * randn(P, 1)).contiguous()
+    if opacity_range is not None:
+        # nearly transparent splats: the blend walks thousands of list entries before T < 1e-4 (long-list scenes)
+        lo, hi = opacity_range
+        opac = (lo + (hi - lo) * rand(P, 1)).contiguous()
     n_coef = 16  # allocated like the reference model (max_sh_degree 3): SHM = 16 regardless of active degree
     shs = torch.cat([randn(P, 1, 3), 0.15 * randn(P, n_coef - 1, 3)], 1).contiguous()
     SGM = sg_degree
@@ -182,3 +186,32 @@ def make_scene(name: str = "c1", *, seed: Optional[int] = None, view: int = 0, n
     sc = Scene(name, sh_degree, sg_degree, kernel_size, cam, bg, means, scales, rot, opac, shs, ax, sharp, sgc, grads)
     sc.mask_depth_grad = mask_depth_grad
     return sc
+
+
+def rotation_matrices(q: torch.Tensor) -> torch.Tensor:
+    """[P,4] (r,x,y,z) -> [P,3,3]; normalises like utils/general_utils.py build_rotation."""
+    q = q / q.norm(dim=1, keepdim=True)
+    r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R = torch.stack([
+        1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+        2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+        2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], dim=1)
+    return R.view(-1, 3, 3)
+
+
+def tetra_points(sc: Scene, device="cpu") -> torch.Tensor:
+    """The query points of the tetrahedral mesh extraction: per Gaussian the 8 corners of its box at 1.5 sigma, the
+    6 axis points at 3 sigma (all 14 per Gaussian first, Gaussian-major), then the centres -- the 15-point stencil of
+    GaussianModel.get_tetra_points (scene/gaussian_model.py:496-519).  [15 P, 3]."""
+    xyz = sc.means3D.to(device)
+    scale = sc.scales.to(device)
+    R = rotation_matrices(sc.rotations.to(device))
+    box = torch.tensor([[sx, sy, sz] for sx in (-1.0, 1.0) for sy in (-1.0, 1.0) for sz in (-1.0, 1.0)],
+                       dtype=torch.float32, device=device) * 1.5
+    axes = torch.tensor([[1, 0, 0], [0, 1, 0], [0, 0, 1], [-1, 0, 0], [0, -1, 0], [0, 0, -1]],
+                        dtype=torch.float32, device=device) * 3.0
+    verts = torch.cat([box, axes], 0).t().unsqueeze(0)  # [1,3,14]
+    v = verts * scale.unsqueeze(-1)  # [P,3,14]
+    v = torch.bmm(R, v) + xyz.unsqueeze(-1)
+    v = v.permute(0, 2, 1).reshape(-1, 3)
+    return torch.cat([v, xyz], 0).contiguous()

@@ -140,3 +140,27 @@ def test_non_default_stream_and_noncontiguous_grads(device):
     s.synchronize()
     assert torch.equal(base["color"], out["color"])
     assert H.grad_rel_err(g["means3D"], gbase["means3D"]) < 1e-5
+
+
+def test_point_queries_accept_the_reference_callers_bg(device):
+    """gaussian_renderer/__init__.py passes bg=None to integrate (:117) and evaluate_sdf (:178) and bg=0 to sample_depth
+    (:238); none of those paths reads it."""
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("tiny", scale_mult=3.0)
+    g = torch.Generator().manual_seed(3)
+    pts = (torch.randn(4000, 3, generator=g) * 0.6).to(device)
+    x = [getattr(sc, k).to(device) for k in ("means3D", "opacities", "scales", "rotations")]
+    base = H.settings_for(ours, sc, device)
+    want = ours.GaussianRasterizer(base)
+    none = ours.GaussianRasterizer(base._replace(bg=None))
+    zero = ours.GaussianRasterizer(base._replace(bg=0))
+    a0, i0 = want.integrate(pts, *x, None, None)
+    a1, i1 = none.integrate(pts, *x, None, None)
+    assert torch.equal(a0, a1) and torch.equal(i0, i1) and int(i0.sum()) > 0
+    d0 = want.evaluate_sdf(pts, *x, None, None)
+    d1 = none.evaluate_sdf(pts, *x, None, None)
+    assert all(torch.equal(u, v) for u, v in zip(d0, d1))
+    c0, j0 = want.sample_depth(pts, *x)
+    c1, j1 = zero.sample_depth(pts, *x)
+    assert torch.equal(c0, c1) and torch.equal(j0, j1)
