@@ -65,12 +65,16 @@ uint32_t* pinned_word() {
 int sort_end_bit(int tiles) { return 32 + (int)higher_msb((uint32_t)tiles); }
 int sort_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS; }
 
-int make_frame(const GgsFrame* f, const GgsGaussians* g, FrameParams& fp, GaussianInputs& in) {
+// geometry_only: the point-query paths (integrate / sample_depth / evaluate_sdf) ignore colour altogether; the
+// reference's callers hand them the model's active SH / SG degrees without any colour tensors
+// (gaussian_renderer/__init__.py:120-121), so the degrees are not validated there.
+int make_frame(const GgsFrame* f, const GgsGaussians* g, FrameParams& fp, GaussianInputs& in,
+               bool geometry_only = false) {
     if (!f || !g) return fail(GGS_ERR_INVALID_ARGUMENT, "null frame or gaussians");
     if (f->image_width <= 0 || f->image_height <= 0)
         return fail(GGS_ERR_INVALID_ARGUMENT, "image size must be positive");
     if (g->count < 0 || g->count > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad Gaussian count");
-    if (!f->viewmatrix || !f->projmatrix || !f->campos || !f->background)
+    if (!f->viewmatrix || !f->projmatrix || !f->campos || (!f->background && !geometry_only))
         return fail(GGS_ERR_INVALID_ARGUMENT, "camera tensors must be device pointers");
     if (g->count > 0 && (!g->means3D || !g->opacities))
         return fail(GGS_ERR_INVALID_ARGUMENT, "means3D and opacities are required");
@@ -84,10 +88,10 @@ int make_frame(const GgsFrame* f, const GgsGaussians* g, FrameParams& fp, Gaussi
     fp.gx = (fp.W + TILE_X - 1) / TILE_X;
     fp.gy = (fp.H + TILE_Y - 1) / TILE_Y;
     if (fp.gx >= 65536 || fp.gy >= 65536) return fail(GGS_ERR_INVALID_ARGUMENT, "image too large");
-    fp.SHD = f->sh_degree;
-    fp.SHM = g->shs ? g->sh_coeffs : 0;
-    fp.SGD = f->sg_degree;
-    fp.SGM = g->sg_color ? g->sg_lobes : 0;
+    fp.SHD = geometry_only ? 0 : f->sh_degree;
+    fp.SHM = (g->shs && !geometry_only) ? g->sh_coeffs : 0;
+    fp.SGD = geometry_only ? 0 : f->sg_degree;
+    fp.SGM = (g->sg_color && !geometry_only) ? g->sg_lobes : 0;
     if (fp.SHD < 0 || fp.SHD > 3) return fail(GGS_ERR_INVALID_ARGUMENT, "sh_degree must be in 0..3");
     if (g->shs && (fp.SHD + 1) * (fp.SHD + 1) > fp.SHM)
         return fail(GGS_ERR_INVALID_ARGUMENT, "sh_coeffs smaller than (sh_degree+1)^2");
@@ -107,11 +111,11 @@ int make_frame(const GgsFrame* f, const GgsGaussians* g, FrameParams& fp, Gaussi
     in.opacities = g->opacities;
     in.scales = g->scales;
     in.rotations = g->rotations;
-    in.shs = g->shs;
+    in.shs = geometry_only ? nullptr : g->shs;
     in.sg_axis = fp.SGM ? g->sg_axis : nullptr;
     in.sg_sharpness = fp.SGM ? g->sg_sharpness : nullptr;
     in.sg_color = fp.SGM ? g->sg_color : nullptr;
-    in.colors_precomp = g->colors_precomp;
+    in.colors_precomp = geometry_only ? nullptr : g->colors_precomp;
     return GGS_OK;
 }
 
@@ -509,92 +513,6 @@ int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t sh_coef
     return GGS_OK;
 }
 
-int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
-                             int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
-                             uint8_t* inside, void* stream_) {
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    FrameParams fp;
-    GaussianInputs in;
-    int rc = make_frame(frame, gaussians, fp, in);
-    if (rc) return rc;
-    if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
-    if (fp.P == 0 || num_points == 0) return 0;  // rasterize_points.cu:335
-    if (!points3D || !out_transmittance || !inside || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
-    const bool debug = frame->debug != 0;
-    const int PN = (int)num_points;
-    const int tiles = fp.gx * fp.gy;
-    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;  // rasterizer_impl.cu:638: geometry only
-    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
-
-    const GeomLayout GL = geom_layout(fp.P);
-    // tile workspace: gaussian ranges, point ranges, rounds, offsets, scan scratch
-    size_t o = 0;
-    auto take = [&](size_t bytes) {
-        size_t a = o;
-        o = align_up(o + bytes, 256);
-        return a;
-    };
-    const size_t t_granges = take((size_t)tiles * 8), t_pranges = take((size_t)tiles * 8),
-                 t_rounds = take((size_t)tiles * 4), t_offsets = take((size_t)tiles * 4),
-                 t_status = take(((size_t)tiles / SCAN_TILE + 2) * 8), t_counter = take(256), t_total = take(256);
-    const size_t tile_bytes = o;
-    // point workspace
-    o = 0;
-    const size_t p_xy = take((size_t)PN * 8), p_depth = take((size_t)PN * 4), p_touched = take((size_t)PN * 4),
-                 p_offsets = take((size_t)PN * 4), p_status = take(((size_t)PN / SCAN_TILE + 2) * 8),
-                 p_counter = take(256), p_total = take(256), p_radii = take((size_t)fp.P * 4);
-    const size_t point_bytes = o;
-
-    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
-    void* tile = alloc(GGS_SLOT_TILE, tile_bytes, user);
-    void* pts = alloc(GGS_SLOT_POINT, point_bytes, user);
-    if (!geom || !tile || !pts) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
-
-    int64_t D = 0;
-    void* bin = nullptr;
-    rc = bin_gaussians(fp, in, false, at<int>(pts, p_radii), geom, at<uint2>(tile, t_granges), alloc, user, &bin, &D,
-                       debug, stream);
-    if (rc) return rc;
-
-    launch_preprocess_points(fp, PN, points3D, at<float2>(pts, p_xy), at<float>(pts, p_depth),
-                             at<uint32_t>(pts, p_touched), nullptr, stream);
-    launch_scan(at<uint32_t>(pts, p_touched), at<uint32_t>(pts, p_offsets), PN, at<uint64_t>(pts, p_status),
-                at<uint32_t>(pts, p_counter), at<uint32_t>(pts, p_total), stream);
-    GGS_STAGE("preprocess_points", debug, stream);
-    uint32_t* host = pinned_word();
-    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(pts, p_total), 4, cudaMemcpyDeviceToHost, stream));
-    GGS_CUDA(cudaStreamSynchronize(stream));
-    const uint32_t E = *host;
-
-    const int bit = (int)higher_msb((uint32_t)tiles);
-    const int ppasses = sort_passes(32, 32 + bit);
-    const BinLayout PL = bin_layout(E, ppasses);
-    void* pbin = alloc(GGS_SLOT_POINT_BINNING, PL.bytes, user);
-    if (!pbin) return fail(GGS_ERR_ALLOC, "point binning workspace allocation failed");
-    launch_point_keys(PN, at<uint32_t>(pts, p_offsets), at<uint32_t>(pts, p_touched), at<float2>(pts, p_xy), fp.gx,
-                      fp.gy, at<uint64_t>(pbin, PL.keys_a), at<uint32_t>(pbin, PL.vals_a), stream);
-    const int where = launch_radix_sort(at<uint64_t>(pbin, PL.keys_a), at<uint64_t>(pbin, PL.keys_b),
-                                        at<uint32_t>(pbin, PL.vals_a), at<uint32_t>(pbin, PL.vals_b), E,
-                                        plain_sort_plan(32, 32 + bit), at<uint32_t>(pbin, PL.hist),
-                                        at<uint32_t>(pbin, PL.status), PL.status_bytes, at<uint32_t>(pbin, PL.counters),
-                                        stream);
-    const uint64_t* pkeys = where ? at<uint64_t>(pbin, PL.keys_b) : at<uint64_t>(pbin, PL.keys_a);
-    const uint32_t* plist = where ? at<uint32_t>(pbin, PL.vals_b) : at<uint32_t>(pbin, PL.vals_a);
-    launch_tile_ranges(pkeys, E, at<uint2>(tile, t_pranges), tiles, stream);
-    launch_point_blocks(tiles, at<uint2>(tile, t_pranges), at<uint32_t>(tile, t_rounds), stream);
-    launch_scan(at<uint32_t>(tile, t_rounds), at<uint32_t>(tile, t_offsets), tiles, at<uint64_t>(tile, t_status),
-                at<uint32_t>(tile, t_counter), at<uint32_t>(tile, t_total), stream);
-    GGS_STAGE("point_binning", debug, stream);
-
-    constexpr uint32_t PER_ROUND = TILE_PIXELS * POINT_BATCH;
-    const uint32_t max_blocks = E ? (uint32_t)std::min<uint64_t>((uint64_t)tiles + E / PER_ROUND, (uint64_t)E) : 0;
-    launch_integrate(tiles, max_blocks, at<uint32_t>(tile, t_offsets), at<uint2>(tile, t_granges),
-                     at<uint2>(tile, t_pranges), sorted_list(bin, D, tiles), plist, at<SplatRecord>(geom, GL.records),
-                     at<float2>(pts, p_xy), at<float>(pts, p_depth), out_transmittance, inside, stream);
-    GGS_STAGE("integrate", debug, stream);
-    return D;
-}
-
 int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
                       const GgsPeerExchange* px, float* dL_dsh, int32_t parts, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -782,180 +700,182 @@ int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
 
 }  // extern "C"
 
-// ---- sample_depth ---------------------------------------------------------------------------------------------
+// ---- point queries: integrate / sample_depth / evaluate_sdf ----------------------------------------------------
+// The reference bins the Gaussians of the view inside every call (rasterizer_impl.cu:637-714, :861-936, :1084-1160),
+// i.e. once per (chunk of points, view) in mesh_extract_tetrahedra.py:70-82.  Here that half is its own entry point
+// (ggs_view_prepare) whose result any number of query calls can share; the one-shot entry points run both halves.
 namespace {
 
-struct SampleTileLayout {  // GGS_SLOT_TILE of the point-query paths
-    size_t granges, pranges, rounds, offsets, status, counter, total, bytes;
+struct ViewTileLayout {  // GGS_SLOT_TILE of a prepared view
+    size_t granges, radii, bytes;
 };
-SampleTileLayout sample_tile_layout(int tiles) {
-    SampleTileLayout L;
-    size_t o = 0;
-    auto take = [&](size_t bytes) {
-        size_t a = o;
-        o = align_up(o + bytes, 256);
-        return a;
-    };
-    L.granges = take((size_t)tiles * 8);
-    L.pranges = take((size_t)tiles * 8);
-    L.rounds = take((size_t)tiles * 4);
-    L.offsets = take((size_t)tiles * 4);
-    L.status = take(((size_t)tiles / SCAN_TILE + 2) * 8);
-    L.counter = take(256);
-    L.total = take(256);
-    L.bytes = o;
+ViewTileLayout view_tile_layout(int tiles, int P) {
+    ViewTileLayout L;
+    L.granges = 0;
+    L.radii = align_up((size_t)tiles * 8, 256);
+    L.bytes = L.radii + align_up((size_t)P * 4, 256);
     return L;
 }
 
-struct SamplePointLayout {  // GGS_SLOT_POINT
-    size_t xy, depth, touched, offsets, status, counter, total, radii, n_contrib, median_depth, bytes;
-};
-SamplePointLayout sample_point_layout(int PN, int P) {
-    SamplePointLayout L;
-    size_t o = 0;
-    auto take = [&](size_t bytes) {
-        size_t a = o;
-        o = align_up(o + bytes, 256);
-        return a;
-    };
-    L.xy = take((size_t)PN * 8);
-    L.depth = take((size_t)PN * 4);
-    L.touched = take((size_t)PN * 4);
-    L.offsets = take((size_t)PN * 4);
-    L.status = take(((size_t)PN / SCAN_TILE + 2) * 8);
-    L.counter = take(256);
-    L.total = take(256);
-    L.radii = take((size_t)P * 4);
-    L.n_contrib = take((size_t)PN * 4);
-    L.median_depth = take((size_t)PN * 4);
-    L.bytes = o;
-    return L;
-}
-
-}  // namespace
-
-namespace {
-// Shared driver of sample_depth (sdf == false) and evaluate_sdf (sdf == true: out_points = median depth [PN],
-// out_sdf = depth difference [PN]).
-int64_t sample_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D, int64_t num_points,
-                      GgsAllocFn alloc, void* user, float* out_points, float* out_sdf, uint8_t* inside,
-                      GgsSampleState* state, bool sdf, void* stream_) {
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    FrameParams fp;
+int prepare_view(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user, GgsViewState* view,
+                 FrameParams& fp, cudaStream_t stream) {
     GaussianInputs in;
-    int rc = make_frame(frame, gaussians, fp, in);
+    int rc = make_frame(frame, gaussians, fp, in, /*geometry_only=*/true);
     if (rc) return rc;
-    if (!state) return fail(GGS_ERR_INVALID_ARGUMENT, "null state");
-    *state = GgsSampleState{};
+    if (!view || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null view state / alloc");
+    *view = GgsViewState{};
+    view->count = fp.P;
+    if (fp.P == 0) return GGS_OK;
+    const int tiles = fp.gx * fp.gy;
+    const GeomLayout GL = geom_layout(fp.P);
+    const ViewTileLayout TL = view_tile_layout(tiles, fp.P);
+    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
+    void* tile = alloc(GGS_SLOT_TILE, TL.bytes, user);
+    if (!geom || !tile) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
+    int64_t D = 0;
+    void* bin = nullptr;
+    rc = bin_gaussians(fp, in, false, at<int>(tile, TL.radii), geom, at<uint2>(tile, TL.granges), alloc, user, &bin, &D,
+                       frame->debug != 0, stream);
+    if (rc) return rc;
+    view->geometry = geom;
+    view->binning = bin;
+    view->tile = tile;
+    view->num_rendered = D;
+    return GGS_OK;
+}
+
+// Camera half of a frame for a query against a prepared view (the Gaussians are not needed again).
+int query_frame(const GgsFrame* f, const GgsViewState* view, FrameParams& fp) {
+    if (!f || !view) return fail(GGS_ERR_INVALID_ARGUMENT, "null frame or view state");
+    GgsGaussians g = {};
+    g.count = 0;
+    GaussianInputs in;
+    const int rc = make_frame(f, &g, fp, in, true);
+    if (rc) return rc;
+    fp.P = (int)view->count;
+    if (view->count > 0 && (!view->geometry || !view->binning || !view->tile))
+        return fail(GGS_ERR_INVALID_ARGUMENT, "view state is incomplete");
+    return GGS_OK;
+}
+
+enum QueryKind { Q_INTEGRATE, Q_SAMPLE, Q_SDF };
+
+// Bins the query points and runs one forward kernel.  `ws_out`: the query workspace (GGS_SLOT_POINT).
+int run_query(QueryKind kind, const GgsFrame* frame, const GgsViewState* view, const float* points3D,
+              int64_t num_points, GgsAllocFn alloc, void* user, float* out_a, float* out_b, uint8_t* inside,
+              void** ws_out, cudaStream_t stream) {
+    FrameParams fp;
+    int rc = query_frame(frame, view, fp);
+    if (rc) return rc;
     if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
-    if (fp.P == 0 || num_points == 0) return 0;  // rasterize_points.cu:528
-    if (!points3D || !out_points || !inside || !alloc || (sdf && !out_sdf))
+    if (ws_out) *ws_out = nullptr;
+    if (fp.P == 0 || num_points == 0) return GGS_OK;  // rasterize_points.cu:335, :528: nothing is launched
+    if (!points3D || !out_a || !inside || !alloc || (kind == Q_SDF && !out_b))
         return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
     const bool debug = frame->debug != 0;
     const int PN = (int)num_points;
     const int tiles = fp.gx * fp.gy;
-    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;  // rasterizer_impl.cu:1084: geometry only
-    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
-
+    if (tiles >= (1 << (32 - QUERY_CELL_BITS)) - 1) return fail(GGS_ERR_UNSUPPORTED, "image too large for point queries");
+    const QueryLayout QL = query_layout((size_t)PN, tiles, kind == Q_SAMPLE);
+    void* ws = alloc(GGS_SLOT_POINT, QL.bytes, user);
+    if (!ws) return fail(GGS_ERR_ALLOC, "query workspace allocation failed");
+    if (ws_out) *ws_out = ws;
+    launch_query_binning(fp, PN, points3D, ws, QL, stream);
+    GGS_STAGE("query_binning", debug, stream);
     const GeomLayout GL = geom_layout(fp.P);
-    const SampleTileLayout TL = sample_tile_layout(tiles);
-    const SamplePointLayout PL = sample_point_layout(PN, fp.P);
-    void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
-    void* tile = alloc(GGS_SLOT_TILE, TL.bytes, user);
-    void* pts = alloc(GGS_SLOT_POINT, PL.bytes, user);
-    if (!geom || !tile || !pts) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
-    state->geometry = geom;
-    state->tile = tile;
-    state->point = pts;
-
-    int64_t D = 0;
-    void* bin = nullptr;
-    rc = bin_gaussians(fp, in, false, at<int>(pts, PL.radii), geom, at<uint2>(tile, TL.granges), alloc, user, &bin, &D,
-                       debug, stream);
-    if (rc) return rc;
-    state->binning = bin;
-    state->num_rendered = D;
-
-    launch_preprocess_points(fp, PN, points3D, at<float2>(pts, PL.xy), at<float>(pts, PL.depth),
-                             at<uint32_t>(pts, PL.touched), nullptr, stream);
-    launch_scan(at<uint32_t>(pts, PL.touched), at<uint32_t>(pts, PL.offsets), PN, at<uint64_t>(pts, PL.status),
-                at<uint32_t>(pts, PL.counter), at<uint32_t>(pts, PL.total), stream);
-    GGS_STAGE("preprocess_points", debug, stream);
-    uint32_t* host = pinned_word();
-    if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
-    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(pts, PL.total), 4, cudaMemcpyDeviceToHost, stream));
-    GGS_CUDA(cudaStreamSynchronize(stream));
-    const uint32_t E = *host;
-    state->num_evaluated = E;
-
-    const int bit = (int)higher_msb((uint32_t)tiles);
-    const BinLayout QL = bin_layout(E, sort_passes(32, 32 + bit));
-    void* pbin = alloc(GGS_SLOT_POINT_BINNING, QL.bytes, user);
-    if (!pbin) return fail(GGS_ERR_ALLOC, "point binning workspace allocation failed");
-    state->point_binning = pbin;
-    launch_point_keys(PN, at<uint32_t>(pts, PL.offsets), at<uint32_t>(pts, PL.touched), at<float2>(pts, PL.xy), fp.gx,
-                      fp.gy, at<uint64_t>(pbin, QL.keys_a), at<uint32_t>(pbin, QL.vals_a), stream);
-    const int where = launch_radix_sort(at<uint64_t>(pbin, QL.keys_a), at<uint64_t>(pbin, QL.keys_b),
-                                        at<uint32_t>(pbin, QL.vals_a), at<uint32_t>(pbin, QL.vals_b), E,
-                                        plain_sort_plan(32, 32 + bit), at<uint32_t>(pbin, QL.hist),
-                                        at<uint32_t>(pbin, QL.status), QL.status_bytes, at<uint32_t>(pbin, QL.counters),
-                                        stream);
-    const uint64_t* pkeys = where ? at<uint64_t>(pbin, QL.keys_b) : at<uint64_t>(pbin, QL.keys_a);
-    launch_tile_ranges(pkeys, E, at<uint2>(tile, TL.pranges), tiles, stream);
-    launch_point_blocks(tiles, at<uint2>(tile, TL.pranges), at<uint32_t>(tile, TL.rounds), stream);
-    launch_scan(at<uint32_t>(tile, TL.rounds), at<uint32_t>(tile, TL.offsets), tiles, at<uint64_t>(tile, TL.status),
-                at<uint32_t>(tile, TL.counter), at<uint32_t>(tile, TL.total), stream);
-    GGS_STAGE("point_binning", debug, stream);
-
-    constexpr uint32_t PER_ROUND = TILE_PIXELS * POINT_BATCH;
-    const uint32_t max_blocks = E ? (uint32_t)std::min<uint64_t>((uint64_t)tiles + E / PER_ROUND, (uint64_t)E) : 0;
-    state->num_blocks = max_blocks;
-    void* blocks = alloc(GGS_SLOT_BLOCKS, (size_t)std::max<uint32_t>(max_blocks, 1) * 4, user);
-    if (!blocks) return fail(GGS_ERR_ALLOC, "block workspace allocation failed");
-    state->blocks = blocks;
-    GGS_CUDA(cudaMemsetAsync(blocks, 0, (size_t)std::max<uint32_t>(max_blocks, 1) * 4, stream));
-    const uint32_t* plist = where ? at<uint32_t>(pbin, QL.vals_b) : at<uint32_t>(pbin, QL.vals_a);
-    if (sdf) {
-        launch_evaluate_sdf(fp, tiles, max_blocks, at<uint32_t>(tile, TL.offsets), at<uint2>(tile, TL.granges),
-                            at<uint2>(tile, TL.pranges), sorted_list(bin, D, tiles), plist,
-                            at<SplatRecord>(geom, GL.records), at<float2>(pts, PL.xy), at<float>(pts, PL.depth),
-                            out_points, out_sdf, inside, stream);
-        GGS_STAGE("evaluate_sdf", debug, stream);
-        return D;
-    }
-    launch_sample_depth_forward(fp, tiles, max_blocks, at<uint32_t>(tile, TL.offsets), at<uint2>(tile, TL.granges),
-                                at<uint2>(tile, TL.pranges), sorted_list(bin, D, tiles), plist,
-                                at<SplatRecord>(geom, GL.records), at<float2>(pts, PL.xy),
-                                at<uint32_t>(pts, PL.n_contrib), at<float>(pts, PL.median_depth),
-                                at<uint32_t>(blocks, 0), out_points, inside, stream);
-    GGS_STAGE("sample_depth", debug, stream);
-    return D;
+    const ViewTileLayout TL = view_tile_layout(tiles, fp.P);
+    const uint2* granges = at<uint2>(view->tile, TL.granges);
+    const uint32_t* glist = sorted_list(view->binning, view->num_rendered, tiles);
+    const SplatRecord* records = at<SplatRecord>(view->geometry, GL.records);
+    if (kind == Q_INTEGRATE)
+        launch_integrate(QL, ws, granges, glist, records, out_a, inside, stream);
+    else if (kind == Q_SAMPLE)
+        launch_sample_depth_forward(fp, QL, ws, granges, glist, records, out_a, inside, stream);
+    else
+        launch_evaluate_sdf(fp, QL, ws, granges, glist, records, out_a, out_b, inside, stream);
+    GGS_STAGE("query", debug, stream);
+    return GGS_OK;
 }
+
 }  // namespace
 
-extern "C" int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
-                                            int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
-                                            uint8_t* inside, GgsSampleState* state, void* stream) {
-    return sample_points(frame, gaussians, points3D, num_points, alloc, user, out_points, nullptr, inside, state, false,
-                         stream);
+extern "C" {
+
+int64_t ggs_view_prepare(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user,
+                         GgsViewState* view, void* stream) {
+    FrameParams fp;
+    const int rc = prepare_view(frame, gaussians, alloc, user, view, fp, static_cast<cudaStream_t>(stream));
+    return rc ? rc : view->num_rendered;
 }
 
-extern "C" int64_t ggs_evaluate_sdf(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
-                                    int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
-                                    uint8_t* inside, void* stream) {
-    GgsSampleState state;
-    return sample_points(frame, gaussians, points3D, num_points, alloc, user, out_depth, out_sdf, inside, &state, true,
-                         stream);
+int ggs_integrate_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D, int64_t num_points,
+                       GgsAllocFn alloc, void* user, float* out_transmittance, uint8_t* inside, void* stream) {
+    return run_query(Q_INTEGRATE, frame, view, points3D, num_points, alloc, user, out_transmittance, nullptr, inside,
+                     nullptr, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
-                                         int64_t num_points, const GgsSampleState* state, const uint8_t* inside,
-                                         const float* dL_dout_points, GgsAllocFn alloc, void* user,
-                                         const GgsGradients* grads, float* dL_dpoints3D, void* stream_) {
+int ggs_evaluate_sdf_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D, int64_t num_points,
+                          GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf, uint8_t* inside,
+                          void* stream) {
+    return run_query(Q_SDF, frame, view, points3D, num_points, alloc, user, out_depth, out_sdf, inside, nullptr,
+                     static_cast<cudaStream_t>(stream));
+}
+
+int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                             int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
+                             uint8_t* inside, void* stream) {
+    if (num_points == 0 || (gaussians && gaussians->count == 0)) return 0;  // rasterize_points.cu:335
+    GgsViewState view;
+    FrameParams fp;
+    int rc = prepare_view(frame, gaussians, alloc, user, &view, fp, static_cast<cudaStream_t>(stream));
+    if (rc) return rc;
+    rc = ggs_integrate_view(frame, &view, points3D, num_points, alloc, user, out_transmittance, inside, stream);
+    return rc ? rc : view.num_rendered;
+}
+
+int64_t ggs_evaluate_sdf(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                         int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
+                         uint8_t* inside, void* stream) {
+    if (num_points == 0 || (gaussians && gaussians->count == 0)) return 0;
+    GgsViewState view;
+    FrameParams fp;
+    int rc = prepare_view(frame, gaussians, alloc, user, &view, fp, static_cast<cudaStream_t>(stream));
+    if (rc) return rc;
+    rc = ggs_evaluate_sdf_view(frame, &view, points3D, num_points, alloc, user, out_depth, out_sdf, inside, stream);
+    return rc ? rc : view.num_rendered;
+}
+
+int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                                 int64_t num_points, GgsAllocFn alloc, void* user, float* out_points,
+                                 uint8_t* inside, GgsSampleState* state, void* stream) {
+    if (!state) return fail(GGS_ERR_INVALID_ARGUMENT, "null state");
+    *state = GgsSampleState{};
+    if (num_points == 0 || (gaussians && gaussians->count == 0)) return 0;  // rasterize_points.cu:528
+    GgsViewState view;
+    FrameParams fp;
+    int rc = prepare_view(frame, gaussians, alloc, user, &view, fp, static_cast<cudaStream_t>(stream));
+    if (rc) return rc;
+    void* ws = nullptr;
+    rc = run_query(Q_SAMPLE, frame, &view, points3D, num_points, alloc, user, out_points, nullptr, inside, &ws,
+                   static_cast<cudaStream_t>(stream));
+    if (rc) return rc;
+    state->geometry = view.geometry;
+    state->binning = view.binning;
+    state->tile = view.tile;
+    state->point = ws;
+    state->num_rendered = view.num_rendered;
+    state->num_evaluated = num_points;
+    return view.num_rendered;
+}
+
+int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
+                              int64_t num_points, const GgsSampleState* state, const uint8_t* inside,
+                              const float* dL_dout_points, GgsAllocFn alloc, void* user, const GgsGradients* grads,
+                              float* dL_dpoints3D, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     FrameParams fp;
     GaussianInputs in;
-    int rc = make_frame(frame, gaussians, fp, in);
+    int rc = make_frame(frame, gaussians, fp, in, /*geometry_only=*/true);
     if (rc) return rc;
     if (num_points < 0 || num_points > 0x7fffffffLL) return fail(GGS_ERR_INVALID_ARGUMENT, "bad point count");
     if (!grads || !state || !alloc) return fail(GGS_ERR_INVALID_ARGUMENT, "null state/grads/alloc");
@@ -981,21 +901,13 @@ extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussia
         return GGS_OK;
     }
     if (!points3D || !inside || !dL_dout_points) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
-    if (!state->geometry || !state->binning || !state->point || !state->point_binning || !state->tile ||
-        !state->blocks)
+    if (!state->geometry || !state->binning || !state->point || !state->tile)
         return fail(GGS_ERR_INVALID_ARGUMENT, "forward state is incomplete");
     const bool debug = frame->debug != 0;
     const int tiles = fp.gx * fp.gy;
-    fp.SHD = fp.SHM = fp.SGD = fp.SGM = 0;
-    in.shs = in.sg_axis = in.sg_sharpness = in.sg_color = in.colors_precomp = nullptr;
     const GeomLayout GL = geom_layout(fp.P);
-    const SampleTileLayout TL = sample_tile_layout(tiles);
-    const SamplePointLayout PL = sample_point_layout(PN, fp.P);
-    const int bit = (int)higher_msb((uint32_t)tiles);
-    const int ppasses = sort_passes(32, 32 + bit);
-    const BinLayout QL = bin_layout((size_t)state->num_evaluated, ppasses);
-    const uint32_t* plist = (ppasses & 1) ? at<uint32_t>(state->point_binning, QL.vals_b)
-                                          : at<uint32_t>(state->point_binning, QL.vals_a);
+    const ViewTileLayout TL = view_tile_layout(tiles, fp.P);
+    const QueryLayout QL = query_layout((size_t)PN, tiles, true);
 
     // scratch: accumulator rows (double) + dL_dpoints2D
     const size_t acc_bytes = align_up(P * GRAD_STRIDE * sizeof(double), 256);
@@ -1006,14 +918,9 @@ extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussia
     float2* dp2d = reinterpret_cast<float2*>(scratch + acc_bytes);
     GGS_CUDA(cudaMemsetAsync(scratch, 0, acc_bytes + p2d_bytes, stream));
 
-    void* pts = state->point;
-    launch_sample_depth_backward(fp, tiles, (uint32_t)state->num_blocks, at<uint32_t>(state->blocks, 0),
-                                 at<uint32_t>(state->tile, TL.offsets), at<uint2>(state->tile, TL.granges),
-                                 at<uint2>(state->tile, TL.pranges),
-                                 sorted_list(state->binning, state->num_rendered, tiles), plist,
-                                 at<SplatRecord>(state->geometry, GL.records), at<float2>(pts, PL.xy),
-                                 at<uint32_t>(pts, PL.n_contrib), at<float>(pts, PL.median_depth), inside,
-                                 dL_dout_points, dp2d, acc, stream);
+    launch_sample_depth_backward(fp, QL, state->point, at<uint2>(state->tile, TL.granges),
+                                 sorted_list(state->binning, state->num_rendered, tiles),
+                                 at<SplatRecord>(state->geometry, GL.records), inside, dL_dout_points, dp2d, acc, stream);
     GGS_STAGE("sample_depth_backward", debug, stream);
 
     GaussianGrads gg{};
@@ -1023,9 +930,12 @@ extern "C" int ggs_sample_depth_backward(const GgsFrame* frame, const GgsGaussia
     gg.dL_dopacity = grads->dL_dopacity;
     gg.dL_dscales = grads->dL_dscales;
     gg.dL_drotations = grads->dL_drotations;
-    launch_gaussian_backward(fp, in, at<int>(pts, PL.radii), at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
+    launch_gaussian_backward(fp, in, at<int>(state->tile, TL.radii), at<uint8_t>(state->geometry, GL.clamped), acc, gg,
+                             stream);
     GGS_STAGE("gaussian_backward", debug, stream);
-    launch_points_backward(fp, PN, points3D, at<uint32_t>(pts, PL.touched), dp2d, dL_dpoints3D, stream);
+    launch_points_backward(fp, PN, points3D, at<float2>(state->point, QL.xy), dp2d, dL_dpoints3D, stream);
     GGS_STAGE("points_backward", debug, stream);
     return GGS_OK;
 }
+
+}  // extern "C"

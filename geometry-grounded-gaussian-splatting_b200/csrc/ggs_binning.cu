@@ -232,30 +232,6 @@ void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets
         P, order, offsets, rects, gx, tile_keys, vals, passes > 4 ? 4 : passes, hist);
 }
 
-// Points fall into exactly one tile (rasterizer_impl.cu:109-137).
-__global__ void point_keys_kernel(int PN, const uint32_t* __restrict__ offsets,
-                                  const uint32_t* __restrict__ touched, const float2* __restrict__ points2D, int gx,
-                                  int gy, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (size_t)PN) return;
-    if (touched[idx] > 0) {
-        const uint32_t off = (idx == 0) ? 0 : offsets[idx - 1];
-        const float2 p = points2D[idx];
-        const int x = min(gx - 1, max((int)0, (int)((p.x + 0.5f) / TILE_X)));
-        const int y = min(gy - 1, max((int)0, (int)((p.y + 0.5f) / TILE_Y)));
-        uint64_t key = (uint64_t)(uint32_t)(y * gx + x);
-        key <<= 32;
-        keys[off] = key;
-        vals[off] = (uint32_t)idx;
-    }
-}
-
-void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,
-                       int gy, uint64_t* keys, uint32_t* vals, cudaStream_t stream) {
-    if (PN == 0) return;
-    point_keys_kernel<<<(PN + 255) / 256, 256, 0, stream>>>(PN, offsets, touched, points2D, gx, gy, keys, vals);
-}
-
 // ------------------------------------------------------------------------------------------------
 // Tile ranges from the sorted keys (rasterizer_impl.cu:142-161); untouched tiles stay (0,0).
 // ------------------------------------------------------------------------------------------------

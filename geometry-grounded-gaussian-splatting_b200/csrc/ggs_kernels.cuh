@@ -45,10 +45,6 @@ void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets
                            uint32_t* tile_keys, uint32_t* vals, uint32_t D, int passes, uint32_t* hist,
                            cudaStream_t stream);
 
-// point variant (reference createWithKeys, rasterizer_impl.cu:109-137): key = tile<<32
-void launch_point_keys(int PN, const uint32_t* offsets, const uint32_t* touched, const float2* points2D, int gx,
-                       int gy, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
-
 // Digit plan of the radix sort.  Plain: 8-bit digits of bits [begin_bit, end_bit).  Compact (rasterizer keys
 // tile<<32 | depth bits only): the top byte of a positive float depth takes very few distinct values (sign + 7
 // exponent bits: 0.2 .. 100 spans five), so after three plain passes over depth bits 0..23 the remaining order is
@@ -76,6 +72,10 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 // launch_duplicate_keys.  Input in (tk_a, vals_a) when tile_sort_passes() is even, in (tk_b, vals_b) when odd; the
 // sorted values land in vals_a and the last pass writes the reference's 64-bit keys (tile << 32 | depth bits of the
 // pair's Gaussian) to keys64_out.
+// Stable sort of (u32 key, u32 value) pairs on key bits [0, bits).  Returns 0 if the result is in *_a, 1 if in *_b.
+int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
+                        uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
+                        cudaStream_t stream);
 int tile_sort_passes(int tile_bits);
 void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int tile_bits,
                       const uint32_t* depth_bits, uint64_t* keys64_out, uint32_t* hist, uint32_t* status,
@@ -137,14 +137,43 @@ void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, c
                               const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
                               cudaStream_t stream);
 
-// ---- point queries (integrate) ----------------------------------------------------------------
-void launch_preprocess_points(const FrameParams& fp, int PN, const float* points3D, float2* points2D,
-                              float* depths, uint32_t* touched, uint8_t* inside, cudaStream_t stream);
-void launch_point_blocks(int tiles, const uint2* point_ranges, uint32_t* tile_rounds, cudaStream_t stream);
-void launch_integrate(int tiles, uint32_t max_blocks, const uint32_t* tile_offsets, const uint2* gaussian_ranges,
-                      const uint2* point_ranges, const uint32_t* gaussian_list, const uint32_t* point_list,
-                      const SplatRecord* records, const float2* points2D, const float* point_depths,
-                      float* out_transmittance, uint8_t* inside, cudaStream_t stream);
+// ---- point queries (integrate / sample_depth / evaluate_sdf), ggs_query.cu -------------------------------------
+// Queries are sorted by (tile, Morton code of the quarter-pixel cell inside the tile); a CTA owns QUERY_CTA consecutive
+// queries of one tile.  Everything a query call needs lives in ONE workspace whose layout depends on the number of
+// points and tiles only -- no count is read back by the host.
+constexpr int QUERY_CTA = 128;
+constexpr int QUERY_CELL_BITS = 12;
+struct QueryLayout {
+    size_t xy, ts;                          // float2[PN] pixel position ((-1,-1): not evaluated), f32[PN] ray depth
+    size_t keys_a, keys_b, vals_a, vals_b;  // u32[PN] sort ping-pong: key = tile << 12 | cell, value = point index
+    size_t hist, status, counters, status_bytes;
+    size_t ranges;                          // uint2[tiles] slice of the sorted queries per tile
+    size_t rounds, offsets;                 // u32[tiles] CTAs per tile and their inclusive scan
+    size_t scan_status, scan_counter, scan_total;
+    size_t block_tile;                      // u32[max_blocks] tile of each CTA (0xffffffff: none)
+    size_t n_contrib, median_depth;         // u32[PN], f32[PN]: sample_depth keeps them for its backward
+    size_t bytes;
+    uint32_t max_blocks;
+    int sort_bits;
+    bool sorted_in_b;
+};
+QueryLayout query_layout(size_t PN, int tiles, bool sample);
+void launch_query_binning(const FrameParams& fp, int PN, const float* points3D, void* ws, const QueryLayout& L,
+                          cudaStream_t stream);
+void launch_integrate(const QueryLayout& L, void* ws, const uint2* gaussian_ranges, const uint32_t* gaussian_list,
+                      const SplatRecord* records, float* out_transmittance, uint8_t* inside, cudaStream_t stream);
+void launch_sample_depth_forward(const FrameParams& fp, const QueryLayout& L, void* ws, const uint2* gaussian_ranges,
+                                 const uint32_t* gaussian_list, const SplatRecord* records, float* output,
+                                 uint8_t* inside, cudaStream_t stream);
+void launch_evaluate_sdf(const FrameParams& fp, const QueryLayout& L, void* ws, const uint2* gaussian_ranges,
+                         const uint32_t* gaussian_list, const SplatRecord* records, float* out_depth, float* out_sdf,
+                         uint8_t* inside, cudaStream_t stream);
+void launch_sample_depth_backward(const FrameParams& fp, const QueryLayout& L, void* ws, const uint2* gaussian_ranges,
+                                  const uint32_t* gaussian_list, const SplatRecord* records, const uint8_t* inside,
+                                  const float* dL_doutputs, float2* dL_dpoints2D, double* grad_acc,
+                                  cudaStream_t stream);
+void launch_points_backward(const FrameParams& fp, int PN, const float* points3D, const float2* points2D,
+                            const float2* dL_dpoints2D, float* dL_dpoints3D, cudaStream_t stream);
 
 // View-parallel training: dL_dsh[p][k][c] = sum_v basis_k(dir(p, campos[v])) * dL_drgb[v][p][c]  (ggs_multiview.cu)
 constexpr int MAX_VIEWS = 16;
@@ -184,27 +213,6 @@ struct PushSlices {  // dest[s] = slot `rank` of rank s's reduce stage; slice s 
 void launch_push_rgb(int P, const double* grad_acc, const uint8_t* clamped, const int* radii, const float* campos,
                      const PushTargets& t, cudaStream_t stream);
 void launch_push_slices(const float4* send, const PushSlices& t, cudaStream_t stream);
-
-// ---- sampled median depth (sample_depth), ggs_sample_depth.cu ---------------------------------------------------
-void launch_sample_depth_forward(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
-                                 const uint2* gaussian_ranges, const uint2* point_ranges, const uint32_t* gaussian_list,
-                                 const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
-                                 uint32_t* n_contrib, float* median_depth, uint32_t* block_max_contributor,
-                                 float* output, uint8_t* inside, cudaStream_t stream);
-void launch_evaluate_sdf(const FrameParams& fp, int tiles, uint32_t max_blocks, const uint32_t* tile_offsets,
-                         const uint2* gaussian_ranges, const uint2* point_ranges, const uint32_t* gaussian_list,
-                         const uint32_t* point_list, const SplatRecord* records, const float2* points2D,
-                         const float* point_ts, float* out_depth, float* out_sdf, uint8_t* inside,
-                         cudaStream_t stream);
-void launch_sample_depth_backward(const FrameParams& fp, int tiles, uint32_t max_blocks,
-                                  const uint32_t* block_max_contributor, const uint32_t* tile_offsets,
-                                  const uint2* gaussian_ranges, const uint2* point_ranges,
-                                  const uint32_t* gaussian_list, const uint32_t* point_list,
-                                  const SplatRecord* records, const float2* points2D, const uint32_t* n_contrib,
-                                  const float* median_depth, const uint8_t* inside, const float* dL_doutputs,
-                                  float2* dL_dpoints2D, double* grad_acc, cudaStream_t stream);
-void launch_points_backward(const FrameParams& fp, int PN, const float* points3D, const uint32_t* touched,
-                            const float2* dL_dpoints2D, float* dL_dpoints3D, cudaStream_t stream);
 
 // Fused caller-side activations (ggs_activations.cu; scene/gaussian_model.py:158-160,203-212)
 void launch_activate_forward(int P, const float* raw_scaling, const float* raw_opacity, const float* raw_rotation,

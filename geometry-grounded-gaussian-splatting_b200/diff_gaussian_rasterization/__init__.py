@@ -27,7 +27,8 @@ import torch.nn as nn
 from . import _abi
 from ._abi import lib as _lib
 
-__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "activate_gaussians"]
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "PreparedView", "rasterize_gaussians",
+           "activate_gaussians"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -370,8 +371,7 @@ class _SampleDepth(torch.autograd.Function):
             nr, ne, nb = ctx.counts
             state = _abi.GgsSampleState(
                 _abi.ptr(b.get(_abi.SLOT_GEOMETRY)), _abi.ptr(b.get(_abi.SLOT_BINNING)), _abi.ptr(b.get(_abi.SLOT_POINT)),
-                _abi.ptr(b.get(_abi.SLOT_POINT_BINNING)), _abi.ptr(b.get(_abi.SLOT_TILE)),
-                _abi.ptr(b.get(_abi.SLOT_BLOCKS)), nr, ne, nb)
+                None, _abi.ptr(b.get(_abi.SLOT_TILE)), None, nr, ne, nb)
             grads = _abi.GgsGradients(_abi.ptr(d_means3D), _abi.ptr(d_means2D), _abi.ptr(d_colors),
                                       _abi.ptr(d_opacity), _abi.ptr(d_scales), _abi.ptr(d_rot))
             arena = _abi.Arena(device)
@@ -437,6 +437,86 @@ def activate_gaussians(raw_scaling, raw_opacity, raw_rotation, filter_3D):
     return _ActivateGaussians.apply(raw_scaling, raw_opacity, raw_rotation, filter_3D)
 
 
+class PreparedView:
+    """One view's Gaussians, binned once, for any number of point-query batches.
+
+    The reference bins the Gaussians of the view inside every `integrate` / `evaluate_sdf` call
+    (rasterizer_impl.cu:637-714, :861-936), i.e. once per (chunk, view) of mesh_extract_tetrahedra.py:65-87, and once
+    more for every round of its binary search.  `GaussianRasterizer.prepare(...)` does that half once; `integrate` and
+    `evaluate_sdf` of the returned object only bin the query points (no host synchronisation) and run the query
+    kernel.  Results are those of the one-shot methods, bit for bit.  No autograd (as in the reference)."""
+
+    def __init__(self, raster_settings, means3D, opacities, scales, rotations):
+        _check_means(means3D)
+        rs = raster_settings
+        self.raster_settings = rs
+        device = self.device = means3D.device
+        with torch.no_grad():
+            m3, op, sc, ro = (_dev_f32(t, device) for t in (means3D, opacities, scales, rotations))
+            self._keep = []
+            with torch.cuda.device(device):
+                # the reference's wrappers pass kernel_size 0.0 on the point-query paths (__init__.py:382,443)
+                self._frame = _frame(rs, device, self._keep, kernel_size=0.0)
+                g = _gaussians(m3, op, sc, ro, None, None, None, None, None, 0)
+                self._arena = arena = _abi.Arena(device)
+                self._view = _abi.GgsViewState()
+                n = _lib.ggs_view_prepare(C.byref(self._frame), C.byref(g), arena.fn, None, C.byref(self._view),
+                                          _abi.stream_handle(device))
+                arena.done()
+                if n < 0:
+                    if arena.error is not None:
+                        raise arena.error
+                    _abi.check(n, "ggs_view_prepare")
+        self.num_rendered = int(n)
+        self.count = int(m3.shape[0])
+
+    def _points(self, points3D):
+        if points3D.dim() != 2 or points3D.shape[1] != 3:
+            raise RuntimeError("points3D must have dimensions (num_points, 3)")
+        return _dev_f32(points3D, self.device)
+
+    def integrate(self, points3D):
+        """(1 - transmittance [PN], inside [PN] bool), as GaussianRasterizer.integrate."""
+        device = self.device
+        with torch.no_grad():
+            pts = self._points(points3D)
+            PN = pts.shape[0]
+            transmittance = torch.zeros(PN, dtype=torch.float32, device=device)
+            inside = torch.zeros(PN, dtype=torch.bool, device=device)
+            with torch.cuda.device(device):
+                arena = _abi.Arena(device)
+                rc = _lib.ggs_integrate_view(C.byref(self._frame), C.byref(self._view), _abi.ptr(pts), PN, arena.fn,
+                                             None, _abi.ptr(transmittance), _abi.ptr(inside),
+                                             _abi.stream_handle(device))
+                arena.done()
+                if rc < 0:
+                    if arena.error is not None:
+                        raise arena.error
+                    _abi.check(rc, "ggs_integrate_view")
+        return 1 - transmittance, inside
+
+    def evaluate_sdf(self, points3D):
+        """(median ray depth, depth minus the point's own ray depth, inside), as GaussianRasterizer.evaluate_sdf."""
+        device = self.device
+        with torch.no_grad():
+            pts = self._points(points3D)
+            PN = pts.shape[0]
+            depth = torch.zeros(PN, dtype=torch.float32, device=device)
+            sdf = torch.zeros(PN, dtype=torch.float32, device=device)
+            inside = torch.zeros(PN, dtype=torch.bool, device=device)
+            with torch.cuda.device(device):
+                arena = _abi.Arena(device)
+                rc = _lib.ggs_evaluate_sdf_view(C.byref(self._frame), C.byref(self._view), _abi.ptr(pts), PN, arena.fn,
+                                                None, _abi.ptr(depth), _abi.ptr(sdf), _abi.ptr(inside),
+                                                _abi.stream_handle(device))
+                arena.done()
+                if rc < 0:
+                    if arena.error is not None:
+                        raise arena.error
+                    _abi.check(rc, "ggs_evaluate_sdf_view")
+        return depth, sdf, inside
+
+
 class GaussianRasterizer(nn.Module):
     def __init__(self, raster_settings):
         super().__init__()
@@ -475,6 +555,11 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
         return rasterize_gaussians(means3D, means2D, shs, sg_axis, sg_sharpness, sg_color, colors_precomp, opacities,
                                    scales, rotations, cov3D_precomp, rs)
+
+    def prepare(self, means3D, opacities, scales, rotations):
+        """Bins this view's Gaussians once for repeated point queries (see PreparedView).  Not part of the reference's
+        surface: `integrate` / `evaluate_sdf` below keep its one-shot signatures."""
+        return PreparedView(self.raster_settings, means3D, opacities, scales, rotations)
 
     def integrate(self, points3D, means3D, opacities, scales=None, rotations=None, cov3D_precomp=None,
                   view2gaussian_precomp=None):

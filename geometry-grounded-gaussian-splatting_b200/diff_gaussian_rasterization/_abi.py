@@ -55,6 +55,11 @@ class GgsSampleState(C.Structure):
                 ("num_rendered", C.c_int64), ("num_evaluated", C.c_int64), ("num_blocks", C.c_int64)]
 
 
+class GgsViewState(C.Structure):
+    _fields_ = [("geometry", C.c_void_p), ("binning", C.c_void_p), ("tile", C.c_void_p),
+                ("num_rendered", C.c_int64), ("count", C.c_int64)]
+
+
 class GgsBackwardInputs(C.Structure):
     _fields_ = [("alpha", _f32p), ("normal", _f32p), ("mdepth", _f32p), ("radii", C.c_void_p),
                 ("dL_dcolor", _f32p), ("dL_dmdepth", _f32p), ("dL_dalpha", _f32p), ("dL_dnormal", _f32p)]
@@ -92,7 +97,7 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
-           "ggs_integrate_points", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
+           "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
            "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
@@ -133,6 +138,15 @@ def _load():
     lib.ggs_integrate_points.restype = C.c_int64
     lib.ggs_integrate_points.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.c_void_p, C.c_int64,
                                          ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_view_prepare.restype = C.c_int64
+    lib.ggs_view_prepare.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), ALLOC_FN, C.c_void_p,
+                                     C.POINTER(GgsViewState), C.c_void_p]
+    lib.ggs_integrate_view.restype = C.c_int
+    lib.ggs_integrate_view.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsViewState), C.c_void_p, C.c_int64, ALLOC_FN,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_evaluate_sdf_view.restype = C.c_int
+    lib.ggs_evaluate_sdf_view.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsViewState), C.c_void_p, C.c_int64,
+                                          ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_mark_visible.restype = C.c_int
     lib.ggs_mark_visible.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_describe_layout.restype = C.c_int

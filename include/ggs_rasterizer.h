@@ -14,10 +14,11 @@
  * Conventions
  *   - plain C: pointers, sizes and PODs only; no torch, STL or CUDA types in any signature;
  *   - every data pointer is a DEVICE pointer on the current CUDA device unless marked "host";
- *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it.  The forward and the
- *     point integration synchronise that stream once / twice to learn how many (tile, Gaussian)
- *     pairs exist, exactly where the reference issues its blocking cudaMemcpy
- *     (rasterizer_impl.cu:384, :676, :743);
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it.  Binning the Gaussians of a
+ *     view (ggs_rasterize_forward, ggs_view_prepare and the one-shot point queries built on it)
+ *     synchronises that stream once to learn how many (tile, Gaussian) pairs exist, where the reference
+ *     issues its blocking cudaMemcpy (rasterizer_impl.cu:384, :676).  Queries against a prepared view
+ *     never synchronise (the reference blocks a second time per call to count the points, :743);
  *   - the caller owns all memory.  Where the reference takes std::function<char*(size_t)> resize
  *     callbacks (rasterizer.h:30-33) this ABI takes ONE C callback, GgsAllocFn, tagged with the
  *     buffer slot it is asked to provide.  Buffers handed out in the forward must be passed back
@@ -185,6 +186,31 @@ GGS_API int ggs_sh_gradient_from_views(int64_t count, int32_t sh_degree, int32_t
                                const float* means3D, const float* campos, const float* dL_drgb, float* dL_dsh,
                                void* stream);
 
+/* ---- point queries against one view ---------------------------------------------------------------
+ * The reference bins the view's Gaussians inside every query call (evaluateTransmittance, sampleDepth, evaluateSDF:
+ * rasterizer_impl.cu:637-714, :861-936, :1084-1160), i.e. once per (chunk of points, view) of
+ * mesh_extract_tetrahedra.py:65-87.  Here that half is its own entry point: ggs_view_prepare runs preprocess, sort and
+ * tile ranges once (slots GEOMETRY, BINNING, TILE; colour is not evaluated, sh_degree / sg_degree of the frame are
+ * ignored) and the *_view entry points answer any number of query batches against it (slot POINT per call; no host
+ * synchronisation).  The one-shot entry points below them (= the reference's signatures) run both halves. */
+typedef struct GgsViewState {
+    void* geometry;
+    void* binning;
+    void* tile;
+    int64_t num_rendered; /* (tile, Gaussian) pairs */
+    int64_t count;        /* Gaussians the view was prepared with */
+} GgsViewState;
+/* Returns num_rendered (>= 0) or a negative GgsStatus.  The frame's kernel_size applies (the reference's wrappers pass
+ * 0 on these paths, __init__.py:382,443,513). */
+GGS_API int64_t ggs_view_prepare(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user,
+                         GgsViewState* view, void* stream);
+/* `frame` must describe the same camera and image as at preparation.  Outputs as for the one-shot entry points. */
+GGS_API int ggs_integrate_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D, int64_t num_points,
+                       GgsAllocFn alloc, void* user, float* out_transmittance, uint8_t* inside, void* stream);
+GGS_API int ggs_evaluate_sdf_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D,
+                          int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
+                          uint8_t* inside, void* stream);
+
 /* Transmittance of query points seen from `frame` (integrate): out_transmittance [PN] and
  * inside [PN] (uint8 0/1) must be zero-initialised by the caller.  Returns num_rendered. */
 GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
@@ -195,8 +221,8 @@ GGS_API int64_t ggs_integrate_points(const GgsFrame* frame, const GgsGaussians* 
  * (rasterizer.h:170,197; rasterize_points.cu:459-634; pybind sample_rasterized_depth[_backward], ext.cpp:21-22).
  * out_points [PN,3] (camera-space point on the ray through the query's pixel position at the median depth) and
  * inside [PN] (uint8) must be zero-initialised by the caller: queries that project outside the image are not
- * touched.  `state` receives the buffers the backward needs (slots GEOMETRY, BINNING, POINT, POINT_BINNING, TILE,
- * BLOCKS).  Returns num_rendered.  The reference's Python wrapper passes kernel_size = 0 to the forward and the
+ * touched.  `state` receives the buffers the backward needs (slots GEOMETRY, BINNING, POINT, TILE; point_binning and
+ * blocks are reserved and stay NULL).  Returns num_rendered.  The reference's Python wrapper passes kernel_size = 0 to the forward and the
  * settings' kernel_size to the backward (__init__.py:513,606); callers wanting parity do the same. */
 typedef struct GgsSampleState {
     void* geometry;
@@ -206,8 +232,8 @@ typedef struct GgsSampleState {
     void* tile;
     void* blocks;
     int64_t num_rendered;  /* (tile, Gaussian) pairs */
-    int64_t num_evaluated; /* query points inside the image */
-    int64_t num_blocks;    /* upper bound of (tile, round) blocks the kernels are launched with */
+    int64_t num_evaluated; /* query points handed in (how many fall inside the image stays on the device) */
+    int64_t num_blocks;    /* reserved */
 } GgsSampleState;
 
 GGS_API int64_t ggs_sample_depth_forward(const GgsFrame* frame, const GgsGaussians* gaussians, const float* points3D,
