@@ -20,6 +20,9 @@ and normal all carry upstream gradients) on the workload BASELINE.json quotes th
          has no CPU implementation of this path); same scene, same step, same timing.  Under torchrun
          rank 0 alone runs it.
   cpu_baseline       the C restatement (oracle/, OpenMP) timed on the host cores on a bounded sample.
+  --workload c5      the other shardable path (BASELINE config 5): the opacity test of the tetrahedral mesh extraction
+         (mesh_extract_tetrahedra.py:65-87) -- the 15-point stencil of a SH2 + 7-lobe model against V views, point
+         range per rank; metric = (point, view) queries/s.  See run_c5.
 
 Timing: CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks.  The
 working set (236 MB parameters + >500 MB binning buffers per step) exceeds the 126 MB L2, so no explicit
@@ -414,6 +417,231 @@ def cpu_baseline(seconds_budget=20.0):
                       f"with OpenMP on {os.cpu_count()} host threads; the reference has no CPU path"}
 
 
+
+def pipe_roofline(counts, stage_ms, sm_mhz, sms):
+    """Issue-pipe roofline of the two tile kernels (SURVEY.md 8(d) "ALGORITHMIC ops").  counts = (A, Cpairs, Cactive, Gpx)
+    from ggs_count_blend_ops: list positions visited, accepted (pixel, Gaussian) pairs, accepted pairs of the pixels
+    the bisection runs on, number of those pixels.  Per-pair constants of 8(d):
+      forward   pass 1: 1 MUFU + 22 FP32 per visited position; bisection: 80 MUFU + 355 FP32 per accepted pair of an
+                active pixel (5 ex2 for alpha + 37 depth samples x (ex2 + rsqrt), 37 x ~9 FP32 + the alpha arithmetic);
+      backward  pass A: 2 ex2 + 3 rcp and ~15 FP32 per accepted pair of an active pixel; pass B: 2 ex2 + 4 rcp and
+                ~120 FP32 per accepted pair.
+    Peaks: XU (MUFU) 16 lanes / clk / SM, FP32 128 lanes / clk / SM, at the SM clock measured during the run."""
+    A, C, Ca, G = (float(x) for x in counts)
+    clk = float(sm_mhz) * 1e6
+    peak = {"xu": sms * 16 * clk, "fp32": sms * 128 * clk}
+    ops = {"render_forward": {"xu": A + 80.0 * Ca, "fp32": 22.0 * A + 355.0 * Ca},
+           "render_backward": {"xu": 5.0 * Ca + 6.0 * C, "fp32": 15.0 * Ca + 120.0 * C}}
+    out = {}
+    for k, o in ops.items():
+        t = stage_ms.get(k)
+        if not t:
+            continue
+        fr = {p: o[p] / (t * 1e-3) / peak[p] for p in ("xu", "fp32")}
+        b = max(fr, key=fr.get)
+        out[k] = {"bound": b, "achieved": o[b] / (t * 1e-3) / 1e9, "peak": peak[b] / 1e9, "unit": "Gop/s",
+                  "frac": fr[b], "frac_xu": fr["xu"], "frac_fp32": fr["fp32"], "mufu_ops": o["xu"],
+                  "fp32_ops": o["fp32"], "ms": t}
+    return out
+
+
+def blend_op_counts(sc, device):
+    """(A, Cpairs, Cactive, Gpx) of the scene's forward (ggs_count_blend_ops; measurement, outside any timed region)."""
+    import ctypes as C
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
+    from diff_gaussian_rasterization import _abi
+
+    outs, inter, ctx = H.ours_forward_raw(sc, str(device), want_ctx=True)
+    counters = torch.zeros(4, dtype=torch.int64, device=device)
+    _abi.check(_abi.lib.ggs_count_blend_ops(C.byref(ctx["frame"]), C.byref(ctx["g"]), C.byref(ctx["state"]),
+                                            _abi.ptr(counters), _abi.stream_handle(torch.device(device))),
+               "ggs_count_blend_ops")
+    torch.cuda.synchronize()
+    return outs, inter, [int(v) for v in counters.tolist()]
+
+
+# ---- workload c5: opacity queries of the tetrahedral mesh extraction ---------------------------------------------
+C5_METRIC = "integrate (point, view) queries/s (C5: SH2 + 7 SG lobes model, 15-point stencil, all views)"
+
+
+def c5_settings(mod, sc, cam, device):
+    return mod.GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, kernel_size=0.0, bg=None,
+        scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(device), projmatrix=cam.projmatrix.to(device),
+        sh_degree=sc.sh_degree, sg_degree=sc.sg_degree, campos=cam.campos.to(device), prefiltered=False,
+        require_depth=True, debug=False)
+
+
+def c5_reference_loop(mod, points, settings, x, chunk_size=10_000_000):
+    """evaluage_alpha_cull as the reference runs it (mesh_extract_tetrahedra.py:65-87): chunk-major, one one-shot
+    integrate per (chunk, view)."""
+    sdf, valid = [], []
+    for chunk in torch.chunk(points, points.shape[0] // chunk_size + 1):
+        w = torch.ones(chunk.shape[0], dtype=torch.float32, device=chunk.device)
+        anyv = torch.zeros(chunk.shape[0], dtype=torch.bool, device=chunk.device)
+        for rs in settings:
+            alpha, inside = mod.GaussianRasterizer(rs).integrate(chunk, x[0], x[1], x[2], x[3], None, None)
+            anyv = torch.logical_or(anyv, inside)
+            w = torch.where(inside, torch.min(alpha, w), w)
+        w[torch.logical_not(anyv)] = 0
+        sdf.append(0.5 - w)
+        valid.append(anyv)
+    return torch.cat(sdf), torch.cat(valid)
+
+
+def c5_cpu_baseline(seconds_budget=20.0):
+    """C restatement of integrate on the host cores: a 100 k-Gaussian C5-shaped scene, 300 k stencil points, one view."""
+    from oracle.oracle import Oracle
+
+    sc = scenes.make_scene("c5", P=100_000)
+    pts = scenes.tetra_points(sc)[:300_000].contiguous()
+    c = sc.cam
+    kw = dict(points3D=pts, means3D=sc.means3D, opacities=sc.opacities, scales=sc.scales, rotations=sc.rotations,
+              viewmatrix=c.viewmatrix, projmatrix=c.projmatrix, campos=c.campos, tanfovx=c.tanfovx, tanfovy=c.tanfovy,
+              kernel_size=0.0, image_height=c.H, image_width=c.W)
+    orc = Oracle()
+    orc.integrate(**kw)
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        orc.integrate(**kw)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > seconds_budget or n >= 50:
+            break
+    return {"value": n * pts.shape[0] / dt / 1e6, "unit": "Mqueries/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{n} x integrate of 300000 stencil points against one 1237x822 view of a 100000-Gaussian C5-shaped "
+                      f"scene through the C oracle (OpenMP, {os.cpu_count()} host threads), Gaussian binning included as "
+                      "in the reference; the reference has no CPU path"}
+
+
+def run_c5(args, rank, world, local, device, multi):
+    """One step = the opacity test of ALL stencil points against ALL views (what the reference's
+    evaluage_alpha_cull computes once per query round).  Ours: parallel.alpha_cull -- Gaussians of a view binned once,
+    point range per rank, the two result arrays all-gathered at the end of the step (inside the timed region).
+    Reference arm: the reference's own chunk-major loop over its one-shot integrate, one GPU."""
+    import torch.distributed as dist
+
+    P, V = args.c5_gaussians, args.c5_views
+    sc = scenes.make_scene("c5", P=P)
+    cams = [scenes.config_camera("c5", v, V) for v in range(V)]
+    pts_host = scenes.tetra_points(sc).pin_memory()
+    n = pts_host.shape[0]
+    x = [getattr(sc, k).to(device) for k in ("means3D", "opacities", "scales", "rotations")]
+    if args.impl == "ours":
+        import diff_gaussian_rasterization as mod
+        from diff_gaussian_rasterization import _abi, parallel
+    else:
+        from oracle import ref_loader
+
+        if not ref_loader.available():
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_dgr/_C.so not built"}))
+            return 0
+        mod = ref_loader.load()
+    settings = [c5_settings(mod, sc, cam, device) for cam in cams]
+    points = pts_host.to(device)
+    n_ranks = world if multi else 1
+    lo, hi = (parallel.shard_range(n, rank, world) if multi else (0, n))
+
+    if args.impl == "ours":
+        def resident():
+            return parallel.alpha_cull(points, settings, *x)
+    else:
+        def resident():
+            return c5_reference_loop(mod, points, settings, x)
+
+    own_dev = torch.empty(hi - lo, 3, device=device)
+    sdf_host = torch.empty(hi - lo).pin_memory()
+    valid_host = torch.empty(hi - lo, dtype=torch.bool).pin_memory()
+
+    def end_to_end():
+        # this step's query points from pinned host memory, its two result arrays back to the host.  With several ranks
+        # every rank's own range arrives from ITS host and goes back to it (gather=False): the hosts of one node
+        # together hold the result
+        if multi:
+            points[lo:hi].copy_(pts_host[lo:hi], non_blocking=True)
+            sdf, valid = parallel.alpha_cull(points, settings, *x, gather=False)
+        else:
+            own_dev.copy_(pts_host, non_blocking=True)
+            if args.impl == "ours":
+                sdf, valid = parallel.alpha_cull(own_dev, settings, *x)
+            else:
+                sdf, valid = c5_reference_loop(mod, own_dev, settings, x)
+        sdf_host.copy_(sdf, non_blocking=True)
+        valid_host.copy_(valid, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        resident()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, clocks = timed(resident, args.steps, args.warmup, n_ranks, sampler)
+    ms_per_step = ms / args.steps
+    value = n * V / (ms_per_step * 1e-3) / 1e6
+    ms_e2e, _ = timed(end_to_end, args.steps, args.warmup, n_ranks, None)
+    e2e_value = n * V / (ms_e2e / args.steps * 1e-3) / 1e6
+    if rank != 0:
+        return 0
+    chunks = len(torch.chunk(points[lo:hi], (hi - lo) // 10_000_000 + 1))
+    line = {
+        "metric": C5_METRIC, "value": value, "unit": "Mqueries/s", "n_gpus": n_ranks, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"c5: {P} Gaussians (SH2 + 7 SG lobes), {n} stencil points (15 per Gaussian), {V} views "
+                               f"of {cams[0].W}x{cams[0].H}, chunks of <= 10 M points",
+                   "parallelism": (f"point range per rank x{n_ranks} (no data-path collective), all-gather of sdf + valid "
+                                   "(5 B/point) at the end of the step") if multi else "single GPU",
+                   "l2": f"query points + workspaces ({n * 52 // 2**20} MiB per view pass) exceed the 126 MB L2; no explicit flush"},
+        "e2e": {"value": e2e_value, "unit": "Mqueries/s", "h2d_bytes_per_step": (hi - lo) * 12,
+                "d2h_bytes_per_step": (hi - lo) * 5},
+        "clocks": clocks,
+    }
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["gpu_launches"] = 0
+        line["cpu_baseline"] = {"value": value, "unit": "Mqueries/s", "cores": 0, "kind": "reference",
+                                "sample": "the reference CUDA rasterizer's integrate (oracle/_ref, unmodified sources) in the "
+                                          "reference's own chunk-major loop on one B200; it has no CPU implementation"}
+    else:
+        # per (view, chunk): query_project, histogram, offsets, 3 onesweep passes, ranges, rounds, scan, block table,
+        # integrate = 11; per view: preprocess, depth pre-sort (6), scan, duplicate, tile sort (offsets + passes), ranges
+        line["gpu_launches"] = args.steps * V * (chunks * 11 + 13)
+        # the query kernel against the XU pipe: pair counts from the counted variant on view 0, kernel time from the
+        # in-library events (separate untimed pass)
+        view = mod.GaussianRasterizer(settings[0]).prepare(*x)
+        counters = torch.zeros(3, dtype=torch.int64, device=device)
+        first = torch.chunk(points[lo:hi], (hi - lo) // 10_000_000 + 1)[0]
+        view.integrate(first, op_counters=counters)
+        _abi.profile_enable(True)
+        tk, tb, reps = 0.0, 0.0, 5
+        for _ in range(reps):
+            view.integrate(first)
+            t = _abi.profile_read()
+            tk += t["query_kernel_ms"] / reps
+            tb += t["query_binning_ms"] / reps
+        _abi.profile_enable(False)
+        ev, acc, staged = (int(v) for v in counters.tolist())
+        sms = torch.cuda.get_device_properties(device).multi_processor_count
+        clk = float((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+        mufu = 3.0 * acc + (ev - acc)  # alpha ex2 for every pair evaluated, + ex2 + rsqrt for the accepted ones
+        hbm, how, _ = peaks()
+        line["roofline"] = {
+            "kernel": "integrate_kernel", "bound": "xu", "achieved": mufu / (tk * 1e-3) / 1e9,
+            "peak": sms * 16 * clk / 1e9, "unit": "Gop/s", "frac": mufu / (tk * 1e-3) / (sms * 16 * clk),
+            "traffic": None, "ms": tk, "points": int(first.shape[0]), "pairs_evaluated": ev, "pairs_accepted": acc,
+            "list_entries_staged": staged,
+            "note": "MUFU ops = 3 per accepted pair (alpha ex2, depth-profile ex2, rsqrt) + 1 per evaluated, rejected "
+                    "pair; the reference evaluates every (point, list entry) pair",
+            "query_binning": {"ms": tb, "alg_bytes": int(first.shape[0]) * (12 + 16 + 3 * 16 + 8),
+                              "frac_hbm": int(first.shape[0]) * 84 / (tb * 1e-3) / 1e9 / hbm, "peak_source": how}}
+        if not args.no_cpu_baseline and not multi:
+            line["cpu_baseline"] = c5_cpu_baseline()
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -422,6 +650,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--c5-gaussians", type=int, default=1_000_000)
+    ap.add_argument("--c5-views", type=int, default=8)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -439,6 +669,13 @@ def main():
         _quiet_nccl()
         dist.init_process_group("nccl", device_id=device)
         guard = watchdog(float(os.environ.get("GGS_BENCH_WATCHDOG_S", "600")), rank)
+
+    if args.workload == "c5":
+        rc = run_c5(args, rank, world, local, device, multi)
+        if multi:
+            guard.cancel()
+            torch.distributed.destroy_process_group()
+        return rc
 
     if args.impl == "ours":
         import diff_gaussian_rasterization as mod
@@ -541,11 +778,7 @@ def main():
         # launches of OUR kernels per fwd+bwd step (counted from the stage sequence in ggs_api.cu):
         # preprocess, scan, duplicate, histogram, offsets, 6 onesweep passes, ranges, render fwd, render bwd,
         # gaussian bwd
-        outs, inter = None, None
-        sys.path.insert(0, os.path.join(ROOT, "tests"))
-        import helpers as H
-
-        outs, inter = H.ours_forward_raw(sc, str(device))
+        outs, inter, counts = blend_op_counts(sc, device)
         stats = {"P": sc.P, "visible": int((outs["radii"] > 0).sum()), "num_rendered": inter["num_rendered"],
                  "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
         stats["sort_passes_run"] = sort_passes_run
@@ -578,11 +811,37 @@ def main():
                     if st in per_stage:
                         per_stage[st]["dram_bytes_ncu"] = traffic[st]
         dom = max(per_stage, key=lambda k: per_stage[k]["ms"])
-        line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": per_stage[dom]["gbs"], "peak": hbm,
-                            "unit": "GB/s", "frac": per_stage[dom]["frac_hbm"], "traffic": traffic.get(dom),
-                            "traffic_source": traffic_src, "peak_source": how,
-                            "note": "render kernels are issue-bound (MUFU/FP32), not HBM-bound; see DESIGN.md "
-                                    "and profiles/ for pipe utilisation"}
+        sms = torch.cuda.get_device_properties(device).multi_processor_count
+        pipes = pipe_roofline(counts, {k: v["ms"] for k, v in per_stage.items()},
+                              (clocks or {}).get("sm_mhz") or 1965.0, sms)
+        for k, v in pipes.items():
+            per_stage[k]["pipes"] = v
+        stats.update(list_positions_visited=counts[0], accepted_pairs=counts[1], accepted_pairs_active=counts[2],
+                     bisection_pixels=counts[3])
+        if dom in pipes:
+            # the dominant kernel is a tile kernel: bounded by an issue pipe, not by HBM (its working set is L2-resident)
+            pr = pipes[dom]
+            line["roofline"] = {"kernel": dom, "bound": pr["bound"], "achieved": pr["achieved"], "peak": pr["peak"],
+                                "unit": "Gop/s", "frac": pr["frac"], "frac_xu": pr["frac_xu"],
+                                "frac_fp32": pr["frac_fp32"], "traffic": traffic.get(dom),
+                                "traffic_source": traffic_src,
+                                "peak_source": f"{sms} SMs x 16 (XU) / 128 (FP32) lanes per clock at the SM clock sampled "
+                                               "during the run",
+                                "ops": "algorithmic, SURVEY.md 8(d): counts from ggs_count_blend_ops x per-pair constants",
+                                "hbm": {"achieved": per_stage[dom]["gbs"], "peak": hbm, "unit": "GB/s",
+                                        "frac": per_stage[dom]["frac_hbm"], "peak_source": how}}
+        else:
+            line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": per_stage[dom]["gbs"], "peak": hbm,
+                                "unit": "GB/s", "frac": per_stage[dom]["frac_hbm"], "traffic": traffic.get(dom),
+                                "traffic_source": traffic_src, "peak_source": how}
+        if "sort" in per_stage:
+            st = per_stage["sort"]
+            st["alg_bytes_reference"] = st.pop("alg_bytes")  # six 8-bit passes over 12-byte pairs (what the reference moves)
+            st["frac_hbm_reference_bytes"] = st.pop("frac_hbm")
+            st["gbs_reference_bytes"] = st.pop("gbs")
+            st["bytes_moved"] = stats["sort_bytes_moved"]
+            st["gbs"] = stats["sort_bytes_moved"] / st["ms"] / 1e6
+            st["frac_hbm"] = st["gbs"] / hbm
         line["stages"] = per_stage
         line["scene"] = stats
         if not args.no_cpu_baseline and not multi:

@@ -36,10 +36,11 @@ int fail(int code, const std::string& msg) {
     } while (0)
 
 // ---- optional per-stage device timing (ggs_profile_enable / ggs_profile_read) -------------------
-enum { EV_F0, EV_PRE, EV_ORDER, EV_SCAN, EV_DUP0, EV_DUP, EV_SORT, EV_RANGES, EV_RENDER, EV_B0, EV_RBWD, EV_GBWD, EV_COUNT };
+enum { EV_F0, EV_PRE, EV_ORDER, EV_SCAN, EV_DUP0, EV_DUP, EV_SORT, EV_RANGES, EV_RENDER, EV_B0, EV_RBWD, EV_GBWD,
+       EV_Q0, EV_QBIN, EV_QRUN, EV_COUNT };
 struct Profiler {
     bool on = false;
-    bool have_fwd = false, have_bwd = false;
+    bool have_fwd = false, have_bwd = false, have_query = false;
     cudaEvent_t ev[EV_COUNT] = {};
     bool created = false;
     int sort_passes = 0;
@@ -586,7 +587,7 @@ int ggs_activate_backward(int64_t count, const float* raw_scaling, const float* 
 
 int ggs_profile_enable(int on) {
     g_prof.on = on != 0;
-    g_prof.have_fwd = g_prof.have_bwd = false;
+    g_prof.have_fwd = g_prof.have_bwd = g_prof.have_query = false;
     return GGS_OK;
 }
 
@@ -615,6 +616,11 @@ int ggs_profile_read(GgsStageTimes* t) {
         if ((rc = span(EV_RBWD, EV_GBWD, &t->gaussian_backward_ms))) return rc;
         t->have_backward = 1;
     }
+    if (g_prof.have_query) {
+        if ((rc = span(EV_Q0, EV_QBIN, &t->query_binning_ms))) return rc;
+        if ((rc = span(EV_QBIN, EV_QRUN, &t->query_kernel_ms))) return rc;
+        t->have_query = 1;
+    }
     return GGS_OK;
 }
 
@@ -627,6 +633,29 @@ int ggs_mark_visible(const float* means3D, int64_t count, const float* viewmatri
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     launch_mark_visible((int)count, means3D, viewmatrix, present, stream);
     GGS_STAGE("mark_visible", false, stream);
+    return GGS_OK;
+}
+
+int ggs_count_blend_ops(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                        uint64_t* counters, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FrameParams fp;
+    GaussianInputs in;
+    int rc = make_frame(frame, gaussians, fp, in);
+    if (rc) return rc;
+    if (!state || !counters) return fail(GGS_ERR_INVALID_ARGUMENT, "null state / counters");
+    if (fp.P == 0) {
+        GGS_CUDA(cudaMemsetAsync(counters, 0, 32, stream));
+        return GGS_OK;
+    }
+    if (!state->geometry || !state->binning || !state->tile) return fail(GGS_ERR_INVALID_ARGUMENT, "forward state is incomplete");
+    const int tiles = fp.gx * fp.gy;
+    const GeomLayout GL = geom_layout(fp.P);
+    const TileLayout TL = tile_layout(tiles);
+    launch_count_blend_ops(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state->num_rendered, tiles),
+                           at<SplatRecord>(state->geometry, GL.records),
+                           reinterpret_cast<unsigned long long*>(counters), stream);
+    GGS_STAGE("count_blend_ops", false, stream);
     return GGS_OK;
 }
 
@@ -763,7 +792,7 @@ enum QueryKind { Q_INTEGRATE, Q_SAMPLE, Q_SDF };
 // Bins the query points and runs one forward kernel.  `ws_out`: the query workspace (GGS_SLOT_POINT).
 int run_query(QueryKind kind, const GgsFrame* frame, const GgsViewState* view, const float* points3D,
               int64_t num_points, GgsAllocFn alloc, void* user, float* out_a, float* out_b, uint8_t* inside,
-              void** ws_out, cudaStream_t stream) {
+              void** ws_out, cudaStream_t stream, uint64_t* op_counters = nullptr) {
     FrameParams fp;
     int rc = query_frame(frame, view, fp);
     if (rc) return rc;
@@ -780,20 +809,25 @@ int run_query(QueryKind kind, const GgsFrame* frame, const GgsViewState* view, c
     void* ws = alloc(GGS_SLOT_POINT, QL.bytes, user);
     if (!ws) return fail(GGS_ERR_ALLOC, "query workspace allocation failed");
     if (ws_out) *ws_out = ws;
+    prof_mark(stream, EV_Q0);
     launch_query_binning(fp, PN, points3D, ws, QL, stream);
     GGS_STAGE("query_binning", debug, stream);
+    prof_mark(stream, EV_QBIN);
     const GeomLayout GL = geom_layout(fp.P);
     const ViewTileLayout TL = view_tile_layout(tiles, fp.P);
     const uint2* granges = at<uint2>(view->tile, TL.granges);
     const uint32_t* glist = sorted_list(view->binning, view->num_rendered, tiles);
     const SplatRecord* records = at<SplatRecord>(view->geometry, GL.records);
     if (kind == Q_INTEGRATE)
-        launch_integrate(QL, ws, granges, glist, records, out_a, inside, stream);
+        launch_integrate(QL, ws, granges, glist, records, out_a, inside,
+                         reinterpret_cast<unsigned long long*>(op_counters), stream);
     else if (kind == Q_SAMPLE)
         launch_sample_depth_forward(fp, QL, ws, granges, glist, records, out_a, inside, stream);
     else
         launch_evaluate_sdf(fp, QL, ws, granges, glist, records, out_a, out_b, inside, stream);
     GGS_STAGE("query", debug, stream);
+    prof_mark(stream, EV_QRUN);
+    g_prof.have_query = g_prof.on;
     return GGS_OK;
 }
 
@@ -812,6 +846,14 @@ int ggs_integrate_view(const GgsFrame* frame, const GgsViewState* view, const fl
                        GgsAllocFn alloc, void* user, float* out_transmittance, uint8_t* inside, void* stream) {
     return run_query(Q_INTEGRATE, frame, view, points3D, num_points, alloc, user, out_transmittance, nullptr, inside,
                      nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int ggs_integrate_view_counted(const GgsFrame* frame, const GgsViewState* view, const float* points3D,
+                               int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
+                               uint8_t* inside, uint64_t* op_counters, void* stream) {
+    if (!op_counters) return fail(GGS_ERR_INVALID_ARGUMENT, "null counters");
+    return run_query(Q_INTEGRATE, frame, view, points3D, num_points, alloc, user, out_transmittance, nullptr, inside,
+                     nullptr, static_cast<cudaStream_t>(stream), op_counters);
 }
 
 int ggs_evaluate_sdf_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D, int64_t num_points,

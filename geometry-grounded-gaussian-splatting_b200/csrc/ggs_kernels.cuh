@@ -160,8 +160,10 @@ struct QueryLayout {
 QueryLayout query_layout(size_t PN, int tiles, bool sample);
 void launch_query_binning(const FrameParams& fp, int PN, const float* points3D, void* ws, const QueryLayout& L,
                           cudaStream_t stream);
+// op_counters (measurement, may be null): u64[3] += pairs evaluated after culling, accepted pairs, list entries staged
 void launch_integrate(const QueryLayout& L, void* ws, const uint2* gaussian_ranges, const uint32_t* gaussian_list,
-                      const SplatRecord* records, float* out_transmittance, uint8_t* inside, cudaStream_t stream);
+                      const SplatRecord* records, float* out_transmittance, uint8_t* inside,
+                      unsigned long long* op_counters, cudaStream_t stream);
 void launch_sample_depth_forward(const FrameParams& fp, const QueryLayout& L, void* ws, const uint2* gaussian_ranges,
                                  const uint32_t* gaussian_list, const SplatRecord* records, float* output,
                                  uint8_t* inside, cudaStream_t stream);
@@ -222,6 +224,10 @@ void launch_activate_backward(int P, const float* raw_scaling, const float* raw_
                               const float* filter_3D, const float* dL_dscales, const float* dL_dopacities,
                               const float* dL_drotations, float* dL_draw_scaling, float* dL_draw_opacity,
                               float* dL_draw_rotation, cudaStream_t stream);
+
+// measurement only (ggs_counters.cu): counters[4] = walked, accepted, accepted on bisection-active pixels, active pixels
+void launch_count_blend_ops(const FrameParams& fp, const uint2* ranges, const uint32_t* list,
+                            const SplatRecord* records, unsigned long long* counters, cudaStream_t stream);
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 

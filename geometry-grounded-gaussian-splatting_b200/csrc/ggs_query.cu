@@ -254,14 +254,19 @@ __device__ __forceinline__ int scatter_component(const int lane) {
 }
 
 // ---- integrate --------------------------------------------------------------------------------------------------
+// COUNT: measurement only -- counters[0] += (query, entry) pairs evaluated after the warp-level culling,
+// counters[1] += pairs that pass the power / alpha tests and update the transmittance (the algorithmic pairs:
+// 2 ex2 + 1 rsqrt each on top of the alpha ex2), counters[2] += list entries the CTAs staged.
+template <bool COUNT>
 __global__ void __launch_bounds__(Q_THREADS, 8)
     integrate_kernel(const uint32_t* __restrict__ block_tile, const uint32_t* __restrict__ tile_offsets,
                      const uint2* __restrict__ gaussian_ranges, const uint2* __restrict__ query_ranges,
                      const uint32_t* __restrict__ gaussian_list, const uint32_t* __restrict__ query_list,
                      const SplatRecord* __restrict__ records, const float2* __restrict__ points2D,
                      const float* __restrict__ point_ts, float* __restrict__ out_transmittance,
-                     uint8_t* __restrict__ inside) {
+                     uint8_t* __restrict__ inside, unsigned long long* __restrict__ counters) {
     __shared__ __align__(16) float4 s_rec[2 * Q_BATCH * Q_QUADS];
+    uint32_t n_eval = 0, n_acc = 0, n_staged = 0;
     Job job;
     if (!locate_job(block_tile, tile_offsets, gaussian_ranges, query_ranges, query_list, job)) return;
     const uint32_t tid = threadIdx.x, lane = tid & 31;
@@ -290,6 +295,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
             if (e + Q_BATCH < n) id_next = __ldg(list + e + Q_BATCH);
         }
         const int lim = min((uint32_t)Q_BATCH, n - i * Q_BATCH);
+        if constexpr (COUNT) n_staged += tid < (uint32_t)lim ? 1u : 0u;
         for (int w = 0; w * 32 < lim; w++) {
             if (__all_sync(Q_FULL, done)) break;
             const int jl = w * 32 + lane;
@@ -300,6 +306,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                 const int jj = __ffs(cand) - 1;
                 cand &= cand - 1;
                 if (done) continue;
+                if constexpr (COUNT) n_eval++;
                 const float4* rec = buf + (w * 32 + jj) * Q_QUADS;
                 const float4 q0 = rec[0];
                 const float4 q1 = rec[1];
@@ -322,6 +329,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                 const float rvacancy = rsqrtf(one_minus_gaussian);
                 T_point *= (pt > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
                 T_gaussian = test_T;
+                if constexpr (COUNT) n_acc++;
             }
         }
     }
@@ -329,6 +337,15 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
     if (job.valid) {
         out_transmittance[job.pid] = T_point;
         inside[job.pid] = 1;
+    }
+    if constexpr (COUNT) {
+        const uint32_t e = __reduce_add_sync(Q_FULL, n_eval), a = __reduce_add_sync(Q_FULL, n_acc),
+                       st = __reduce_add_sync(Q_FULL, n_staged);
+        if (lane == 0) {
+            atomicAdd(counters, (unsigned long long)e);
+            atomicAdd(counters + 1, (unsigned long long)a);
+            atomicAdd(counters + 2, (unsigned long long)st);
+        }
     }
 }
 
@@ -926,12 +943,18 @@ QueryPtrs query_ptrs(void* ws, const QueryLayout& L) {
 }  // namespace
 
 void launch_integrate(const QueryLayout& L, void* ws, const uint2* gaussian_ranges, const uint32_t* gaussian_list,
-                      const SplatRecord* records, float* out_transmittance, uint8_t* inside, cudaStream_t stream) {
+                      const SplatRecord* records, float* out_transmittance, uint8_t* inside,
+                      unsigned long long* op_counters, cudaStream_t stream) {
     if (L.max_blocks == 0) return;
     const QueryPtrs q = query_ptrs(ws, L);
-    integrate_kernel<<<L.max_blocks, Q_THREADS, 0, stream>>>(q.block_tile, q.offsets, gaussian_ranges, q.ranges,
-                                                            gaussian_list, q.list, records, q.xy, q.ts,
-                                                            out_transmittance, inside);
+    if (op_counters)
+        integrate_kernel<true><<<L.max_blocks, Q_THREADS, 0, stream>>>(q.block_tile, q.offsets, gaussian_ranges, q.ranges,
+                                                                      gaussian_list, q.list, records, q.xy, q.ts,
+                                                                      out_transmittance, inside, op_counters);
+    else
+        integrate_kernel<false><<<L.max_blocks, Q_THREADS, 0, stream>>>(q.block_tile, q.offsets, gaussian_ranges,
+                                                                       q.ranges, gaussian_list, q.list, records, q.xy,
+                                                                       q.ts, out_transmittance, inside, nullptr);
 }
 
 void launch_sample_depth_forward(const FrameParams& fp, const QueryLayout& L, void* ws, const uint2* gaussian_ranges,

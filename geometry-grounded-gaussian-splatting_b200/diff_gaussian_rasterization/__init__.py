@@ -475,8 +475,9 @@ class PreparedView:
             raise RuntimeError("points3D must have dimensions (num_points, 3)")
         return _dev_f32(points3D, self.device)
 
-    def integrate(self, points3D):
-        """(1 - transmittance [PN], inside [PN] bool), as GaussianRasterizer.integrate."""
+    def integrate(self, points3D, op_counters=None):
+        """(1 - transmittance [PN], inside [PN] bool), as GaussianRasterizer.integrate.  `op_counters` (measurement
+        only): an int64 [3] device tensor that receives the kernel's pair counts (ggs_integrate_view_counted)."""
         device = self.device
         with torch.no_grad():
             pts = self._points(points3D)
@@ -485,9 +486,14 @@ class PreparedView:
             inside = torch.zeros(PN, dtype=torch.bool, device=device)
             with torch.cuda.device(device):
                 arena = _abi.Arena(device)
-                rc = _lib.ggs_integrate_view(C.byref(self._frame), C.byref(self._view), _abi.ptr(pts), PN, arena.fn,
-                                             None, _abi.ptr(transmittance), _abi.ptr(inside),
-                                             _abi.stream_handle(device))
+                if op_counters is not None:
+                    rc = _lib.ggs_integrate_view_counted(C.byref(self._frame), C.byref(self._view), _abi.ptr(pts), PN,
+                                                         arena.fn, None, _abi.ptr(transmittance), _abi.ptr(inside),
+                                                         _abi.ptr(op_counters), _abi.stream_handle(device))
+                else:
+                    rc = _lib.ggs_integrate_view(C.byref(self._frame), C.byref(self._view), _abi.ptr(pts), PN, arena.fn,
+                                                 None, _abi.ptr(transmittance), _abi.ptr(inside),
+                                                 _abi.stream_handle(device))
                 arena.done()
                 if rc < 0:
                     if arena.error is not None:

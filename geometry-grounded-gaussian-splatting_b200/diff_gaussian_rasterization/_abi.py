@@ -89,7 +89,9 @@ class GgsLayout(C.Structure):
 class GgsStageTimes(C.Structure):
     _fields_ = [("have_forward", C.c_int32), ("have_backward", C.c_int32)] + [(n, C.c_float) for n in (
         "preprocess_ms", "scan_ms", "duplicate_ms", "sort_ms", "ranges_ms", "render_forward_ms",
-        "render_backward_ms", "gaussian_backward_ms")] + [("sort_passes", C.c_int32), ("depth_order_ms", C.c_float)]
+        "render_backward_ms", "gaussian_backward_ms")] + [("sort_passes", C.c_int32), ("depth_order_ms", C.c_float),
+                                                          ("have_query", C.c_int32), ("query_binning_ms", C.c_float),
+                                                          ("query_kernel_ms", C.c_float)]
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
@@ -97,7 +99,7 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
-           "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_describe_layout", "ggs_sort_scratch_bytes",
+           "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_integrate_view_counted", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_count_blend_ops", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
            "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
@@ -144,11 +146,17 @@ def _load():
     lib.ggs_integrate_view.restype = C.c_int
     lib.ggs_integrate_view.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsViewState), C.c_void_p, C.c_int64, ALLOC_FN,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_integrate_view_counted.restype = C.c_int
+    lib.ggs_integrate_view_counted.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsViewState), C.c_void_p, C.c_int64,
+                                               ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_evaluate_sdf_view.restype = C.c_int
     lib.ggs_evaluate_sdf_view.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsViewState), C.c_void_p, C.c_int64,
                                           ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ggs_mark_visible.restype = C.c_int
     lib.ggs_mark_visible.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ggs_count_blend_ops.restype = C.c_int
+    lib.ggs_count_blend_ops.argtypes = [C.POINTER(GgsFrame), C.POINTER(GgsGaussians), C.POINTER(GgsForwardState),
+                                        C.c_void_p, C.c_void_p]
     lib.ggs_describe_layout.restype = C.c_int
     lib.ggs_describe_layout.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.POINTER(GgsLayout)]
     lib.ggs_sort_scratch_bytes.restype = C.c_size_t

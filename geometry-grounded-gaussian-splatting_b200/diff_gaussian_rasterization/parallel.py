@@ -238,3 +238,70 @@ def integrate_sharded(integrate: Callable[[torch.Tensor], tuple[torch.Tensor, to
         out_a[rlo:rhi] = a_all[r * cap:r * cap + (rhi - rlo)]
         out_i[rlo:rhi] = i_all[r * cap:r * cap + (rhi - rlo)].bool()
     return out_a, out_i
+
+
+def alpha_cull(points3D: torch.Tensor, views: Sequence, means3D, opacities, scales, rotations, *,
+               chunk_size: int = 10_000_000, validate: Callable | None = None, group=None,
+               gather: bool = True, prepare: Callable | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """The opacity test of the tetrahedral mesh extraction over all views (`evaluage_alpha_cull`,
+    mesh_extract_tetrahedra.py:65-87): per point the minimum over the views that see it of the integrated opacity.
+    Returns `(sdf = 0.5 - min_alpha  [N], any_valid [N] bool)`.
+
+    `views`: one `GaussianRasterizationSettings` per camera.  `validate(view_index, points, inside) -> bool [n]` is the
+    reference's `evaluation_validation` (its ground-truth-mask test); None keeps `inside`.
+
+    What differs from the reference's loop, not from its result:
+      * view-major instead of chunk-major: the Gaussians of a view are binned ONCE (`GaussianRasterizer.prepare`) and
+        every chunk is queried against that state, where the reference re-runs preprocess + sort for every
+        (chunk, view) pair (rasterizer_impl.cu:637-714).  min() over views and or() are order independent and exact;
+      * with a process group, rank r owns the contiguous point range `shard_range(N, r, world)` (queries are
+        independent: no data-path collective) and the two result arrays are all-gathered at the end, 5 bytes per
+        point (`gather=False` returns the rank's own range instead).
+    `prepare(settings) -> object with .integrate(points)` replaces `GaussianRasterizer(settings).prepare(...)` (tests of
+    the sharding logic on CPU tensors)."""
+    if prepare is None:
+        from . import GaussianRasterizer
+
+        def prepare(rs):
+            return GaussianRasterizer(rs).prepare(means3D, opacities, scales, rotations)
+
+    n = points3D.shape[0]
+    sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    world, rank = (dist.get_world_size(group), dist.get_rank(group)) if sharded else (1, 0)
+    lo, hi = shard_range(n, rank, world)
+    mine = points3D[lo:hi]
+    m = hi - lo
+    device = points3D.device
+    weight = torch.ones(m, dtype=torch.float32, device=device)
+    any_valid = torch.zeros(m, dtype=torch.bool, device=device)
+    chunks = [(a, min(a + chunk_size, m)) for a in range(0, m, chunk_size)]
+    for vi, rs in enumerate(views):
+        view = prepare(rs)
+        for a, b in chunks:
+            pts = mine[a:b]
+            alpha, inside = view.integrate(pts)
+            valid = inside if validate is None else validate(vi, pts, inside)
+            any_valid[a:b] |= valid
+            w = weight[a:b]
+            weight[a:b] = torch.where(valid, torch.min(alpha, w), w)
+        del view
+    weight[~any_valid] = 0
+    sdf = 0.5 - weight
+    if not sharded or not gather:
+        return sdf, any_valid
+    cap = (n + world - 1) // world
+    s_pad = torch.zeros(cap, dtype=torch.float32, device=device)
+    v_pad = torch.zeros(cap, dtype=torch.uint8, device=device)
+    s_pad[:m] = sdf
+    v_pad[:m] = any_valid.to(torch.uint8)
+    s_all = torch.empty(world * cap, dtype=torch.float32, device=device)
+    v_all = torch.empty(world * cap, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(s_all, s_pad, group=group)
+    dist.all_gather_into_tensor(v_all, v_pad, group=group)
+    out_s = torch.empty(n, dtype=torch.float32, device=device)
+    out_v = torch.empty(n, dtype=torch.bool, device=device)
+    for r in range(world):
+        rlo, rhi = shard_range(n, r, world)
+        out_s[rlo:rhi] = s_all[r * cap:r * cap + (rhi - rlo)]
+        out_v[rlo:rhi] = v_all[r * cap:r * cap + (rhi - rlo)].bool()
+    return out_s, out_v

@@ -207,6 +207,12 @@ GGS_API int64_t ggs_view_prepare(const GgsFrame* frame, const GgsGaussians* gaus
 /* `frame` must describe the same camera and image as at preparation.  Outputs as for the one-shot entry points. */
 GGS_API int ggs_integrate_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D, int64_t num_points,
                        GgsAllocFn alloc, void* user, float* out_transmittance, uint8_t* inside, void* stream);
+/* Measurement variant: as ggs_integrate_view, and adds to three device counters (caller-zeroed) [0] the (query, entry)
+ * pairs evaluated after the warp-level culling, [1] the pairs that pass the power / alpha tests (the algorithmic
+ * pairs of SURVEY.md 8(a) A9: 2 ex2 + 1 rsqrt each besides the alpha ex2), [2] the list entries staged. */
+GGS_API int ggs_integrate_view_counted(const GgsFrame* frame, const GgsViewState* view, const float* points3D,
+                               int64_t num_points, GgsAllocFn alloc, void* user, float* out_transmittance,
+                               uint8_t* inside, uint64_t* op_counters, void* stream);
 GGS_API int ggs_evaluate_sdf_view(const GgsFrame* frame, const GgsViewState* view, const float* points3D,
                           int64_t num_points, GgsAllocFn alloc, void* user, float* out_depth, float* out_sdf,
                           uint8_t* inside, void* stream);
@@ -333,9 +339,22 @@ typedef struct GgsStageTimes {
     float render_backward_ms, gaussian_backward_ms;
     int32_t sort_passes; /* radix passes over the (tile, Gaussian) pairs the most recent forward ran */
     float depth_order_ms; /* depth pre-sort of the Gaussians (between preprocess and scan) */
+    /* most recent point query (integrate / sample_depth forward / evaluate_sdf): projecting + sorting + slicing the
+     * query points, and the query kernel itself */
+    int32_t have_query;
+    float query_binning_ms, query_kernel_ms;
 } GgsStageTimes;
 GGS_API int ggs_profile_enable(int on);
 GGS_API int ggs_profile_read(GgsStageTimes* times);
+
+/* ---- measurement: algorithmic operation counts of the tile blend ----------------------------------------
+ * Re-walks every pixel's list of a finished forward with the reference's accept / stop rules
+ * (render_forward.cu:477-532) and writes four device counters: [0] list positions visited, [1] accepted
+ * (pixel, Gaussian) pairs, [2] accepted pairs of the pixels the median-depth bisection runs on (final T <= 0.45),
+ * [3] the number of those pixels.  bench.py turns them into the FP32 / XU pipe roofline; nothing on
+ * the product path calls it. */
+GGS_API int ggs_count_blend_ops(const GgsFrame* frame, const GgsGaussians* gaussians, const GgsForwardState* state,
+                        uint64_t* counters, void* stream);
 
 /* ---- introspection for tests: byte offsets of the arrays inside the opaque workspaces ---------- */
 typedef struct GgsLayout {

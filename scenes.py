@@ -114,6 +114,23 @@ def look_at_camera(W: int, H: int, focal: float, eye, target=(0.0, 0.0, 0.0)) ->
     return Camera(W, H, tanx, tany, view, full, campos)
 
 
+def ring_camera(W: int, H: int, focal: float, view: int = 0, n_views: int = 1) -> Camera:
+    """Camera `view` of `n_views` on a circle of radius 4 around the origin, looking at it (view 0 = the single-view
+    camera at z = -4)."""
+    if n_views > 1:
+        ang = 2.0 * math.pi * view / n_views
+        eye = (4.0 * math.sin(ang), 0.0, -4.0 * math.cos(ang))
+    else:
+        eye = (0.0, 0.0, -4.0)
+    return look_at_camera(W, H, focal, eye)
+
+
+def config_camera(name: str, view: int = 0, n_views: int = 1) -> Camera:
+    """The camera make_scene(name, view=view, n_views=n_views) would use, without generating the Gaussians."""
+    _, W, H, focal, _, _ = CONFIGS[name]
+    return ring_camera(W, H, focal, view, n_views)
+
+
 def make_scene(name: str = "c1", *, seed: Optional[int] = None, view: int = 0, n_views: int = 1,
                P: Optional[int] = None, W: Optional[int] = None, H: Optional[int] = None,
                kernel_size: float = 0.0, random_bg: bool = False, sh_degree: Optional[int] = None,
@@ -167,12 +184,7 @@ def make_scene(name: str = "c1", *, seed: Optional[int] = None, view: int = 0, n
         sharp = torch.zeros(P, 0)
         sgc = torch.zeros(P, 0, 3)
 
-    if n_views > 1:
-        ang = 2.0 * math.pi * view / n_views
-        eye = (4.0 * math.sin(ang), 0.0, -4.0 * math.cos(ang))
-    else:
-        eye = (0.0, 0.0, -4.0)
-    cam = look_at_camera(W, H, focal, eye)
+    cam = ring_camera(W, H, focal, view, n_views)
     bg = rand(3) if random_bg else torch.zeros(3)
 
     gg = torch.Generator().manual_seed(seed + 7919 + view)

@@ -98,8 +98,9 @@ def _bytes_view(buf, offset, dtype, count):
     return buf[offset:offset + count * itemsize].view(dtype)
 
 
-def ours_forward_raw(sc, device, require_depth=True):
-    """Forward through the C ABI keeping the workspaces; returns outputs + bit-exact intermediates."""
+def ours_forward_raw(sc, device, require_depth=True, want_ctx=False):
+    """Forward through the C ABI keeping the workspaces; returns outputs + bit-exact intermediates (+ the call's frame /
+    Gaussians / state structures with want_ctx, for entry points that take a finished forward)."""
     import ctypes as C
 
     import diff_gaussian_rasterization as ours
@@ -148,6 +149,8 @@ def ours_forward_raw(sc, device, require_depth=True):
         sort_bits=int(L.sort_bits),
     )
     outs = dict(color=color, radii=radii, mdepth=mdepth, alpha=alpha, normal=normal)
+    if want_ctx:
+        return outs, inter, dict(frame=frame, g=g, state=state, keep=(keep, t, arena))
     return outs, inter
 
 

@@ -73,6 +73,32 @@ def _worker(rank, world, port, ret):
         ok = ok and torch.equal(a1, pts[:1].sum(dim=1) * 0.5) and i1.shape == (1,)
         a0, i0 = parallel.integrate_sharded(fake_integrate, pts[:0])
         ok = ok and a0.numel() == 0 and i0.numel() == 0
+        # ---- alpha_cull: view-major loop over prepared views, point-range sharding, final all-gather ----
+        prepared = []
+
+        class FakeView:
+            def __init__(self, k):
+                self.k = k
+                prepared.append(k)
+
+            def integrate(self, p):
+                # "opacity" depends on the view and the point; a view sees the point iff a coordinate is positive
+                return (p[:, 0].abs() * (self.k + 1)).clamp(max=1.0) * 0.5, p[:, self.k % 3] > 0
+
+        views = [0, 1, 2, 3]
+        sdf, valid = parallel.alpha_cull(pts, views, None, None, None, None, chunk_size=170, prepare=FakeView)
+        want_w = torch.ones(1001)
+        want_v = torch.zeros(1001, dtype=torch.bool)
+        for k in views:
+            al, ins = FakeView(k).integrate(pts)
+            want_v |= ins
+            want_w = torch.where(ins, torch.min(al, want_w), want_w)
+        want_w[~want_v] = 0
+        ok = ok and torch.equal(sdf, 0.5 - want_w) and torch.equal(valid, want_v)
+        ok = ok and prepared[:4] == [0, 1, 2, 3]  # every view prepared once per rank, whatever the number of chunks
+        s_own, v_own = parallel.alpha_cull(pts, views, None, None, None, None, chunk_size=170, prepare=FakeView,
+                                           gather=False)
+        ok = ok and torch.equal(s_own, sdf[lo:hi]) and torch.equal(v_own, valid[lo:hi])
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
