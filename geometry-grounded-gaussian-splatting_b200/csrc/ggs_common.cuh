@@ -54,6 +54,29 @@ struct View {
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per DEVICE (and per function); a process may drive several
+// devices (and several host threads may launch at once), so the largest size opted into so far is kept per device,
+// atomically.  `state`: one zero-initialised array per kernel.
+constexpr int MAX_DEVICES = 64;
+struct SmemOptIn {
+    unsigned long long bytes[MAX_DEVICES];
+};
+template <typename Kernel>
+inline void opt_in_shared_memory(Kernel kernel, size_t smem, SmemOptIn& state) {
+    if (smem <= 48 * 1024) return;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        return;
+    }
+    unsigned long long seen = __atomic_load_n(&state.bytes[dev], __ATOMIC_ACQUIRE);
+    if (smem <= seen) return;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    while (seen < smem && !__atomic_compare_exchange_n(&state.bytes[dev], &seen, (unsigned long long)smem, false,
+                                                       __ATOMIC_RELEASE, __ATOMIC_ACQUIRE)) {
+    }
+}
+
 // Reference host helper (rasterizer_impl.cu:37-50): NOT ceil(log2(n)).
 inline uint32_t higher_msb(uint32_t n) {
     uint32_t msb = sizeof(n) * 4;

@@ -532,11 +532,8 @@ void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, c
                               cudaStream_t stream) {
     if (fp.P == 0) return;
     const size_t smem = (size_t)(GB_THREADS / 32) * 32 * ((fp.SHM * 3) | 1) * sizeof(float);
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaFuncSetAttribute(gaussian_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn opted;
+    opt_in_shared_memory(gaussian_backward_kernel, smem, opted);
     gaussian_backward_kernel<<<(fp.P + GB_THREADS - 1) / GB_THREADS, GB_THREADS, smem, stream>>>(fp, in, radii, clamped,
                                                                                                grad_acc, g);
 }

@@ -199,11 +199,8 @@ static void launch_view_sum(int P, int SHD, int SHM, int V, const float* means3D
                             float* dL_dsh, const PeerJob& job, cudaStream_t stream) {
     // output slab [warps][32][RS] + colour stage [warps][V][96]; RS = 3 SHM | 1 keeps the slab a multiple of 16 bytes
     const size_t smem = (size_t)(MV_THREADS / 32) * (32 * ((SHM * 3) | 1) + (size_t)V * 96) * sizeof(float);
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaFuncSetAttribute(view_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn opted;
+    opt_in_shared_memory(view_sum_kernel, smem, opted);
     const int sh_blocks = (P + MV_THREADS - 1) / MV_THREADS;
     if (sh_blocks + job.blocks == 0) return;
     view_sum_kernel<<<sh_blocks + job.blocks, MV_THREADS, smem, stream>>>(P, SHD, SHM, V, means3D, src, dL_dsh, job);

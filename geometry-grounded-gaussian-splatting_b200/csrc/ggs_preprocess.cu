@@ -334,11 +334,8 @@ void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool wan
     const int blocks = (fp.P + threads - 1) / threads;
     const bool use_sh = want_color && in.colors_precomp == nullptr;
     const size_t smem = use_sh ? (size_t)(PRE_THREADS / 32) * 32 * ((fp.SHM * 3) | 1) * sizeof(float) : 0;
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn opted;
+    opt_in_shared_memory(preprocess_kernel, smem, opted);
     preprocess_kernel<<<blocks, threads, smem, stream>>>(fp, in, want_color, records, depths, tiles_touched, rects,
                                                          clamped, radii, depth_extremes, order_keys, order_vals);
 }

@@ -396,12 +396,9 @@ void launch_render_backward(const FrameParams& fp, const uint2* ranges, const ui
     const dim3 grid(fp.gx, fp.gy, 1);
     const dim3 block(TILE_PIXELS, 1, 1);
     constexpr size_t SMEM = BWD_REC_BYTES + BWD_ID_BYTES;
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(render_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
-        cudaFuncSetAttribute(render_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM);
-        configured = true;
-    }
+    static SmemOptIn opted_geometry, opted_colour;
+    opt_in_shared_memory(render_backward_kernel<true>, SMEM, opted_geometry);
+    opt_in_shared_memory(render_backward_kernel<false>, SMEM, opted_colour);
     if (require_depth)
         render_backward_kernel<true><<<grid, block, SMEM, stream>>>(
             rp, ranges, point_list, records, in.alpha, in.normal, in.mdepth, in.n_contrib, in.max_contributor,

@@ -440,13 +440,9 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     const dim3 grid(fp.gx, fp.gy, TILE_WARPS / WARPS);
     const dim3 block(THREADS, 1, 1);
     cudaMemsetAsync(out.max_contributor, 0, (size_t)fp.gx * fp.gy * sizeof(uint32_t), stream);
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(render_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(REC_BYTES + MASK_BYTES));
-        cudaFuncSetAttribute(render_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)REC_BYTES);
-        configured = true;
-    }
+    static SmemOptIn opted_geometry, opted_colour;
+    opt_in_shared_memory(render_forward_kernel<true>, REC_BYTES + MASK_BYTES, opted_geometry);
+    opt_in_shared_memory(render_forward_kernel<false>, REC_BYTES, opted_colour);
     if (require_depth)
         render_forward_kernel<true><<<grid, block, REC_BYTES + MASK_BYTES, stream>>>(
             rp, ranges, point_list, records, out.color, out.alpha, out.normal, out.mdepth, out.n_contrib,
