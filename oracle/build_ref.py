@@ -99,6 +99,41 @@ def build_ncc(force: bool = False) -> str:
     return so
 
 
+REF_ROOT = "/root/reference"
+OUT_APP = os.path.join(HERE, "_ref", "ref_app")
+# the reference's own callers of the rasterizer: installed verbatim (install artefacts, git-ignored like ref_dgr), so that
+# tests can run gaussian_renderer.render / integrate / evaluate_sdf / sample_depth and utils.loss_utils.PatchMatch
+# UNCHANGED on top of either rasterizer package (tests/test_reference_callers_gpu.py)
+APP_FILES = ("gaussian_renderer/__init__.py", "scene/gaussian_model.py", "scene/cameras.py",
+             "scene/appearance_network.py", "utils/general_utils.py", "utils/graphics_utils.py", "utils/sh_utils.py",
+             "utils/system_utils.py", "utils/loss_utils.py", "arguments/__init__.py")
+
+
+def build_app(force: bool = False) -> str:
+    """Copies the reference's rasterizer callers into oracle/_ref/ref_app/.  The reference's scene/__init__.py pulls in
+    its dataset readers (COLMAP, PIL, ...); the package marker written here exports the two names its callers import
+    from `scene` and nothing else."""
+    marker = os.path.join(OUT_APP, ".installed")
+    if os.path.exists(marker) and not force:
+        return OUT_APP
+    if not os.path.isdir(REF_ROOT):
+        raise RuntimeError("reference sources not present at " + REF_ROOT)
+    for rel in APP_FILES:
+        dst = os.path.join(OUT_APP, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(os.path.join(REF_ROOT, rel), dst)
+    with open(os.path.join(OUT_APP, "scene", "__init__.py"), "w") as f:
+        f.write("# written by oracle/build_ref.py (not the reference's scene/__init__.py, which imports its dataset readers)\n"
+                "from scene.gaussian_model import GaussianModel  # noqa: F401\n"
+                "from scene.cameras import Camera  # noqa: F401\n")
+    with open(os.path.join(OUT_APP, "utils", "__init__.py"), "w") as f:
+        f.write("")
+    with open(marker, "w") as f:
+        f.write("ok\n")
+    return OUT_APP
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
     print(build_ncc(force="--force" in sys.argv))
+    print(build_app(force="--force" in sys.argv))
