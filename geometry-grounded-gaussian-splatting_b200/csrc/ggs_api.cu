@@ -219,6 +219,16 @@ extern "C" {
 
 int ggs_abi_version(void) { return GGS_ABI_VERSION; }
 
+#ifdef GGS_WALK_STATS
+}
+namespace ggs { void read_walk_stats(unsigned long long* out, bool reset); }
+extern "C" {
+// development builds only (not in the header): [5 iterations][8 counters] of the forward's bisection walk
+__attribute__((visibility("default"))) void ggs_debug_walk_stats(unsigned long long* out, int reset) {
+    ggs::read_walk_stats(out, reset != 0);
+}
+#endif
+
 const char* ggs_last_error(void) { return g_error.c_str(); }
 
 int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocFn alloc, void* user,

@@ -16,6 +16,19 @@ constexpr int SPLIT = 8;                    // config.h:32
 constexpr float SAMPLE_RANGE = 0.4f;        // config.h:34 (TRAINING)
 constexpr int SPLIT_ITERATIONS = 5;         // config.h:35 (TRAINING)
 constexpr int POINT_BATCH = 2;              // config.h:27 SAMPLE_BATCH_SIZE
+// Depth-profile shortcuts of the bisection passes (image and point-query kernels), in units of the splat's depth sigma:
+//   FAR:   beyond 16 sigma exp(-delta^2/2) = 2^-184 and ex2.approx.ftz returns +0 (it does from 13.3 sigma on): the
+//          splat's term is exactly absent from the forward AND from the backward's dT/dt sum -> it leaves the lists.
+//   QUIET: from 6.5 sigma on the Gaussian term no longer reaches the factor: g <= 2^-30.4 (ex2.approx is good to
+//          2^-22), so alpha * g < 2^-25 and 1 - alpha * g rounds to exactly 1.0f, with or without multiply-add
+//          contraction (the smallest |delta| with that property is 6.004).  No exp / rsqrt is issued for it, the
+//          forward is bit-identical; its tiny backward term is kept, so it stays in the exported masks.
+constexpr float FAR_SIGMAS = 16.f;
+#ifndef GGS_QUIET_SIGMAS
+#define GGS_QUIET_SIGMAS 6.5f
+#endif
+constexpr float QUIET_SIGMAS = GGS_QUIET_SIGMAS;
+static_assert(QUIET_SIGMAS >= 6.25f && QUIET_SIGMAS <= FAR_SIGMAS, "1 - alpha * g must round to 1");
 constexpr int MASK_WORDS = 256;  // per warp, words of the acceptance mask the forward keeps (and thins) in shared memory
 
 // Per-Gaussian record consumed by the tile kernels: 16 floats = one 64-byte, 64-byte aligned

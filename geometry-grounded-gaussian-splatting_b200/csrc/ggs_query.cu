@@ -41,7 +41,7 @@ constexpr int Q_QUADS = 3;          // staged quads per record: (mean, conic.xy)
 constexpr uint32_t Q_FULL = 0xffffffffu;
 constexpr uint32_t Q_NEVER = 0xffffffffu;
 constexpr uint32_t NO_TILE = 0xffffffffu;
-constexpr float Q_FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0
+constexpr float Q_FAR_SIGMAS = FAR_SIGMAS;
 
 // ---- projection of the query points -----------------------------------------------------------------------------
 // preprocessPointsCUDA (sample_forward.cu:10-53) + the tile choice of createWithKeys (rasterizer_impl.cu:109-137).
@@ -541,13 +541,15 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                     // in front of / behind the splat's peak depth, exp(-delta^2/2) is exactly 0 at every sample.
                     const float front = depth_min - t_peak;
                     const float back = t_peak - depth_hi;
-                    const bool far = ball && fmaxf(front, back) * rsigma > Q_FAR_SIGMAS && rsigma * depth_hi < 4e6f;
+                    const float reach = fmaxf(front, back) * rsigma;  // |delta| of every sample is at least this
+                    const bool far = ball && reach > Q_FAR_SIGMAS && rsigma * depth_hi < 4e6f;
+                    const bool quiet = ball && reach > QUIET_SIGMAS;  // 1 - alpha * exp() rounds to 1 (ggs_common.cuh)
                     const bool far_front = far && front > 0.f;  // stays so: depth_min never decreases
                     const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
                     const bool constant = !act || far_front || behind_for_good;
                     const bool fold = pfx && open && constant;
                     if (__any_sync(Q_FULL, act && !behind_for_good && !fold)) keep |= bit;
-                    if (__any_sync(Q_FULL, act && !far)) {
+                    if (__any_sync(Q_FULL, act && !quiet)) {
                         if (act) {
                             if (first) {
 #pragma unroll
@@ -560,9 +562,10 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                             }
                         }
                     } else if (act) {
-                        // exp underflows to 0 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
-                        const float f = (far_front ? (1.f - alpha) : 1.0f) * c1;
-                        if (far_front || !exact_one) {
+                        // 1 - alpha * exp() is exactly 1 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
+                        const bool in_front = front > 0.f;  // every active lane is quiet here: in front or behind
+                        const float f = (in_front ? (1.f - alpha) : 1.0f) * c1;
+                        if (in_front || !exact_one) {
                             if (first) {
 #pragma unroll
                                 for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;

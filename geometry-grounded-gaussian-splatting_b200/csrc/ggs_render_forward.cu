@@ -44,7 +44,6 @@ constexpr int THREADS = WARPS * 32;
 constexpr int BATCH = THREADS;  // list entries per staged batch (one per thread)
 constexpr uint32_t FULL = 0xffffffffu;
 constexpr uint32_t NEVER = 0xffffffffu;
-constexpr float FAR_SIGMAS = 16.f;  // exp(-0.5 * 16^2) = 2^-184: ex2.approx.ftz returns +0 (it does from 13.3 sigma on)
 constexpr size_t REC_BYTES = (size_t)2 * BATCH * REC_QUADS * sizeof(float4);
 constexpr size_t MASK_BYTES = (size_t)WARPS * MASK_WORDS * sizeof(uint32_t);
 
@@ -80,6 +79,14 @@ __device__ __forceinline__ bool may_touch(const float4 q0, const float4 q1, floa
     const float M = A * Dx * Dx + 2.f * fabsf(B) * Dx * Dy + C * Dy * Dy;
     return !(0.5f * qmin - 1e-5f * M > L + 0.01f);
 }
+
+#ifdef GGS_WALK_STATS
+// Development build only (make variant DEFS=-DGGS_WALK_STATS): what the bisection walk spends its list positions on.
+__device__ unsigned long long g_walk_stats[SPLIT_ITERATIONS][8];
+#define WALK_STAT(k, v) ws[k] += (v)
+#else
+#define WALK_STAT(k, v)
+#endif
 
 // One depth sample of the vacancy-corrected transmittance product (render_forward.cu:603-621).
 __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsigma, bool ball, float alpha) {
@@ -291,6 +298,9 @@ __global__ void __launch_bounds__(THREADS, 8)
         const int b0 = block_last ? block_first / BATCH : 0;
         const int b1 = (block_last + BATCH - 1) / BATCH;
         bool pfx = exact_one;  // still extending this pixel's constant prefix
+#ifdef GGS_WALK_STATS
+        unsigned int ws[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
 
         uint32_t id_next = 0;
         if (b0 < b1) {
@@ -317,6 +327,7 @@ __global__ void __launch_bounds__(THREADS, 8)
                 const uint32_t gw = i * (BATCH / 32) + w;
                 uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
                 uint32_t keep = 0;  // positions some pixel of the warp can still need in later iterations
+                WALK_STAT(6, 1);
                 while (bits) {
                     const int jj = __ffs(bits) - 1;
                     const uint32_t bit = bits & (0u - bits);
@@ -332,7 +343,9 @@ __global__ void __launch_bounds__(THREADS, 8)
                     const float alpha = fminf(0.99f, q1.y * expf(power));
                     const bool open = pos > pre_pos;  // not yet folded into this pixel's prefix (false if !in_range)
                     const bool act = open && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    WALK_STAT(0, 1);
                     if (!__any_sync(FULL, act)) {
+                        WALK_STAT(1, 1);
                         if (pfx && open) pre_pos = pos;  // contributes to none of this pixel's samples, ever
                         continue;
                     }
@@ -347,7 +360,9 @@ __global__ void __launch_bounds__(THREADS, 8)
                     // median depth through a multiply that may move it by an ulp.)
                     const float front = depth_min - t_peak;
                     const float back = t_peak - depth_hi;
-                    const bool far = ball && fmaxf(front, back) * rsigma > FAR_SIGMAS && rsigma * depth_hi < 4e6f;
+                    const float reach = fmaxf(front, back) * rsigma;  // |delta| of every sample is at least this
+                    const bool far = ball && reach > FAR_SIGMAS && rsigma * depth_hi < 4e6f;
+                    const bool quiet = ball && reach > QUIET_SIGMAS;  // far implies quiet
                     const bool far_front = far && front > 0.f;  // stays so: depth_min never decreases
                     // may be dropped for good only with some slack: the recomputed depth_hi of a later
                     // iteration can sit a few ulps above this one
@@ -356,7 +371,10 @@ __global__ void __launch_bounds__(THREADS, 8)
                     const bool constant = !act || far_front || behind_for_good;
                     const bool fold = pfx && open && constant;
                     if (__any_sync(FULL, act && !behind_for_good && !fold)) keep |= bit;
-                    if (__any_sync(FULL, act && !far)) {
+                    if (__any_sync(FULL, act && !quiet)) {
+                        WALK_STAT(2, 1);
+                        WALK_STAT(4, __popc(__ballot_sync(FULL, act)));
+                        WALK_STAT(5, __popc(__ballot_sync(FULL, act && !quiet)));
                         if (act) {
                             if (first) {
 #pragma unroll
@@ -369,9 +387,11 @@ __global__ void __launch_bounds__(THREADS, 8)
                             }
                         }
                     } else if (act) {
-                        // exp underflows to 0 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
-                        const float f = (far_front ? (1.f - alpha) : 1.0f) * c1;
-                        if (far_front || !exact_one) {
+                        WALK_STAT(3, 1);
+                        // 1 - alpha * exp() is exactly 1 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
+                        const bool in_front = front > 0.f;  // every active lane is quiet here: in front or behind
+                        const float f = (in_front ? (1.f - alpha) : 1.0f) * c1;
+                        if (in_front || !exact_one) {
                             if (first) {
 #pragma unroll
                                 for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
@@ -396,6 +416,12 @@ __global__ void __launch_bounds__(THREADS, 8)
                 }
             }
         }
+#ifdef GGS_WALK_STATS
+        ws[3] = __reduce_max_sync(FULL, ws[3]);  // constant-path entries (counted by the active lanes only)
+        if (lane == 0)
+            for (int k = 0; k < 8; k++)
+                if (ws[k]) atomicAdd(&g_walk_stats[it][k], (unsigned long long)ws[k]);
+#endif
         if (first) {
             in_range = (T_p[0] >= 0.5f) && (T_p[SPLIT] <= 0.5f) && in_range;
             if (!in_range) pre_pos = NEVER;
@@ -452,5 +478,16 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
             rp, ranges, point_list, records, out.color, out.alpha, out.normal, out.mdepth, out.n_contrib,
             out.max_contributor, out.accept_mask, out.warp_words, out.near_mask, out.near_first);
 }
+
+#ifdef GGS_WALK_STATS
+void read_walk_stats(unsigned long long* out, bool reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_walk_stats, sizeof(g_walk_stats));
+    if (reset) {
+        static unsigned long long zero[SPLIT_ITERATIONS][8] = {};
+        cudaMemcpyToSymbol(g_walk_stats, zero, sizeof(zero));
+    }
+}
+#endif
 
 }  // namespace ggs

@@ -11,7 +11,9 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libggs_rasterizer.so")
+# GGS_RASTERIZER_LIB: a differently built copy of the same library (A/B timing of kernel variants, tools/variants.sh);
+# there is still no fallback -- whatever path is named must exist and export the whole ABI.
+LIB_PATH = os.environ.get("GGS_RASTERIZER_LIB") or os.path.join(_HERE, "libggs_rasterizer.so")
 
 (SLOT_GEOMETRY, SLOT_BINNING, SLOT_IMAGE, SLOT_TILE, SLOT_POINT, SLOT_POINT_BINNING, SLOT_BACKWARD,
  SLOT_BLOCKS) = range(8)

@@ -134,6 +134,14 @@ def build_app(force: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv))
-    print(build_ncc(force="--force" in sys.argv))
-    print(build_app(force="--force" in sys.argv))
+    force = "--force" in sys.argv
+    if "--only" in sys.argv:
+        what = sys.argv[sys.argv.index("--only") + 1]
+        print({"dgr": build, "ncc": build_ncc, "app": build_app}[what](force=force))
+    else:
+        # one process per extension: torch.utils.cpp_extension.load() renames a second module called "_C" built in
+        # the same process ("_C_v1"), and the reference's PYBIND11_MODULE(TORCH_EXTENSION_NAME, ...) follows the name
+        import subprocess
+
+        for what in ("dgr", "ncc", "app"):
+            subprocess.check_call([sys.executable, os.path.abspath(__file__), "--only", what] + (["--force"] if force else []))
