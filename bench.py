@@ -294,11 +294,11 @@ class Step:
                         out=torch.empty(3, self.sc.cam.H, self.sc.cam.W, device=dev),
                         chk=torch.empty(1, device=dev), ready=torch.cuda.Event(), free=torch.cuda.Event(),
                         color_host=torch.empty(3, self.sc.cam.H, self.sc.cam.W).pin_memory(),
-                        check_host=torch.empty(1).pin_memory())
+                        check_host=torch.empty(1).pin_memory(), d2h=None)
             slot["free"].record()
             self.slots.append(slot)
         self.pipe_i = 0
-        self.prev_d2h = None
+        self.last_check = None
         self._prefetch(self.slots[0])
 
     def _prefetch(self, slot):
@@ -314,11 +314,16 @@ class Step:
         """One step with its host traffic: H2D of this step's camera + upstream-gradient images from pinned memory
         and D2H of its colour image + gradient checksum.  The copies run on a copy stream, double-buffered, so the
         H2D of step i+1 and the D2H of step i-1 overlap the kernels of step i (what a trainer's data loader does);
-        the host waits every step for the previous step's result to have landed.  Same harness for both arms."""
+        every step the host waits for, and reads, the result of the step two back.  Same harness for both arms."""
         if not hasattr(self, "slots"):
             self._pipeline()
         cur = torch.cuda.current_stream()
         slot = self.slots[self.pipe_i & 1]
+        # the host reads a slot's result (the step two back) before the slot is used again: it runs at most two steps
+        # ahead of the device, and a late host thread (eight ranks share the node's cores) has a step of slack
+        if slot["d2h"] is not None:
+            slot["d2h"].synchronize()
+            self.last_check = float(slot["check_host"][0])
         self._prefetch(self.slots[(self.pipe_i + 1) & 1])
         cur.wait_event(slot["ready"])
         color = self._fwd_bwd(slot["cam"], slot["g"])
@@ -331,10 +336,53 @@ class Step:
             slot["color_host"].copy_(slot["out"], non_blocking=True)
             slot["check_host"].copy_(slot["chk"], non_blocking=True)
             d2h.record(self.copy_stream)
-        if self.prev_d2h is not None:
-            self.prev_d2h.synchronize()
-        self.prev_d2h = d2h
+        slot["d2h"] = d2h
         self.pipe_i += 1
+
+
+def exchange_check(step, device):
+    """One untimed step with the gradient sums through the active peer-memory exchange and one with the NCCL collectives
+    (all-gather of the colour gradients + bucket all-reduce), same views, same inputs: per tensor
+    max|peer - nccl| / max|nccl|, MAX over the ranks.  The only place a driver-run check of the exchange can live: the
+    GPU test box has one GPU."""
+    import torch.distributed as dist
+
+    names = ("means3D", "opacities", "scales", "rotations", "shs")
+    step.resident()
+    torch.cuda.synchronize()
+    got = {k: step.params[k].grad.detach().clone() for k in names}
+    ex, note = step.exchange, step.exchange_note
+    step.exchange, step.flat = None, None
+    try:
+        step.resident()
+        torch.cuda.synchronize()
+        ref = {k: step.params[k].grad.detach().clone() for k in names}
+    finally:
+        step.exchange, step.flat = ex, None
+    errs = torch.tensor([float((got[k] - ref[k]).abs().max() / ref[k].abs().max().clamp_min(1e-30)) for k in names],
+                        dtype=torch.float64, device=device)
+    dist.all_reduce(errs, op=dist.ReduceOp.MAX)
+    per = {k: float(v) for k, v in zip(names, errs.tolist())}
+    return {"max_rel_vs_nccl": max(per.values()), "per_tensor": per, "exchange": note,
+            "reference": "nccl all-gather(dL_drgb) + nccl all-reduce(11 floats/Gaussian), same step, same views"}
+
+
+def pin_rank(local, world):
+    """Eight ranks share the node's host cores: give each rank its own contiguous share (no migration, no two ranks'
+    launch threads on one core).  GGS_BENCH_PIN=0 switches it off."""
+    if os.environ.get("GGS_BENCH_PIN", "1") == "0" or not hasattr(os, "sched_setaffinity"):
+        return None
+    try:
+        cpus = sorted(os.sched_getaffinity(0))
+        share = len(cpus) // world
+        if share < 1:
+            return None
+        mine = cpus[local * share:(local + 1) * share]
+        os.sched_setaffinity(0, mine)
+        torch.set_num_threads(max(1, share))
+        return mine
+    except OSError:
+        return None
 
 
 def timed(fn, steps, warmup, world, sampler=None):
@@ -642,6 +690,38 @@ def run_c5(args, rank, world, local, device, multi):
     return 0
 
 
+def c4_scaling(mod, args, rank, world, device):
+    """BASELINE config 4 next to the headline line (north_star: ">= 7x at 8 GPUs on an 8-view batch"): the 2 M-Gaussian,
+    980x545 scene, one view per rank with the gradient sums inside the timed region, then the same step on rank 0
+    alone (the other ranks wait in a barrier).  Returns the sub-object on rank 0, None elsewhere."""
+    import torch.distributed as dist
+
+    steps, warmup = args.steps, args.warmup
+    sc = make_view("c4", rank, world)
+    step = Step(mod, sc, device, allreduce=True)
+    for _ in range(3):
+        step.resident()
+    ms_n, _ = timed(step.resident, steps, warmup, world, None)
+    note = step.exchange_note
+    del step
+    torch.cuda.synchronize()
+    ms_1 = None
+    if rank == 0:
+        solo = Step(mod, make_view("c4", 0, 1), device, allreduce=False)
+        for _ in range(3):
+            solo.resident()
+        ms_1, _ = timed(solo.resident, steps, warmup, 1, None)
+        del solo
+    dist.barrier()
+    if rank != 0:
+        return None
+    n_val, one_val = world * 1000.0 / (ms_n / steps), 1000.0 / (ms_1 / steps)
+    return {"workload": f"c4: {sc.P} Gaussians, {sc.cam.W}x{sc.cam.H}, SH{sc.sh_degree}, {world} views, one per rank",
+            "n_gpus": world, "iters_per_s": n_val, "ms_per_step": ms_n / steps, "one_gpu_iters_per_s": one_val,
+            "one_gpu_ms_per_step": ms_1 / steps, "ratio": n_val / one_val, "exchange": note, "steps": steps,
+            "warmup": warmup}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -667,8 +747,9 @@ def main():
         import torch.distributed as dist
 
         _quiet_nccl()
+        pinned = pin_rank(local, world)
         dist.init_process_group("nccl", device_id=device)
-        guard = watchdog(float(os.environ.get("GGS_BENCH_WATCHDOG_S", "600")), rank)
+        guard = watchdog(float(os.environ.get("GGS_BENCH_WATCHDOG_S", "240")), rank)
 
     if args.workload == "c5":
         rc = run_c5(args, rank, world, local, device, multi)
@@ -746,6 +827,12 @@ def main():
     ms_e2e, _ = timed(step.end_to_end, args.steps, args.warmup, world if multi else 1, None)
     e2e_value = n_ranks * 1000.0 / (ms_e2e / args.steps)
 
+    xcheck, c4 = None, None
+    if multi and step.exchange is not None:
+        xcheck = exchange_check(step, device)
+    if multi and args.workload == "c3" and os.environ.get("GGS_BENCH_C4", "1" if world == 8 else "0") == "1":
+        c4 = c4_scaling(mod, args, rank, world, device)
+
     if rank != 0:
         if multi:
             guard.cancel()
@@ -767,6 +854,12 @@ def main():
                 "d2h_bytes_per_step": step.d2h_bytes},
         "clocks": clocks,
     }
+    if xcheck is not None:
+        line["exchange_check"] = xcheck
+    if c4 is not None:
+        line["c4"] = c4
+    if multi:
+        line["config"]["host_cores_per_rank"] = len(pinned) if pinned else None
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = 0

@@ -29,7 +29,7 @@ constexpr float FAR_SIGMAS = 16.f;
 #endif
 constexpr float QUIET_SIGMAS = GGS_QUIET_SIGMAS;
 static_assert(QUIET_SIGMAS >= 6.25f && QUIET_SIGMAS <= FAR_SIGMAS, "1 - alpha * g must round to 1");
-constexpr int MASK_WORDS = 256;  // per warp, words of the acceptance mask the forward keeps (and thins) in shared memory
+constexpr int MASK_WORDS = 128;  // per warp, words of the acceptance mask the forward keeps (and thins) in shared memory
 
 // Per-Gaussian record consumed by the tile kernels: 16 floats = one 64-byte, 64-byte aligned
 // gather unit (two full 32-byte sectors, no wasted bytes).

@@ -18,8 +18,8 @@
 //     buffer shared by the CTA (48-byte stride: conflict-free 16-byte stores, broadcast reads);
 //   * sample_depth / evaluate_sdf keep the per-warp acceptance mask of the first pass in shared memory and run the
 //     bisection passes on it, with the exact far-splat shortcuts of the image kernel (ggs_render_forward.cu): a splat
-//     whose depth profile is more than 16 sigma from the whole bracket has exp() == 0 exactly, so its factor is
-//     (1 - alpha) in front of the bracket and 1 behind it, the leading run of such entries is carried over as one
+//     whose depth profile is more than 6.5 sigma from the whole bracket has 1 - alpha * exp() == 1 exactly, so its
+//     factor is (1 - alpha) in front of the bracket and 1 behind it, the leading run of such entries is carried over as one
 //     product, and entries behind every bracket are dropped from the mask.  Per-query float products keep their order;
 //   * the backward reduces the ten per-(warp, entry) partial sums with one transposing butterfly (12 shuffles) and
 //     ten lanes issue one double-precision RED each into the Gaussian's accumulator row (ggs_common.cuh), which the
@@ -41,7 +41,7 @@ constexpr int Q_QUADS = 3;          // staged quads per record: (mean, conic.xy)
 constexpr uint32_t Q_FULL = 0xffffffffu;
 constexpr uint32_t Q_NEVER = 0xffffffffu;
 constexpr uint32_t NO_TILE = 0xffffffffu;
-constexpr float Q_FAR_SIGMAS = FAR_SIGMAS;
+constexpr int Q_MASK_WORDS = 256;  // words of a warp's acceptance mask kept (and thinned) in shared memory
 
 // ---- projection of the query points -----------------------------------------------------------------------------
 // preprocessPointsCUDA (sample_forward.cu:10-53) + the tile choice of createWithKeys (rasterizer_impl.cu:109-137).
@@ -365,7 +365,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                           float* __restrict__ output, float* __restrict__ output_sdf,
                           uint8_t* __restrict__ inside_output) {
     __shared__ __align__(16) float4 s_rec[2 * Q_BATCH * Q_QUADS];
-    __shared__ uint32_t s_mask[Q_WARPS][MASK_WORDS];
+    __shared__ uint32_t s_mask[Q_WARPS][Q_MASK_WORDS];
     __shared__ uint32_t s_first[Q_WARPS];
     __shared__ uint32_t s_last[Q_WARPS];
     Job job;
@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                     if (__any_sync(Q_FULL, blended)) bits |= 1u << jj;
                 }
                 const uint32_t gw = i * (Q_BATCH / 32) + w;
-                if (lane == 0 && gw < MASK_WORDS) s_mask[warp][gw] = bits;
+                if (lane == 0 && gw < Q_MASK_WORDS) s_mask[warp][gw] = bits;
                 mask_words = gw + 1;
             }
         }
@@ -512,7 +512,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                 if (base >= warp_last) break;
                 if (base + 32 <= warp_first) continue;
                 const uint32_t gw = i * (Q_BATCH / 32) + w;
-                uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : Q_FULL) : 0u;
+                uint32_t bits = gw < mask_words ? (gw < Q_MASK_WORDS ? s_mask[warp][gw] : Q_FULL) : 0u;
                 uint32_t keep = 0;  // positions some query of the warp can still need in later iterations
                 while (bits) {
                     const int jj = __ffs(bits) - 1;
@@ -537,13 +537,15 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                     const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
                     const float rsigma = q2.y;
                     const bool ball = rsigma > 0;
-                    // Every sample depth lies in [depth_min, depth_hi]; if that whole interval is more than 16 sigma
-                    // in front of / behind the splat's peak depth, exp(-delta^2/2) is exactly 0 at every sample.
+                    // Every sample depth lies in [depth_min, depth_hi]; if that whole interval is more than 6.5 sigma
+                    // in front of / behind the splat's peak depth, 1 - alpha * exp(-delta^2/2) is exactly 1 at every sample.
                     const float front = depth_min - t_peak;
                     const float back = t_peak - depth_hi;
                     const float reach = fmaxf(front, back) * rsigma;  // |delta| of every sample is at least this
-                    const bool far = ball && reach > Q_FAR_SIGMAS && rsigma * depth_hi < 4e6f;
                     const bool quiet = ball && reach > QUIET_SIGMAS;  // 1 - alpha * exp() rounds to 1 (ggs_common.cuh)
+                    // ... and stays so: brackets only shrink, up to a few ulps of the depth (see ggs_render_forward.cu).
+                    // Nothing downstream needs the 16-sigma rule here: the backward of sample_depth walks its own lists.
+                    const bool far = quiet && rsigma * depth_hi < 5e5f;
                     const bool far_front = far && front > 0.f;  // stays so: depth_min never decreases
                     const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
                     const bool constant = !act || far_front || behind_for_good;
@@ -582,7 +584,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
                         pfx = false;
                     }
                 }
-                if (exact_one && lane == 0 && gw < MASK_WORDS && gw < mask_words) s_mask[warp][gw] = keep;
+                if (exact_one && lane == 0 && gw < Q_MASK_WORDS && gw < mask_words) s_mask[warp][gw] = keep;
             }
         }
         if (first) {

@@ -6,10 +6,11 @@
 // One CTA per 16x16 tile; warp w owns an 8x4 pixel block, as in the forward.  Pass B walks only the list
 // positions that the forward recorded as blended by at least one pixel of the warp (accept_mask): about a
 // third of the list.  Pass A walks fewer still: every term of dT/dt_m carries exp(-delta^2/2) of the splat's
-// depth profile at the median depth, which is exactly 0 (ex2.approx.ftz underflow) for the splats the forward's
-// bisection classified as far from the pixel's final bracket -- the forward exports that thinned mask
-// (near_mask) and the end of each warp's constant prefix (near_first).  Adding an exact zero changes nothing,
-// so skipping those entries is exact.  Batches are staged with cp.async into a double buffer (ggs_tile.cuh).
+// depth profile at the median depth, which is exactly 0 (ex2.approx.ftz underflow) beyond 16 sigma.  The forward's
+// bisection exports the list positions it saw within 16 sigma of some pixel's bracket the last time it examined
+// them (near_mask); what is left of those is tested against the median depth itself before any alpha arithmetic.
+// Adding an exact zero changes nothing, so skipping those entries is exact.  Batches are staged with cp.async
+// into a double buffer (ggs_tile.cuh).
 // Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
 // scalar atomics from one lane (the reference), the warp runs ONE transposing butterfly (20
 // shuffles) that leaves component c on its own lane, and those 17 lanes issue a single predicated
@@ -171,7 +172,7 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         float dT_dtm = 0.f;
         const bool live = !((mDepth == 0) || (last_contributor == 0) || !inside);
         const uint32_t warp_last_a = __reduce_max_sync(FULL_B, live ? last_contributor : 0u);
-        // list positions <= nf have exp() == 0 at this warp's median depths (the forward folded them)
+        // list positions <= nf need no visit: the forward cleared them all in near_mask
         const uint32_t nf = near_first[tile_id * TILE_WARPS + warp];
         const uint32_t* my_near = near_mask + (size_t)mask_base * 8 + warp;
         if (lane == 0) {
@@ -220,16 +221,21 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                     const float4* rec = buf + (w * 32 + jj) * REC_QUADS_B;
                     const float4 q0 = rec[0];
                     const float4 q1 = rec[1];
+                    const float4 q2 = rec[2];
                     const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                    const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
+                    const float rsigma = q2.y;
+                    const float t_delta = (mDepth - t_peak) * rsigma;
+                    // The forward's list is exact but not minimal (it stops examining an entry once every pixel has
+                    // folded it into its constant prefix): beyond 16 sigma exp(-delta^2/2) underflows to +0 (it does
+                    // from 13.3 on) and the term below is exactly 0 -- decided before the alpha arithmetic.
+                    const bool near = live && pos <= last_contributor &&
+                                      !(fabsf(t_delta) > FAR_SIGMAS && fabsf(t_delta) < 3e38f);  // (0 * inf is not 0)
+                    if (!__any_sync(FULL_B, near)) continue;
                     const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                     const float alpha = fminf(0.99f, q1.y * expf(power));
-                    const bool act = live && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                    if (!__any_sync(FULL_B, act)) continue;
+                    const bool act = near && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                     if (act) {
-                        const float4 q2 = rec[2];
-                        const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
-                        const float rsigma = q2.y;
-                        const float t_delta = (mDepth - t_peak) * rsigma;
                         const float G_exp = expf(-0.5f * t_delta * t_delta);
                         const float Gt = alpha * G_exp;
                         dT_dtm += -0.25f * Gt / (1.f - Gt) * fabsf(t_delta) * rsigma;

@@ -14,16 +14,17 @@
 //     (exact minimum of the conic's quadratic form over the rectangle against the alpha >= 1/255 threshold,
 //     with slack); only entries that can touch the rectangle are evaluated per pixel.  The pass leaves, per
 //     warp, a bitmask of the list positions that at least one of its pixels blended;
-//   * the five bisection passes walk only those positions.  A splat whose depth profile is more than 16 sigma
-//     away from the whole current bracket contributes exp() == 0 exactly (ex2.approx.ftz underflows), so its
-//     factor is exactly (1 - alpha) in front of the bracket and exactly 1 behind it: no exp / rsqrt is issued
-//     for it unless some pixel of the warp is close to it.  Brackets only shrink, so such a splat stays far:
-//       - the leading run of far / inactive entries of a pixel multiplies every sample by the same floats in
+//   * the five bisection passes walk only those positions.  A splat whose depth profile is more than 6.5 sigma
+//     away from the whole current bracket has 1 - alpha * exp() == 1 exactly (ggs_common.cuh), so its factor is
+//     exactly (1 - alpha) in front of the bracket and exactly 1 behind it: no exp / rsqrt is issued for it unless some
+//     pixel of the warp is close to it.  Brackets only shrink, so such a splat stays quiet:
+//       - the leading run of quiet / inactive entries of a pixel multiplies every sample by the same floats in
 //         the same order in every iteration: its product is carried over (pre_T, pre_pos) instead of being
 //         recomputed, and the warp starts its walk after the shortest such prefix of its pixels;
-//       - entries behind every pixel's bracket for good are dropped from the warp's mask.
+//       - entries behind every pixel's bracket are dropped from the warp's list for good.
 //     All shortcuts keep the order of the per-pixel floating-point products: outputs are bit-identical to
-//     the plain evaluation.  The thinned mask and the prefix end are exported for the backward's dT/dt pass.
+//     the plain evaluation.  A second mask is thinned with the 16-sigma rule only (exp() == 0 exactly) and exported
+//     for the backward's dT/dt pass, whose terms still see a quiet splat.
 #include "ggs_kernels.cuh"
 #include "ggs_tile.cuh"
 
@@ -45,7 +46,7 @@ constexpr int BATCH = THREADS;  // list entries per staged batch (one per thread
 constexpr uint32_t FULL = 0xffffffffu;
 constexpr uint32_t NEVER = 0xffffffffu;
 constexpr size_t REC_BYTES = (size_t)2 * BATCH * REC_QUADS * sizeof(float4);
-constexpr size_t MASK_BYTES = (size_t)WARPS * MASK_WORDS * sizeof(uint32_t);
+constexpr size_t MASK_BYTES = (size_t)2 * WARPS * MASK_WORDS * sizeof(uint32_t);  // s_mask + s_near
 
 // Can the splat (q0 = mean.xy, conic.xy; q1 = conic.z, opacity, ..) reach alpha >= 1/255 on any pixel centre of
 // the rectangle [x0, x0+7] x [y0, y0+3]?  Conservative: `false` only when every pixel is provably rejected.
@@ -88,6 +89,15 @@ __device__ unsigned long long g_walk_stats[SPLIT_ITERATIONS][8];
 #define WALK_STAT(k, v)
 #endif
 
+// Staged records are read through 32-bit shared-memory addresses: one multiply-add per record instead of the 64-bit
+// generic pointer arithmetic the compiler emits for `buf + slot * REC_QUADS`.
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+constexpr uint32_t REC_STRIDE = REC_QUADS * sizeof(float4);
+
 // One depth sample of the vacancy-corrected transmittance product (render_forward.cu:603-621).
 __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsigma, bool ball, float alpha) {
     const float delta = (ts - t_peak) * rsigma;
@@ -108,7 +118,11 @@ __global__ void __launch_bounds__(THREADS, 8)
                           uint32_t* __restrict__ near_mask, uint32_t* __restrict__ near_first) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* const s_rec = reinterpret_cast<float4*>(smem_raw);  // [2][BATCH * REC_QUADS]
+    const uint32_t s_rec_addr = static_cast<uint32_t>(__cvta_generic_to_shared(smem_raw));
+    // s_mask: list positions this warp still has to visit (thinned with the QUIET rule); s_near: what the backward's
+    // dT/dt pass has to visit (thinned with the FAR rule only: a quiet splat still has a non-zero exp() there)
     uint32_t(*const s_mask)[MASK_WORDS] = reinterpret_cast<uint32_t(*)[MASK_WORDS]>(smem_raw + REC_BYTES);
+    // (s_near[w] is s_mask[WARPS + w]: one base pointer)
     __shared__ uint32_t s_red[WARPS];
     __shared__ uint32_t s_first[WARPS];
     __shared__ uint32_t s_last[WARPS];
@@ -152,7 +166,7 @@ __global__ void __launch_bounds__(THREADS, 8)
         for (int i = 0; i < rounds; i++) {
             cp_async_wait_all();
             if (__syncthreads_and(done)) break;
-            const float4* const buf = s_rec + (i & 1) * (BATCH * REC_QUADS);
+            const uint32_t buf_addr = s_rec_addr + (i & 1) * (BATCH * REC_STRIDE);
             if (i + 1 < rounds) {
                 const uint32_t e = (i + 1) * BATCH + tid;
                 if (e < n) stage_record(s_rec + ((i + 1) & 1) * (BATCH * REC_QUADS), tid, records, id_next, 4);
@@ -165,7 +179,8 @@ __global__ void __launch_bounds__(THREADS, 8)
                 // lane-parallel candidate test: one entry per lane against the warp's pixel rectangle
                 const int jl = w * 32 + lane;
                 bool c = false;
-                if (jl < lim) c = may_touch(buf[jl * REC_QUADS], buf[jl * REC_QUADS + 1], rx0, ry0);
+                const uint32_t word_addr = buf_addr + w * (32 * REC_STRIDE);
+                if (jl < lim) c = may_touch(lds128(word_addr + lane * REC_STRIDE), lds128(word_addr + lane * REC_STRIDE + 16), rx0, ry0);
                 uint32_t cand = __ballot_sync(FULL, c);
                 uint32_t bits = 0;
                 while (cand) {
@@ -173,9 +188,9 @@ __global__ void __launch_bounds__(THREADS, 8)
                     cand &= cand - 1;
                     bool blended = false;
                     if (!done) {
-                        const float4* rec = buf + (w * 32 + jj) * REC_QUADS;
-                        const float4 q0 = rec[0];
-                        const float4 q1 = rec[1];
+                        const uint32_t rec = word_addr + jj * REC_STRIDE;
+                        const float4 q0 = lds128(rec);
+                        const float4 q1 = lds128(rec + 16);
                         const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                         const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                         if (power <= 0.0f) {
@@ -186,8 +201,8 @@ __global__ void __launch_bounds__(THREADS, 8)
                                     done = true;
                                 } else {
                                     const float aT = alpha * T;
-                                    const float4 q2 = rec[2];
-                                    const float4 q3 = rec[3];
+                                    const float4 q2 = lds128(rec + 32);
+                                    const float4 q3 = lds128(rec + 48);
                                     C[0] += q2.z * aT;
                                     C[1] += q2.w * aT;
                                     C[2] += q3.x * aT;
@@ -209,7 +224,10 @@ __global__ void __launch_bounds__(THREADS, 8)
                 }
                 const uint32_t gw = i * (BATCH / 32) + w;
                 if (lane == 0) {
-                    if (GEOMETRY && gw < MASK_WORDS) s_mask[warp][gw] = bits;
+                    if (GEOMETRY && gw < MASK_WORDS) {
+                        s_mask[warp][gw] = bits;
+                        s_mask[WARPS + warp][gw] = bits;
+                    }
                     accept_mask[(size_t)(mask_base + gw) * 8 + twarp] = bits;  // kept for the backward
                 }
                 mask_words = gw + 1;
@@ -313,65 +331,69 @@ __global__ void __launch_bounds__(THREADS, 8)
             cp_async_wait_all();
             __syncthreads();
             const int k = i - b0;
-            const float4* const buf = s_rec + (k & 1) * (BATCH * REC_QUADS);
             if (i + 1 < b1) {
                 const uint32_t e = (i + 1) * BATCH + tid;
                 if (e < block_last) stage_record(s_rec + ((k + 1) & 1) * (BATCH * REC_QUADS), tid, records, id_next, 3);
                 cp_async_commit();
                 if (e + BATCH < block_last) id_next = __ldg(list + e + BATCH);
             }
+            const uint32_t buf_addr = s_rec_addr + (k & 1) * (BATCH * REC_STRIDE);
             for (int w = 0; w < BATCH / 32; w++) {
                 const uint32_t base = i * BATCH + w * 32;
                 if (base >= warp_last) break;
                 if (base + 32 <= warp_first) continue;
                 const uint32_t gw = i * (BATCH / 32) + w;
                 uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
-                uint32_t keep = 0;  // positions some pixel of the warp can still need in later iterations
+                // only list positions (1-based: base + jj + 1) in (warp_first, warp_last]: bits below are folded
+                // everywhere, nothing lives beyond
+                const uint32_t upto = warp_last - base >= 32u ? FULL : (1u << (warp_last - base)) - 1u;
+                bits &= upto;
+                if (warp_first > base) bits &= FULL << (warp_first - base);
+                uint32_t keep = 0;    // positions some pixel of the warp can still need in later iterations
+                uint32_t drop16 = 0;  // positions that leave the backward's list
+                const uint32_t word_addr = buf_addr + w * (32 * REC_STRIDE);
                 WALK_STAT(6, 1);
                 while (bits) {
-                    const int jj = __ffs(bits) - 1;
                     const uint32_t bit = bits & (0u - bits);
                     bits ^= bit;
+                    const int jj = __ffs(bit) - 1;
                     const uint32_t pos = base + jj + 1;  // 1-based list position == `contributor`
-                    if (pos > warp_last) break;
-                    if (pos <= warp_first) continue;
-                    const float4* rec = buf + (w * 32 + jj) * REC_QUADS;
-                    const float4 q0 = rec[0];
-                    const float4 q1 = rec[1];
+                    const uint32_t rec = word_addr + jj * REC_STRIDE;
+                    const float4 q0 = lds128(rec);
+                    const float4 q1 = lds128(rec + 16);
                     const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                     const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                     const float alpha = fminf(0.99f, q1.y * expf(power));
                     const bool open = pos > pre_pos;  // not yet folded into this pixel's prefix (false if !in_range)
-                    const bool act = open && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    const bool live = in_range && pos <= last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    const bool act = open && live;
                     WALK_STAT(0, 1);
                     if (!__any_sync(FULL, act)) {
                         WALK_STAT(1, 1);
                         if (pfx && open) pre_pos = pos;  // contributes to none of this pixel's samples, ever
-                        continue;
+                        continue;  // (the backward's list keeps what it had for this position)
                     }
-                    const float4 q2 = rec[2];
+                    const float4 q2 = lds128(rec + 32);
                     const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
                     const float rsigma = q2.y;
                     const bool ball = rsigma > 0;
-                    // Exact shortcut.  Every sample depth lies in [depth_min, depth_hi] (rounding is monotone),
-                    // so if that whole interval is more than 16 sigma in front of / behind the splat's peak
-                    // depth then |delta| > 16 at every sample and exp(-delta^2/2) is exactly 0.  (Splats thinner
-                    // than a few ulps of the depth itself are never treated as far: the backward re-derives the
-                    // median depth through a multiply that may move it by an ulp.)
+                    // Exact shortcuts (ggs_common.cuh).  Every sample depth lies in [depth_min, depth_hi] (rounding is
+                    // monotone), so a splat whose peak depth is r sigmas outside that interval is at least that far
+                    // from every sample.  QUIET (6.5): its factor is exactly (1 - alpha) in front of the bracket and
+                    // exactly 1 behind it.  Brackets only shrink, up to a few ulps of the depth; 6.5 against 6.004
+                    // leaves 0.49 sigma, twice what 4 ulps are worth for a splat whose sigma is 2e-6 of the depth;
+                    // thinner ones are never quiet.  FAR (16): exp() == 0 exactly, also in the backward's dT/dt sum
+                    // (which re-derives the median depth through a multiply that may move it by an ulp).
                     const float front = depth_min - t_peak;
                     const float back = t_peak - depth_hi;
-                    const float reach = fmaxf(front, back) * rsigma;  // |delta| of every sample is at least this
-                    const bool far = ball && reach > FAR_SIGMAS && rsigma * depth_hi < 4e6f;
-                    const bool quiet = ball && reach > QUIET_SIGMAS;  // far implies quiet
-                    const bool far_front = far && front > 0.f;  // stays so: depth_min never decreases
-                    // may be dropped for good only with some slack: the recomputed depth_hi of a later
-                    // iteration can sit a few ulps above this one
-                    const bool behind_for_good = far && !far_front && back > 1e-5f * depth_hi;
+                    const bool in_front = front > 0.f;
+                    const float reach = (in_front ? front : back) * rsigma;  // |delta| of every sample is at least this
+                    const bool quiet = ball && reach > QUIET_SIGMAS && rsigma * depth_hi < 5e5f;
                     // constant factor in every remaining iteration: (1 - alpha) in front, 1 behind, none if inactive
-                    const bool constant = !act || far_front || behind_for_good;
-                    const bool fold = pfx && open && constant;
-                    if (__any_sync(FULL, act && !behind_for_good && !fold)) keep |= bit;
+                    const bool fold = pfx && open && (!act || quiet);
                     if (__any_sync(FULL, act && !quiet)) {
+                        // needed again by this kernel, and by the backward
+                        keep |= bit;
                         WALK_STAT(2, 1);
                         WALK_STAT(4, __popc(__ballot_sync(FULL, act)));
                         WALK_STAT(5, __popc(__ballot_sync(FULL, act && !quiet)));
@@ -386,18 +408,28 @@ __global__ void __launch_bounds__(THREADS, 8)
                                     T_p[s] *= sample_factor(depth_min + interval * s, t_peak, rsigma, ball, alpha);
                             }
                         }
-                    } else if (act) {
-                        WALK_STAT(3, 1);
-                        // 1 - alpha * exp() is exactly 1 at every sample: factor = ((1 - alpha) | 1) * rsqrt(1)
-                        const bool in_front = front > 0.f;  // every active lane is quiet here: in front or behind
-                        const float f = (in_front ? (1.f - alpha) : 1.0f) * c1;
-                        if (in_front || !exact_one) {
-                            if (first) {
+                    } else {
+                        // 1 - alpha * exp() is exactly 1 at every sample of every active pixel: factor
+                        // ((1 - alpha) | 1) * rsqrt(1).  This kernel's list: a quiet splat behind the bracket is never
+                        // needed again, one in front is needed until every pixel has folded it into its prefix.
+                        if (__any_sync(FULL, act && in_front && !fold)) keep |= bit;
+                        // The backward's list: its dT/dt pass adds one term per (pixel, entry), in any order, so an
+                        // entry leaves that list once the term is exactly 0 for every pixel it is live on (pixels
+                        // that folded it into their prefix still vote) -- far in front, or far behind with some slack
+                        // (the recomputed depth_hi of a later iteration can sit a few ulps above this one).
+                        const bool gone = quiet && reach > FAR_SIGMAS && (in_front || back > 1e-5f * depth_hi);
+                        if (!__any_sync(FULL, live && !gone)) drop16 |= bit;
+                        if (act) {
+                            WALK_STAT(3, 1);
+                            const float f = (in_front ? (1.f - alpha) : 1.0f) * c1;
+                            if (in_front || !exact_one) {
+                                if (first) {
 #pragma unroll
-                                for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
-                            } else {
+                                    for (int s = 0; s < SPLIT + 1; s++) T_p[s] *= f;
+                                } else {
 #pragma unroll
-                                for (int s = 1; s < SPLIT; s++) T_p[s] *= f;
+                                    for (int s = 1; s < SPLIT; s++) T_p[s] *= f;
+                                }
                             }
                         }
                     }
@@ -408,11 +440,10 @@ __global__ void __launch_bounds__(THREADS, 8)
                         pfx = false;
                     }
                 }
-                // positions that were behind every pixel's bracket stay behind it (brackets only shrink):
-                // drop them from the warp's list.  Unvisited positions (beyond warp_last) are never needed.
                 if (exact_one && lane == 0 && gw < MASK_WORDS && gw < mask_words) {
-                    // bits below warp_first in this word were skipped, not examined: they are folded everywhere
                     s_mask[warp][gw] = keep;
+                    // the backward's list keeps what was not examined, except positions beyond warp_last
+                    s_mask[WARPS + warp][gw] &= ~drop16 & upto;
                 }
             }
         }
@@ -446,11 +477,18 @@ __global__ void __launch_bounds__(THREADS, 8)
     if (inside) out_mdepth[pix_id] = mDepth * rln;
 
     // what the backward's dT/dt pass has to visit: (near_first, ...] restricted to the thinned mask
-    const uint32_t nf = __reduce_min_sync(FULL, in_range ? pre_pos : NEVER);
-    if (lane == 0) near_first[tile_id * TILE_WARPS + twarp] = nf;
+    // what the backward's dT/dt pass has to visit: the 16-sigma mask, and the number of leading list positions it
+    // has cleared (the backward starts staging at the first batch any of its warps needs)
     __syncwarp();
-    for (uint32_t gw = lane; gw < min(mask_words, (uint32_t)MASK_WORDS); gw += 32)
-        near_mask[(size_t)(mask_base + gw) * 8 + twarp] = s_mask[warp][gw];
+    const uint32_t kept_words = min(mask_words, (uint32_t)MASK_WORDS);
+    uint32_t first_set = kept_words * 32u;  // nothing set among the kept words: positions beyond use the accept mask
+    for (uint32_t gw = lane; gw < kept_words; gw += 32) {
+        const uint32_t word = s_mask[WARPS + warp][gw];
+        near_mask[(size_t)(mask_base + gw) * 8 + twarp] = word;
+        if (word) first_set = min(first_set, gw * 32u + (uint32_t)__ffs(word) - 1u);
+    }
+    first_set = __reduce_min_sync(FULL, first_set);
+    if (lane == 0) near_first[tile_id * TILE_WARPS + twarp] = first_set;
 }
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,

@@ -16,7 +16,14 @@ namespace ggs {
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_PREFIX = 2u << 30;
 constexpr uint32_t VALUE_MASK = (1u << 30) - 1;
-constexpr int LOOK_WINDOW = 8;
+// blocks of the digit-histogram kernel: every block flushes up to passes x 256 bins with global atomics
+#ifndef GGS_HIST_BLOCKS
+#define GGS_HIST_BLOCKS (148 * 2)
+#endif
+#ifndef GGS_LOOK_WINDOW
+#define GGS_LOOK_WINDOW 8
+#endif
+constexpr int LOOK_WINDOW = GGS_LOOK_WINDOW;
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
     uint32_t v;
@@ -319,7 +326,7 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
     cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
     cudaMemsetAsync(status, 0, status_bytes, stream);
     cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
-    const int hist_blocks = (int)min((uint32_t)(148 * 8), (n + 255) / 256);
+    const int hist_blocks = (int)min((uint32_t)GGS_HIST_BLOCKS, (n + 255) / 256);
     histogram_kernel<uint64_t><<<hist_blocks, 256, 0, stream>>>(keys_a, n, specs, passes, hist);
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
     uint64_t* kin = keys_a;
@@ -368,7 +375,7 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
     cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
     cudaMemsetAsync(status, 0, status_bytes, stream);
     cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
-    const int hist_blocks = (int)min((uint32_t)(148 * 8), (n + 255) / 256);
+    const int hist_blocks = (int)min((uint32_t)GGS_HIST_BLOCKS, (n + 255) / 256);
     histogram_kernel<uint32_t><<<hist_blocks, 256, 0, stream>>>(keys_a, n, specs, passes, hist);
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
