@@ -223,7 +223,9 @@ class Step:
 
                 mc = {"0": False, "1": True}.get(os.environ.get("GGS_MULTICAST", ""), None)
                 pull = os.environ.get("GGS_PEER_PULL", "0") == "1"
-                self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc, pull_reduce=pull)
+                # zero_copy: the step drops its gradients (p.grad = None) before the next backward, as a trainer with
+                # zero_grad(set_to_none=True) does, so the sums may stay in the exchange buffers
+                self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc, pull_reduce=pull, zero_copy=True)
                 self.exchange_note = "fused peer-memory sum (ggs_view_sum_peer, %s%s)" % (
                     "NVSwitch multimem" if self.exchange.multicast_ptr else "P2P loads/stores",
                     ", slices reduced in the switch" if pull and self.exchange.multicast_ptr else

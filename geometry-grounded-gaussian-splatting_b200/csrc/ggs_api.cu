@@ -14,6 +14,8 @@ namespace {
 
 thread_local std::string g_error;
 thread_local uint32_t* g_pinned = nullptr;
+// the event behind the asynchronous read-back of the pair count, one per host thread and device
+thread_local cudaEvent_t g_count_event[MAX_DEVICES] = {};
 
 int fail(int code, const std::string& msg) {
     g_error = msg;
@@ -54,6 +56,15 @@ void prof_mark(cudaStream_t s, int which) {
         g_prof.created = true;
     }
     cudaEventRecord(g_prof.ev[which], s);
+}
+
+cudaEvent_t count_event() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return nullptr;
+    if (!g_count_event[dev] &&
+        cudaEventCreateWithFlags(&g_count_event[dev], cudaEventDisableTiming) != cudaSuccess)
+        g_count_event[dev] = nullptr;
+    return g_count_event[dev];
 }
 
 uint32_t* pinned_word() {
@@ -125,11 +136,20 @@ T* at(void* base, size_t off) {
     return reinterpret_cast<T*>(static_cast<char*>(base) + off);
 }
 
-// Bins the visible Gaussians of a frame: preprocess, scan, (sync), duplicate, sort, ranges.
-// On return *D holds the number of (tile, Gaussian) pairs and *bin the binning workspace.
+// Bins the visible Gaussians of a frame: preprocess, depth order, scan, duplicate, sort, ranges.
+// On return *D holds the number of (tile, Gaussian) pairs, *bin the binning workspace and *capacity the number of pairs
+// that workspace is laid out for (every later use of the workspace derives its offsets from it).
+//
+// The pair count D is produced on the device by the scan.  The reference blocks the host on it before it can size the
+// buffers and launch anything else (rasterizer_impl.cu:384).  capacity_hint == 0 does the same: capacity = D.  With a
+// hint (what a caller saw on earlier frames, with head room) the workspace is sized from the hint, the D-dependent
+// kernels are launched for the capacity and take the count from device memory, and the host only waits for the
+// count -- copied to pinned memory right behind the scan -- AFTER it has queued duplicate / sort / ranges: the device
+// never runs dry while the host launches.  If the count turns out to exceed the capacity the three stages are queued
+// again on an exact-size workspace (nothing downstream has consumed the short one).
 int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_color, int* radii, void* geom,
-                  uint2* ranges, GgsAllocFn alloc, void* user, void** bin, int64_t* D_out, bool debug,
-                  cudaStream_t stream) {
+                  uint2* ranges, GgsAllocFn alloc, void* user, void** bin, int64_t* D_out, int64_t capacity_hint,
+                  int64_t* capacity_out, bool debug, cudaStream_t stream) {
     const GeomLayout GL = geom_layout(fp.P);
     prof_mark(stream, EV_F0);
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
@@ -147,55 +167,76 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     GGS_STAGE("depth_order", debug, stream);
     prof_mark(stream, EV_ORDER);
     const uint32_t* order = at<uint32_t>(geom, GL.order_vals_a);
+    uint32_t* const total = at<uint32_t>(geom, GL.total);
     launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
-                at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter),
-                at<uint32_t>(geom, GL.total), stream, order);
+                at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter), total, stream, order);
     GGS_STAGE("scan", debug, stream);
     prof_mark(stream, EV_SCAN);
-    // one small read-back where the reference blocks too (rasterizer_impl.cu:384): D and the depth-key range
     uint32_t* host = pinned_word();
-    if (!host) return fail(GGS_ERR_CUDA, "cudaMallocHost failed");
-    GGS_CUDA(cudaMemcpyAsync(host, at<uint32_t>(geom, GL.total), 12, cudaMemcpyDeviceToHost, stream));
-    GGS_CUDA(cudaStreamSynchronize(stream));
-    const uint32_t D = host[0];
-    const uint32_t depth_max_bits = host[1], depth_min_bits = ~host[2];
-    if (D >= (1u << 30)) return fail(GGS_ERR_UNSUPPORTED, "more than 2^30 (tile, Gaussian) pairs");
-    *D_out = D;
+    cudaEvent_t counted = count_event();
+    if (!host || !counted) return fail(GGS_ERR_CUDA, "cudaMallocHost / cudaEventCreate failed");
+    GGS_CUDA(cudaMemcpyAsync(host, total, 4, cudaMemcpyDeviceToHost, stream));
+    GGS_CUDA(cudaEventRecord(counted, stream));
 
     const int tiles = fp.gx * fp.gy;
     const int end_bit = sort_end_bit(tiles);
-    const BinLayout BL = bin_layout(D, sort_passes(32, end_bit), tiles);
-    void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
-    if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
-    *bin = b;
-    (void)depth_min_bits;
-    (void)depth_max_bits;
-    // The pairs are emitted in depth order, so only the tile bits [32, end_bit) are left to sort (stable), and only
-    // the 32-bit tile halves of the keys move through the passes: two u32[D] ping-pong arrays inside keys_b; the
-    // last pass writes the reference's 64-bit keys into keys_a.  Sorted values always land in vals_a.
     const int tile_bits = end_bit - 32;
     const int passes = tile_sort_passes(tile_bits);
     g_prof.sort_passes = passes;
-    uint32_t* tk_a = at<uint32_t>(b, BL.keys_b);
-    uint32_t* tk_b = tk_a + D;
-    uint32_t* v_a = at<uint32_t>(b, BL.vals_a);
-    uint32_t* v_b = at<uint32_t>(b, BL.vals_b);
     const bool odd = passes & 1;
-    prof_mark(stream, EV_DUP0);
-    launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects), fp.gx,
-                          odd ? tk_b : tk_a, odd ? v_b : v_a, D, passes, at<uint32_t>(b, BL.hist), stream);
-    GGS_STAGE("duplicate_keys", debug, stream);
-    prof_mark(stream, EV_DUP);
-    launch_tile_sort(tk_a, tk_b, v_a, v_b, D, tile_bits, at<uint32_t>(geom, GL.depths), at<uint64_t>(b, BL.keys_a),
-                     at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), at<uint32_t>(b, BL.counters), stream);
-    GGS_STAGE("radix_sort", debug, stream);
-    prof_mark(stream, EV_SORT);
-    const uint64_t* sorted_keys = at<uint64_t>(b, BL.keys_a);
-    launch_tile_ranges(sorted_keys, D, ranges, tiles, stream);
-    GGS_STAGE("tile_ranges", debug, stream);
-    prof_mark(stream, EV_RANGES);
+    uint64_t cap = capacity_hint > 0 ? (uint64_t)std::min<int64_t>(capacity_hint, (1 << 30) - 1) : 0;
+    bool counted_yet = false;
+    uint32_t D = 0;
+    for (;;) {
+        if (cap == 0) {
+            // no hint (or the hint was too small): the host waits where the reference does
+            GGS_CUDA(cudaEventSynchronize(counted));
+            D = host[0];
+            counted_yet = true;
+            if (D >= (1u << 30)) return fail(GGS_ERR_UNSUPPORTED, "more than 2^30 (tile, Gaussian) pairs");
+            cap = D;
+        }
+        const BinLayout BL = bin_layout((size_t)cap, sort_passes(32, end_bit), tiles);
+        void* b = alloc(GGS_SLOT_BINNING, BL.bytes, user);
+        if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
+        *bin = b;
+        // The pairs are emitted in depth order, so only the tile bits [32, end_bit) are left to sort (stable), and only
+        // the 32-bit tile halves of the keys move through the passes: two u32[cap] ping-pong arrays inside keys_b; the
+        // last pass writes the reference's 64-bit keys into keys_a.  Sorted values always land in vals_a.
+        uint32_t* tk_a = at<uint32_t>(b, BL.keys_b);
+        uint32_t* tk_b = tk_a + cap;
+        uint32_t* v_a = at<uint32_t>(b, BL.vals_a);
+        uint32_t* v_b = at<uint32_t>(b, BL.vals_b);
+        const uint32_t* n_dev = counted_yet ? nullptr : total;
+        prof_mark(stream, EV_DUP0);
+        launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects), fp.gx,
+                              odd ? tk_b : tk_a, odd ? v_b : v_a, (uint32_t)cap, passes, at<uint32_t>(b, BL.hist),
+                              stream);
+        GGS_STAGE("duplicate_keys", debug, stream);
+        prof_mark(stream, EV_DUP);
+        launch_tile_sort(tk_a, tk_b, v_a, v_b, (uint32_t)cap, n_dev, tile_bits, at<uint32_t>(geom, GL.depths),
+                         at<uint64_t>(b, BL.keys_a), at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status),
+                         at<uint32_t>(b, BL.counters), stream);
+        GGS_STAGE("radix_sort", debug, stream);
+        prof_mark(stream, EV_SORT);
+        launch_tile_ranges(at<uint64_t>(b, BL.keys_a), (uint32_t)cap, n_dev, ranges, tiles, stream);
+        GGS_STAGE("tile_ranges", debug, stream);
+        prof_mark(stream, EV_RANGES);
+        if (counted_yet) break;
+        GGS_CUDA(cudaEventSynchronize(counted));  // long since signalled: the device is busy with the three stages
+        D = host[0];
+        counted_yet = true;
+        if (D >= (1u << 30)) return fail(GGS_ERR_UNSUPPORTED, "more than 2^30 (tile, Gaussian) pairs");
+        if (D <= cap) break;
+        cap = 0;  // the hint was too small: once more, exact
+    }
+    *D_out = D;
+    *capacity_out = (int64_t)cap;
     return GGS_OK;
 }
+
+// pairs the binning workspace of a finished forward is laid out for (a state filled in by hand, capacity 0: exact)
+int64_t state_capacity(const GgsForwardState* s) { return s->capacity > 0 ? s->capacity : s->num_rendered; }
 
 const uint32_t* sorted_list(void* bin, int64_t D, int tiles) {
     const int passes = sort_passes(32, sort_end_bit(tiles));
@@ -246,8 +287,10 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     const bool debug = frame->debug != 0;
     const size_t npix = (size_t)fp.W * fp.H;
     const int tiles = fp.gx * fp.gy;
+    const int64_t capacity_hint = state->capacity;  // in: 0 = none (see include/ggs_rasterizer.h)
     state->geometry = state->binning = state->image = state->tile = nullptr;
     state->num_rendered = 0;
+    state->capacity = 0;
 
     if (fp.P == 0) {
         // rasterize_points.cu:95: nothing is launched, the zero-filled outputs are returned
@@ -269,13 +312,14 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     state->tile = tile;
     state->image = img;
 
-    int64_t D = 0;
+    int64_t D = 0, cap = 0;
     void* bin = nullptr;
-    rc = bin_gaussians(fp, in, true, out->radii, geom, at<uint2>(tile, TL.ranges), alloc, user, &bin, &D, debug,
-                       stream);
+    rc = bin_gaussians(fp, in, true, out->radii, geom, at<uint2>(tile, TL.ranges), alloc, user, &bin, &D,
+                       capacity_hint, &cap, debug, stream);
     if (rc) return rc;
     state->binning = bin;
     state->num_rendered = D;
+    state->capacity = cap;
 
     if (!frame->require_depth) {
         GGS_CUDA(cudaMemsetAsync(out->normal, 0, 3 * npix * 4, stream));
@@ -288,11 +332,11 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     ro.mdepth = out->mdepth;
     ro.n_contrib = at<uint32_t>(img, IL.n_contrib);
     ro.max_contributor = at<uint32_t>(tile, TL.max_contributor);
-    ro.accept_mask = accept_mask(bin, D, tiles);
+    ro.accept_mask = accept_mask(bin, cap, tiles);
     ro.warp_words = at<uint32_t>(tile, TL.warp_words);
-    ro.near_mask = near_mask(bin, D, tiles);
+    ro.near_mask = near_mask(bin, cap, tiles);
     ro.near_first = at<uint32_t>(tile, TL.near_first);
-    launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, D, tiles),
+    launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, cap, tiles),
                           at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
     GGS_STAGE("render_forward", debug, stream);
     prof_mark(stream, EV_RENDER);
@@ -384,15 +428,15 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     ri.mdepth = bi->mdepth;
     ri.n_contrib = at<uint32_t>(state->image, 0);
     ri.max_contributor = at<uint32_t>(state->tile, TL.max_contributor);
-    ri.accept_mask = accept_mask(state->binning, state->num_rendered, tiles);
+    ri.accept_mask = accept_mask(state->binning, state_capacity(state), tiles);
     ri.warp_words = at<uint32_t>(state->tile, TL.warp_words);
-    ri.near_mask = near_mask(state->binning, state->num_rendered, tiles);
+    ri.near_mask = near_mask(state->binning, state_capacity(state), tiles);
     ri.near_first = at<uint32_t>(state->tile, TL.near_first);
     ri.dL_dcolor = bi->dL_dcolor;
     ri.dL_dmdepth = bi->dL_dmdepth;
     ri.dL_dalpha = bi->dL_dalpha;
     ri.dL_dnormal = bi->dL_dnormal;
-    launch_render_backward(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state->num_rendered, tiles),
+    launch_render_backward(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state_capacity(state), tiles),
                            at<SplatRecord>(state->geometry, GL.records), ri, acc, frame->require_depth != 0, stream);
     GGS_STAGE("render_backward", debug, stream);
     prof_mark(stream, EV_RBWD);
@@ -662,7 +706,7 @@ int ggs_count_blend_ops(const GgsFrame* frame, const GgsGaussians* gaussians, co
     const int tiles = fp.gx * fp.gy;
     const GeomLayout GL = geom_layout(fp.P);
     const TileLayout TL = tile_layout(tiles);
-    launch_count_blend_ops(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state->num_rendered, tiles),
+    launch_count_blend_ops(fp, at<uint2>(state->tile, TL.ranges), sorted_list(state->binning, state_capacity(state), tiles),
                            at<SplatRecord>(state->geometry, GL.records),
                            reinterpret_cast<unsigned long long*>(counters), stream);
     GGS_STAGE("count_blend_ops", false, stream);
@@ -771,10 +815,11 @@ int prepare_view(const GgsFrame* frame, const GgsGaussians* gaussians, GgsAllocF
     void* geom = alloc(GGS_SLOT_GEOMETRY, GL.bytes, user);
     void* tile = alloc(GGS_SLOT_TILE, TL.bytes, user);
     if (!geom || !tile) return fail(GGS_ERR_ALLOC, "workspace allocation failed");
-    int64_t D = 0;
+    int64_t D = 0, cap = 0;
     void* bin = nullptr;
+    // no capacity hint: a prepared view is binned once and queried many times, its workspace is exact (capacity == D)
     rc = bin_gaussians(fp, in, false, at<int>(tile, TL.radii), geom, at<uint2>(tile, TL.granges), alloc, user, &bin, &D,
-                       frame->debug != 0, stream);
+                       0, &cap, frame->debug != 0, stream);
     if (rc) return rc;
     view->geometry = geom;
     view->binning = bin;

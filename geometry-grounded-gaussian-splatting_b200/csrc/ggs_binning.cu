@@ -150,8 +150,8 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
                                                                      const uint32_t* __restrict__ offsets,
                                                                      const uint2* __restrict__ rects, int gx,
                                                                      uint32_t* __restrict__ tile_keys,
-                                                                     uint32_t* __restrict__ vals, int passes,
-                                                                     uint32_t* __restrict__ hist) {
+                                                                     uint32_t* __restrict__ vals, uint32_t capacity,
+                                                                     int passes, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_off[DUP_THREADS + 1];
     __shared__ uint32_t s_g[DUP_THREADS];
     __shared__ uint2 s_rect[DUP_THREADS];
@@ -175,7 +175,9 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
     // whole warps walk the slice together (the histogram votes below need every lane)
     for (uint32_t ob = (tid & ~31u); ob < span; ob += DUP_THREADS) {
         const uint32_t o = begin + ob + (tid & 31u);
-        const bool live = o < end;
+        // `capacity`: slots of the key arrays.  It is the exact pair count unless the workspace was sized from a hint
+        // before the count was known; a count beyond it is detected by the host, which bins again (ggs_api.cu)
+        const bool live = o < end && o < capacity;
         uint32_t tile = 0;
         if (live) {
             // largest j in [0,last) with s_off[j] <= o
@@ -224,12 +226,12 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
 }
 
 void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
-                           uint32_t* tile_keys, uint32_t* vals, uint32_t D, int passes, uint32_t* hist,
+                           uint32_t* tile_keys, uint32_t* vals, uint32_t capacity, int passes, uint32_t* hist,
                            cudaStream_t stream) {
     cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
-    if (P == 0 || D == 0) return;
+    if (P == 0 || capacity == 0) return;
     duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(
-        P, order, offsets, rects, gx, tile_keys, vals, passes > 4 ? 4 : passes, hist);
+        P, order, offsets, rects, gx, tile_keys, vals, capacity, passes > 4 ? 4 : passes, hist);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -239,7 +241,9 @@ void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets
 // at a third of the HBM rate.
 constexpr int RANGE_ITEMS = 4;
 __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n,
+                                                          const uint32_t* __restrict__ n_dev,
                                                           uint2* __restrict__ ranges) {
+    if (n_dev) n = min(n, __ldg(n_dev));  // launched for the capacity, the count lives on the device
     const uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) * RANGE_ITEMS;
     if (base >= n) return;
     uint32_t t[RANGE_ITEMS + 1];
@@ -270,11 +274,12 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __rest
     }
 }
 
-void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream) {
+void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
+                        cudaStream_t stream) {
     cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
     if (n == 0) return;
     const uint32_t per_block = 256 * RANGE_ITEMS;
-    tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_keys, n, ranges);
+    tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_keys, n, n_dev, ranges);
 }
 
 }  // namespace ggs

@@ -41,8 +41,10 @@ void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uin
 // order[i] = Gaussian at depth rank i; offsets = inclusive scan of the tile counts in that order.  Emits 32-bit TILE
 // keys (the depth half of the reference's 64-bit key is implied by the emission order) and accumulates the 8-bit
 // digit histograms of the `passes` tile-sort passes into hist[passes][256] (zeroed here).
+// `capacity`: slots of the key arrays -- the pair count, or more when the workspace was sized from a hint before the
+// count was known (slots beyond the count stay unwritten; pairs beyond the capacity are dropped, see bin_gaussians).
 void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
-                           uint32_t* tile_keys, uint32_t* vals, uint32_t D, int passes, uint32_t* hist,
+                           uint32_t* tile_keys, uint32_t* vals, uint32_t capacity, int passes, uint32_t* hist,
                            cudaStream_t stream);
 
 // Digit plan of the radix sort.  Plain: 8-bit digits of bits [begin_bit, end_bit).  Compact (rasterizer keys
@@ -77,11 +79,14 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
                         cudaStream_t stream);
 int tile_sort_passes(int tile_bits);
-void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int tile_bits,
-                      const uint32_t* depth_bits, uint64_t* keys64_out, uint32_t* hist, uint32_t* status,
-                      uint32_t* counters, cudaStream_t stream);
+// n_dev (may be null): the pair count in device memory; the launch is then sized for n = the capacity and the kernels
+// clamp to min(n, *n_dev).
+void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
+                      const uint32_t* n_dev, int tile_bits, const uint32_t* depth_bits, uint64_t* keys64_out,
+                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream);
 
-void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, uint2* ranges, int tiles, cudaStream_t stream);
+void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
+                        cudaStream_t stream);
 
 // ---- stage 3: tile blend --------------------------------------------------------------------
 struct RenderOut {

@@ -163,8 +163,10 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
                                                                 uint32_t* __restrict__ status,
                                                                 uint32_t* __restrict__ counter,
                                                                 uint64_t* __restrict__ keys64_out,
-                                                                const uint32_t* __restrict__ depth_bits) {
+                                                                const uint32_t* __restrict__ depth_bits,
+                                                                const uint32_t* __restrict__ n_dev) {
     constexpr int WARPS = SORT_THREADS / 32;
+    if (n_dev) n = min(n, __ldg(n_dev));  // launched for the capacity, the count lives on the device
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_warp_hist[WARPS][RADIX];
     __shared__ uint32_t s_bin_start[RADIX];
@@ -179,6 +181,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t base = tile * SORT_TILE;
+    if (base >= n) return;  // (whole block: tiles beyond the count publish nothing and nobody looks back at them)
     const uint32_t count = min((uint32_t)SORT_TILE, n - base);
 
     // ---- load (warp-striped) and rank --------------------------------------------------------
@@ -339,11 +342,11 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
         if (tile_digit)
             onesweep_kernel<false, uint64_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
-                nullptr, nullptr);
+                nullptr, nullptr, nullptr);
         else
             onesweep_kernel<true, uint64_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
-                nullptr, nullptr);
+                nullptr, nullptr, nullptr);
         uint64_t* tk = kin;
         kin = kout;
         kout = tk;
@@ -385,11 +388,11 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
         if (p == 0)
             onesweep_kernel<true, uint32_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
-                nullptr, nullptr);
+                nullptr, nullptr, nullptr);
         else
             onesweep_kernel<false, uint32_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
-                nullptr, nullptr);
+                nullptr, nullptr, nullptr);
         uint32_t* tk = kin;
         kin = kout;
         kout = tk;
@@ -402,9 +405,9 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
 
 int tile_sort_passes(int tile_bits) { return (tile_bits + RADIX_BITS - 1) / RADIX_BITS; }
 
-void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int tile_bits,
-                      const uint32_t* depth_bits, uint64_t* keys64_out, uint32_t* hist, uint32_t* status,
-                      uint32_t* counters, cudaStream_t stream) {
+void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
+                      const uint32_t* n_dev, int tile_bits, const uint32_t* depth_bits, uint64_t* keys64_out,
+                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream) {
     if (n == 0) return;
     const int passes = tile_sort_passes(tile_bits);
     const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
@@ -426,10 +429,10 @@ void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t
         // tile digits of depth-ordered pairs come in runs: rank with ballots (see onesweep_kernel)
         if (p + 1 == passes)
             onesweep_kernel<false, uint32_t, true><<<tiles, SORT_THREADS, 0, stream>>>(
-                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, keys64_out, depth_bits);
+                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, keys64_out, depth_bits, n_dev);
         else
             onesweep_kernel<false, uint32_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
-                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, nullptr, nullptr);
+                kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, nullptr, nullptr, n_dev);
         uint32_t* tk = kin;
         kin = kout;
         kout = tk;

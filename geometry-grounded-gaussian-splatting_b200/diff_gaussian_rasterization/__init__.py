@@ -19,6 +19,7 @@ include/ggs_rasterizer.h; this file only marshals tensors.  No CPU / PyTorch fal
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import NamedTuple
 
 import torch
@@ -54,6 +55,20 @@ class GaussianRasterizationSettings(NamedTuple):
 # (ggs_sh_gradient_from_views).  Process-wide on purpose: autograd runs the backward on its own thread.
 # "exchange": a parallel.PeerGradientExchange -- the sums then go through peer memory in one fused launch instead of NCCL.
 _SH_FACTORING = {"on": False, "group": None, "exchange": None}
+
+# Pair-count hints for ggs_rasterize_forward (GgsForwardState.capacity): with a hint the host does not block on the
+# count before it launches the rest of the forward (the reference does, rasterizer_impl.cu:384).  Per (device, P, H, W):
+# 1.25 x the largest count of recent frames, decaying slowly; a frame that exceeds its hint is binned again at its exact
+# size, so results never depend on it.  A cache of sizes, nothing else: losing it costs one blocking frame.
+_CAPACITY_HINTS: dict = {}
+_USE_HINTS = os.environ.get("GGS_CAPACITY_HINTS", "1") != "0"  # 0: every forward blocks on the count (A/B timing)
+
+
+def _remember_pair_count(key, n):
+    old = _CAPACITY_HINTS.get(key, 0)
+    _CAPACITY_HINTS[key] = max(int(n * 1.25) + 4096, int(old * 0.97))
+    if len(_CAPACITY_HINTS) > 64:
+        _CAPACITY_HINTS.pop(next(iter(_CAPACITY_HINTS)))
 
 
 def _dev_f32(t, device):
@@ -197,6 +212,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             out = _abi.GgsForwardOutputs(_abi.ptr(color), _abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth),
                                          _abi.ptr(radii))
             state = _abi.GgsForwardState()
+            hint_key = (device.index, P, H, W)
+            state.capacity = _CAPACITY_HINTS.get(hint_key, 0) if (_USE_HINTS and not rs.debug) else 0
             arena = _abi.Arena(device)
             n = _lib.ggs_rasterize_forward(C.byref(frame), C.byref(g), arena.fn, None, C.byref(out), C.byref(state),
                                            _abi.stream_handle(device))
@@ -205,8 +222,10 @@ class _RasterizeGaussians(torch.autograd.Function):
                 if arena.error is not None:
                     raise arena.error
                 _abi.check(n, "ggs_rasterize_forward")
+            _remember_pair_count(hint_key, int(n))
         ctx.raster_settings = rs
         ctx.num_rendered = int(n)
+        ctx.capacity = int(state.capacity)
         ctx.arena = arena
         ctx.had = [_present(t) for t in (sh, sg_axis, sg_sharpness, sg_color, colors_precomp)]
         ctx.save_for_backward(m3, op, sc, ro, sh_, sa, ss, sgc, cp, alpha, normal, mdepth, radii)
@@ -261,7 +280,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             fwd = ctx.arena.buffers
             state = _abi.GgsForwardState(
                 _abi.ptr(fwd.get(_abi.SLOT_GEOMETRY)), _abi.ptr(fwd.get(_abi.SLOT_BINNING)),
-                _abi.ptr(fwd.get(_abi.SLOT_IMAGE)), _abi.ptr(fwd.get(_abi.SLOT_TILE)), ctx.num_rendered)
+                _abi.ptr(fwd.get(_abi.SLOT_IMAGE)), _abi.ptr(fwd.get(_abi.SLOT_TILE)), ctx.num_rendered,
+                ctx.capacity)
             bi = _abi.GgsBackwardInputs(_abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth), _abi.ptr(radii),
                                         _abi.ptr(gc), _abi.ptr(gd), _abi.ptr(ga), _abi.ptr(gn))
             grads = _abi.GgsGradients(_abi.ptr(d_means3D), _abi.ptr(d_means2D), _abi.ptr(d_colors),

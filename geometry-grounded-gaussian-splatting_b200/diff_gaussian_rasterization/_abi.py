@@ -15,6 +15,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # there is still no fallback -- whatever path is named must exist and export the whole ABI.
 LIB_PATH = os.environ.get("GGS_RASTERIZER_LIB") or os.path.join(_HERE, "libggs_rasterizer.so")
 
+ABI_VERSION = 2  # GGS_ABI_VERSION of include/ggs_rasterizer.h this binding was written against
+
 (SLOT_GEOMETRY, SLOT_BINNING, SLOT_IMAGE, SLOT_TILE, SLOT_POINT, SLOT_POINT_BINNING, SLOT_BACKWARD,
  SLOT_BLOCKS) = range(8)
 
@@ -47,8 +49,9 @@ class GgsForwardOutputs(C.Structure):
 
 
 class GgsForwardState(C.Structure):
+    # capacity: in = hint (0: none, the forward blocks on the pair count), out = pairs the binning workspace is laid out for
     _fields_ = [("geometry", C.c_void_p), ("binning", C.c_void_p), ("image", C.c_void_p), ("tile", C.c_void_p),
-                ("num_rendered", C.c_int64)]
+                ("num_rendered", C.c_int64), ("capacity", C.c_int64)]
 
 
 class GgsSampleState(C.Structure):
@@ -180,7 +183,7 @@ def _load():
     lib.ggs_activate_backward.argtypes = [C.c_int64] + [C.c_void_p] * 11
     lib.ggs_profile_read.restype = C.c_int
     lib.ggs_profile_read.argtypes = [C.POINTER(GgsStageTimes)]
-    if lib.ggs_abi_version() != 1:
+    if lib.ggs_abi_version() != ABI_VERSION:
         raise ImportError("libggs_rasterizer.so has an unexpected ABI version")
     return lib
 
@@ -253,6 +256,8 @@ def profile_read() -> dict:
 
 
 def describe_layout(P: int, W: int, H: int, num_rendered: int) -> GgsLayout:
+    # num_rendered: the CAPACITY the binning workspace is laid out for (GgsForwardState.capacity; == the pair count
+    # when the forward ran without a hint)
     L = GgsLayout()
     check(lib.ggs_describe_layout(P, W, H, num_rendered, C.byref(L)), "ggs_describe_layout")
     return L

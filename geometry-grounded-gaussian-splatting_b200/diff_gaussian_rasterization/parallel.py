@@ -59,6 +59,34 @@ def exchange_layout(P: int, world: int) -> dict:
     return L
 
 
+class ResultLease:
+    """Guards results handed out as views into persistent buffers: `check()` raises if tensors of the previous hand-out
+    are still alive when the buffers are about to be overwritten (autograd's AccumulateGrad would then add the new sum
+    to a `.grad` that aliases it: twice the new gradient, the old one lost)."""
+
+    def __init__(self, what: str):
+        import weakref
+
+        self._weakref = weakref
+        self.what = what
+        self._refs = []
+
+    def alive(self) -> int:
+        return sum(1 for r in self._refs if r() is not None)
+
+    def check(self):
+        n = self.alive()
+        if n:
+            raise RuntimeError(
+                f"{self.what}: {n} gradient tensor(s) of the previous backward are still referenced and alias the "
+                "exchange buffers the next backward overwrites.  Drop them first (optimizer.zero_grad(set_to_none=True) "
+                "/ p.grad = None), or build the exchange with zero_copy=False (results are then cloned out of the buffers).")
+
+    def hand_out(self, tensors):
+        self._refs = [self._weakref.ref(t) for t in tensors]
+        return tensors
+
+
 class PeerGradientExchange:
     """View-parallel gradient sums through peer memory (NVLink / NVSwitch) instead of NCCL collectives.
 
@@ -73,7 +101,13 @@ class PeerGradientExchange:
          gradients; node barrier.
     Wire bytes received per rank and step: 12 B x P x (world - 1) colour gradients + 2 x 44 B x P x (world - 1) / world."""
 
-    def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool = False):
+    def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool = False,
+                 zero_copy: bool = False):
+        """`zero_copy=False` (default): the summed gradients are cloned out of the exchange buffers (236 B per
+        Gaussian at SH3), so they may be kept, accumulated into, or outlive the next backward like any gradient.
+        `zero_copy=True`: they are views into the buffers, valid until the next backward through this exchange; that
+        backward raises if they are still referenced (`ResultLease`).  The buffers are sized for `P` Gaussians: after
+        densification / pruning build a new exchange (`resized`)."""
         import ctypes as C
 
         import torch.distributed._symmetric_memory as symm
@@ -87,6 +121,9 @@ class PeerGradientExchange:
         if self.world > 16:
             raise RuntimeError("at most 16 ranks (one node)")
         self.P, self.device = int(P), torch.device(device)
+        self.zero_copy = bool(zero_copy)
+        self._lease = ResultLease("PeerGradientExchange(zero_copy=True)")
+        self._args = dict(multicast=multicast, pull_reduce=pull_reduce, zero_copy=zero_copy)
         L = self.layout = exchange_layout(self.P, self.world)
         self.buf = symm.empty(L["total"], dtype=torch.float32, device=self.device)
         self.buf.zero_()
@@ -114,8 +151,18 @@ class PeerGradientExchange:
         self.hdl.barrier(channel=0)
 
     def check(self, P, device):
+        """Called when a backward starts: the buffers must fit, and nothing may still alias what is about to be
+        overwritten."""
         if int(P) != self.P or torch.device(device) != self.device:
-            raise RuntimeError("PeerGradientExchange was built for another Gaussian count / device")
+            raise RuntimeError(f"PeerGradientExchange was built for {self.P} Gaussians on {self.device}, the backward has "
+                               f"{int(P)} on {torch.device(device)}: after densification / pruning build a new one "
+                               "(exchange.resized(P)) on every rank")
+        if self.zero_copy:
+            self._lease.check()
+
+    def resized(self, P: int) -> "PeerGradientExchange":
+        """A new exchange for `P` Gaussians with the same options (collective: call it on every rank of the group)."""
+        return PeerGradientExchange(P, self.device, self.group, **self._args)
 
     def _view(self, base, name):
         o, w = self.layout[name]
@@ -129,8 +176,8 @@ class PeerGradientExchange:
 
     def sum_over_views(self, rs, means3D, SHM):
         """Call after `ggs_rasterize_backward_peer(..., side_stream=self.side)` has been enqueued on the current stream.
-        Returns the gradients of (means3D, opacities, scales, rotations, shs) summed over the views of all ranks; all
-        five live in buffers of this object and are valid until the next backward."""
+        Returns the gradients of (means3D, opacities, scales, rotations, shs) summed over the views of all ranks: clones,
+        or with zero_copy=True views into buffers of this object that are valid until the next backward."""
         import ctypes as C
 
         from . import _abi
@@ -159,8 +206,11 @@ class PeerGradientExchange:
         r = self.layout["recv"]
         # fresh view objects: autograd's AccumulateGrad adopts a gradient it holds the only reference to, and clones
         # (192 MB for the SH gradient) one that something else still references
-        return (self._view(r, "means3D"), self._view(r, "opacities"), self._view(r, "scales"),
-                self._view(r, "rotations"), d_sh.view(self.P, SHM, 3))
+        out = (self._view(r, "means3D"), self._view(r, "opacities"), self._view(r, "scales"),
+               self._view(r, "rotations"), d_sh.view(self.P, SHM, 3))
+        if self.zero_copy:
+            return self._lease.hand_out(out)
+        return tuple(t.clone() for t in out)
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:

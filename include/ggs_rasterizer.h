@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GGS_ABI_VERSION 1
+#define GGS_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define GGS_API __attribute__((visibility("default")))
@@ -117,13 +117,23 @@ typedef struct GgsForwardOutputs {
     int32_t* radii; /* [P] */
 } GgsForwardOutputs;
 
-/* What the forward handed out and the backward needs again. */
+/* What the forward handed out and the backward needs again.
+ * `capacity` is read by ggs_rasterize_forward as a HINT and written back:
+ *   in   0: none.  The host waits for the pair count before it sizes the binning workspace and launches anything
+ *           else -- where the reference blocks (rasterizer_impl.cu:384).
+ *       >0: pairs to lay the binning workspace out for (e.g. 1.25 x the count of the caller's last frames).  The
+ *           count-dependent kernels are launched for that capacity and take the count from device memory; the host
+ *           waits for the count only after it has queued them, and queues them again on an exact-size workspace if
+ *           the count exceeds the hint.  Results do not depend on the hint.
+ *   out  the number of pairs the binning workspace IS laid out for (>= num_rendered); the backward and
+ *        ggs_describe_layout take their offsets from it. */
 typedef struct GgsForwardState {
     void* geometry;
     void* binning;
     void* image;
     void* tile;
     int64_t num_rendered;
+    int64_t capacity;
 } GgsForwardState;
 
 typedef struct GgsBackwardInputs {

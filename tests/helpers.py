@@ -98,7 +98,7 @@ def _bytes_view(buf, offset, dtype, count):
     return buf[offset:offset + count * itemsize].view(dtype)
 
 
-def ours_forward_raw(sc, device, require_depth=True, want_ctx=False):
+def ours_forward_raw(sc, device, require_depth=True, want_ctx=False, capacity_hint=0):
     """Forward through the C ABI keeping the workspaces; returns outputs + bit-exact intermediates (+ the call's frame /
     Gaussians / state structures with want_ctx, for entry points that take a finished forward)."""
     import ctypes as C
@@ -122,19 +122,22 @@ def ours_forward_raw(sc, device, require_depth=True, want_ctx=False):
     out = _abi.GgsForwardOutputs(_abi.ptr(color), _abi.ptr(alpha), _abi.ptr(normal), _abi.ptr(mdepth),
                                  _abi.ptr(radii))
     state = _abi.GgsForwardState()
+    state.capacity = int(capacity_hint)  # 0: the forward blocks on the pair count, as the reference does
     arena = _abi.Arena(torch.device(device))
     n = _abi.lib.ggs_rasterize_forward(C.byref(frame), C.byref(g), arena.fn, None, C.byref(out), C.byref(state),
                                        _abi.stream_handle(torch.device(device)))
     _abi.check(n, "ggs_rasterize_forward")
     torch.cuda.synchronize(device)
     D = int(n)
-    L = _abi.describe_layout(P, W, H, D)
+    assert int(state.num_rendered) == D and int(state.capacity) >= D
+    L = _abi.describe_layout(P, W, H, int(state.capacity))
     geom, binb, img, tile = (arena.buffers[s] for s in (_abi.SLOT_GEOMETRY, _abi.SLOT_BINNING, _abi.SLOT_IMAGE,
                                                        _abi.SLOT_TILE))
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     rec = _bytes_view(geom, L.records, torch.float32, P * 16).view(P, 16)
     inter = dict(
         num_rendered=D,
+        capacity=int(state.capacity),
         tiles_touched=_bytes_view(geom, L.tiles_touched, torch.int32, P).clone(),
         point_offsets=_bytes_view(geom, L.point_offsets, torch.int32, P).clone(),  # scan in depth order
         depth_order=_bytes_view(geom, L.depth_order, torch.int32, P).clone(),

@@ -26,7 +26,7 @@ def test_header_symbols_exported():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/ggs_rasterizer.h but not exported"
     assert set(names) == set(_abi.EXPORTS)
-    assert lib.ggs_abi_version() == 1
+    assert lib.ggs_abi_version() == 2
 
 
 def test_no_torch_in_abi_and_arch():

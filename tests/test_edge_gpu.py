@@ -164,3 +164,48 @@ def test_point_queries_accept_the_reference_callers_bg(device):
     c0, j0 = want.sample_depth(pts, *x)
     c1, j1 = zero.sample_depth(pts, *x)
     assert torch.equal(c0, c1) and torch.equal(j0, j1)
+
+
+@pytest.mark.parametrize("scene", [dict(name="tiny", scale_mult=4.0, seed=77), dict(name="c1")],
+                         ids=["tiny_dense", "c1"])
+def test_capacity_hint_does_not_change_results(device, scene):
+    """GgsForwardState.capacity (include/ggs_rasterizer.h): with a hint the host no longer blocks on the pair count
+    before it launches duplicate / sort / ranges, the kernels take the count from device memory and the workspace is
+    laid out for the hint.  Generous hint, exact hint, hint too small (binned again at the exact size), hint 1: images,
+    sorted keys / list / ranges are bit-identical to the blocking call."""
+    sc = scenes.make_scene(**scene)
+    ref_out, ref_it = H.ours_forward_raw(sc, device)
+    D = ref_it["num_rendered"]
+    assert ref_it["capacity"] == D and D > 0
+    for hint in (2 * D + 12345, D + 1, D, D - 1, D // 2, 1):
+        out, it = H.ours_forward_raw(sc, device, capacity_hint=hint)
+        assert it["num_rendered"] == D
+        assert it["capacity"] == (hint if hint >= D else D), (hint, it["capacity"])
+        for k in ("color", "alpha", "mdepth", "normal", "radii"):
+            assert torch.equal(out[k], ref_out[k]), (hint, k)
+        for k in ("sorted_keys", "point_list", "ranges", "max_contributor", "n_contrib"):
+            assert torch.equal(it[k], ref_it[k]), (hint, k)
+
+
+def test_hinted_forward_backward_through_the_module(device):
+    """The Python surface keeps a per-(device, P, H, W) hint: the first call blocks, the next ones do not; forward
+    and backward results are the same bits either way (the backward takes its offsets from the capacity)."""
+    import diff_gaussian_rasterization as ours
+
+    sc = scenes.make_scene("c1")
+    ours._CAPACITY_HINTS.clear()
+    out0, g0 = H.run_module(ours, sc, device)
+    assert len(ours._CAPACITY_HINTS) == 1 and next(iter(ours._CAPACITY_HINTS.values())) > 0
+    out1, g1 = H.run_module(ours, sc, device)
+    for k in out0:
+        assert torch.equal(out0[k], out1[k]), k
+    for k in g0:
+        assert torch.equal(g0[k], g1[k]), k
+    # a stale hint that is far too small
+    key = next(iter(ours._CAPACITY_HINTS))
+    ours._CAPACITY_HINTS[key] = 7
+    out2, g2 = H.run_module(ours, sc, device)
+    for k in out0:
+        assert torch.equal(out0[k], out2[k]), k
+    for k in g0:
+        assert torch.equal(g0[k], g2[k]), k

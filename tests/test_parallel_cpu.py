@@ -228,3 +228,31 @@ def test_gloo_world2_ranks_agree_on_the_number_of_pre_run_steps():
         p.join(180)
         assert p.exitcode == 0
     assert dict(ret) == {0: 5, 1: 5}
+
+
+def test_result_lease_detects_aliasing_gradients():
+    """results handed out as views into persistent buffers must not survive into the next
+    backward unnoticed."""
+    import gc
+
+    import pytest
+    import torch
+
+    from diff_gaussian_rasterization.parallel import ResultLease
+
+    buf = torch.zeros(8)
+    lease = ResultLease("test")
+    lease.check()  # nothing handed out yet
+    views = lease.hand_out((buf[:4].view(2, 2), buf[4:].view(2, 2)))
+    assert lease.alive() == 2
+    with pytest.raises(RuntimeError, match="still referenced"):
+        lease.check()
+    holder = views[0]  # e.g. a parameter's .grad
+    del views
+    gc.collect()
+    assert lease.alive() == 1
+    with pytest.raises(RuntimeError):
+        lease.check()
+    del holder
+    gc.collect()
+    lease.check()
