@@ -222,14 +222,14 @@ class Step:
                 from diff_gaussian_rasterization.parallel import PeerGradientExchange
 
                 mc = {"0": False, "1": True}.get(os.environ.get("GGS_MULTICAST", ""), None)
-                pull = os.environ.get("GGS_PEER_PULL", "0") == "1"
+                pull = {"0": False, "1": True}.get(os.environ.get("GGS_PEER_PULL", ""), None)  # default: with multicast
                 # zero_copy: the step drops its gradients (p.grad = None) before the next backward, as a trainer with
                 # zero_grad(set_to_none=True) does, so the sums may stay in the exchange buffers
                 self.exchange = PeerGradientExchange(sc.P, dev, multicast=mc, pull_reduce=pull, zero_copy=True)
                 self.exchange_note = "fused peer-memory sum (ggs_view_sum_peer, %s%s)" % (
                     "NVSwitch multimem" if self.exchange.multicast_ptr else "P2P loads/stores",
-                    ", slices reduced in the switch" if pull and self.exchange.multicast_ptr else
-                    (", slices pulled" if pull else ""))
+                    ", slices reduced in the switch" if self.exchange.pull_reduce and self.exchange.multicast_ptr else
+                    (", slices pulled" if self.exchange.pull_reduce else ""))
             except Exception as ex:  # noqa: BLE001
                 print(f"[bench] peer exchange unavailable ({type(ex).__name__}: {ex}); using NCCL", file=sys.stderr)
                 self.exchange = None
@@ -632,6 +632,19 @@ def run_c5(args, rank, world, local, device, multi):
     value = n * V / (ms_per_step * 1e-3) / 1e6
     ms_e2e, _ = timed(end_to_end, args.steps, args.warmup, n_ranks, None)
     e2e_value = n * V / (ms_e2e / args.steps * 1e-3) / 1e6
+    rounds = None
+    if args.impl == "ours":
+        # later query rounds of the same extraction (the binary search on the level set): the views stay prepared
+        prepared = parallel.prepare_views(settings, *x)
+
+        def later_round():
+            return parallel.alpha_cull(points, settings, *x, prepared=prepared)
+
+        ms_r, _ = timed(later_round, args.steps, args.warmup, n_ranks, None)
+        rounds = {"value": n * V / (ms_r / args.steps * 1e-3) / 1e6, "unit": "Mqueries/s", "ms_per_step": ms_r / args.steps,
+                  "what": "a later query round of the same extraction: the views' Gaussians stay binned "
+                          "(parallel.prepare_views), only the points are binned and queried"}
+        del prepared
     if rank != 0:
         return 0
     chunks = len(torch.chunk(points[lo:hi], (hi - lo) // 10_000_000 + 1))
@@ -648,6 +661,8 @@ def run_c5(args, rank, world, local, device, multi):
                 "d2h_bytes_per_step": (hi - lo) * 5},
         "clocks": clocks,
     }
+    if rounds is not None:
+        line["later_rounds"] = rounds
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = 0

@@ -101,7 +101,7 @@ class PeerGradientExchange:
          gradients; node barrier.
     Wire bytes received per rank and step: 12 B x P x (world - 1) colour gradients + 2 x 44 B x P x (world - 1) / world."""
 
-    def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool = False,
+    def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool | None = None,
                  zero_copy: bool = False):
         """`zero_copy=False` (default): the summed gradients are cloned out of the exchange buffers (236 B per
         Gaussian at SH3), so they may be kept, accumulated into, or outlive the next backward like any gradient.
@@ -141,6 +141,11 @@ class PeerGradientExchange:
         if multicast and not mc:
             raise RuntimeError("no NVSwitch multicast mapping for the exchange buffer")
         self.multicast_ptr = mc
+        # slices summed inside the switch (multimem.ld_reduce) where the buffer has a multicast mapping: no slice push,
+        # bit-identical to the NCCL sums at 2 and 8 ranks (profiles/r02_peer_check_n8_c3.log); posted stores otherwise
+        if pull_reduce is None:
+            pull_reduce = bool(mc)
+        self.pull_reduce = bool(pull_reduce)
         self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
                                        L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
                                        L["reduce_stage"], L["reduce_stride"], int(bool(pull_reduce)))
@@ -290,9 +295,24 @@ def integrate_sharded(integrate: Callable[[torch.Tensor], tuple[torch.Tensor, to
     return out_a, out_i
 
 
+def prepare_views(views: Sequence, means3D, opacities, scales, rotations, prepare: Callable | None = None) -> list:
+    """Bins the Gaussians of every view once (`GaussianRasterizer.prepare`) for any number of `alpha_cull` rounds over
+    the same model: the tetrahedral extraction evaluates its vertices, then refines the level set with a binary search
+    -- every round queries the same views (mesh_extract_tetrahedra.py).  About 0.3 KB per (view, Gaussian) + 24 B per
+    (tile, Gaussian) pair of device memory stay allocated per view."""
+    if prepare is None:
+        from . import GaussianRasterizer
+
+        def prepare(rs):
+            return GaussianRasterizer(rs).prepare(means3D, opacities, scales, rotations)
+
+    return [prepare(rs) for rs in views]
+
+
 def alpha_cull(points3D: torch.Tensor, views: Sequence, means3D, opacities, scales, rotations, *,
                chunk_size: int = 10_000_000, validate: Callable | None = None, group=None,
-               gather: bool = True, prepare: Callable | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+               gather: bool = True, prepare: Callable | None = None,
+               prepared: Sequence | None = None) -> tuple[torch.Tensor, torch.Tensor]:
     """The opacity test of the tetrahedral mesh extraction over all views (`evaluage_alpha_cull`,
     mesh_extract_tetrahedra.py:65-87): per point the minimum over the views that see it of the integrated opacity.
     Returns `(sdf = 0.5 - min_alpha  [N], any_valid [N] bool)`.
@@ -308,7 +328,10 @@ def alpha_cull(points3D: torch.Tensor, views: Sequence, means3D, opacities, scal
         independent: no data-path collective) and the two result arrays are all-gathered at the end, 5 bytes per
         point (`gather=False` returns the rank's own range instead).
     `prepare(settings) -> object with .integrate(points)` replaces `GaussianRasterizer(settings).prepare(...)` (tests of
-    the sharding logic on CPU tensors)."""
+    the sharding logic on CPU tensors).  `prepared` (from `prepare_views`): the views' binned Gaussians from an earlier
+    round over the same model; nothing is binned again."""
+    if prepared is not None and len(prepared) != len(views):
+        raise ValueError("`prepared` must hold one prepared view per entry of `views`")
     if prepare is None:
         from . import GaussianRasterizer
 
@@ -326,7 +349,7 @@ def alpha_cull(points3D: torch.Tensor, views: Sequence, means3D, opacities, scal
     any_valid = torch.zeros(m, dtype=torch.bool, device=device)
     chunks = [(a, min(a + chunk_size, m)) for a in range(0, m, chunk_size)]
     for vi, rs in enumerate(views):
-        view = prepare(rs)
+        view = prepared[vi] if prepared is not None else prepare(rs)
         for a, b in chunks:
             pts = mine[a:b]
             alpha, inside = view.integrate(pts)

@@ -12,7 +12,8 @@ from typing import NamedTuple
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libggs_patch_ncc.so")
+# GGS_PATCH_NCC_LIB: a differently built copy of the same library (A/B timing of kernel variants); no fallback either way
+LIB_PATH = os.environ.get("GGS_PATCH_NCC_LIB") or os.path.join(_HERE, "libggs_patch_ncc.so")
 EXPORTS = ("ggs_ncc_abi_version", "ggs_ncc_last_error", "ggs_ncc_warp_patch")
 ABI_VERSION = 1
 

@@ -256,3 +256,31 @@ def test_result_lease_detects_aliasing_gradients():
     del holder
     gc.collect()
     lease.check()
+
+
+def test_alpha_cull_with_prepared_views_matches():
+    """parallel.prepare_views: later rounds reuse the prepared views; same result as preparing inside the call."""
+    import torch
+
+    from diff_gaussian_rasterization import parallel
+
+    torch.manual_seed(3)
+    pts = torch.rand(1000, 3)
+    views = [0.3, 0.5, 0.9]
+    made = []
+
+    class View:
+        def __init__(self, thr):
+            self.thr = thr
+            made.append(thr)
+
+        def integrate(self, p):
+            return (p[:, 0] * self.thr).float(), p[:, 1] < self.thr
+
+    a = parallel.alpha_cull(pts, views, None, None, None, None, prepare=View, chunk_size=300)
+    assert made == views
+    prepared = parallel.prepare_views(views, None, None, None, None, prepare=View)
+    n_made = len(made)
+    b = parallel.alpha_cull(pts, views, None, None, None, None, prepare=View, prepared=prepared, chunk_size=170)
+    assert len(made) == n_made, "nothing may be prepared again"
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])

@@ -52,12 +52,17 @@ def _quantiles(d):
     return [float(v) for v in q] + [float(d.max())]
 
 
-# Bounds on (median, 99 %, 99.9 %) of the differences.  Calibrated on the CPU: the kernel's routine compiled with
-# multiply-add contraction against the same routine without it differs by (6e-6, 1.3e-4, 3.1e-4) in the value and by
-# (9e-7, 5e-5, 3.9e-4) of the largest element in the depth derivative, with single patches off by 40 % (variance
-# = sum of squares - square of sum / 49 cancels), so the worst element is reported but not bounded.
-VALUE_BOUNDS = (5e-5, 1e-3, 3e-3)
-GRAD_BOUNDS = (1e-5, 5e-4, 4e-3)
+# Bounds on (median, 99 %, 99.9 %) of the differences = 2 x what was measured on a B200 (profiles/r02_ncc_parity_v0.json,
+# worst of the three scenes; gradients relative to the tensor's largest element).  Against the compiled reference module
+# the outputs are NOT bit-equal (bit_equal false in every scene) although more than half of the patches are (median 0
+# or 2e-7): the two kernels order a few additions differently, and variance = sum of squares - square of sum / 49
+# cancels 5-6 digits, so the tail is heavy (worst element: 1.7e-3 in the value, 1.7e-2 of the largest depth
+# derivative) -- the worst element is reported but not bounded.  The C oracle is IEEE arithmetic against
+# --use_fast_math: wider.  No `valid` flag differed in any scene.
+BOUNDS = {
+    "reference": {"ncc": (5e-7, 2.5e-4, 6e-4), "grad_depths": (1e-7, 8e-5, 5e-4), "grad_normals": (1e-8, 1.5e-7, 7e-7)},
+    "c_oracle": {"ncc": (2e-5, 3.2e-4, 8e-4), "grad_depths": (5e-6, 1.7e-4, 5e-3), "grad_normals": (5e-9, 2e-7, 1.6e-6)},
+}
 
 
 def _compare(got, want, tag, arm, flip_frac):
@@ -76,10 +81,8 @@ def _compare(got, want, tag, arm, flip_frac):
     print(tag, arm, stats)
     assert stats["valid"] > n // 2, "scene does not exercise the kernel"
     assert flips <= max(2, int(flip_frac * n)), stats
-    for got_q, bound in zip(stats["ncc"][:3], VALUE_BOUNDS):
-        assert got_q <= bound, ("ncc", stats)
-    for name in ("grad_depths", "grad_normals"):
-        for got_q, bound in zip(stats[name][:3], GRAD_BOUNDS):
+    for name, bounds in BOUNDS[arm].items():
+        for got_q, bound in zip(stats[name][:3], bounds):
             assert got_q <= bound, (name, stats)
     # invalid patches are exactly zero in every output
     for t in g[:3]:
@@ -95,7 +98,7 @@ def test_patch_ncc_vs_c_oracle(tag, device):
     got = _ours(sc, device)
     torch.cuda.synchronize()
     want = O.warp_patch_ncc(*ncc_scenes.args_of(sc))
-    _compare(got, want, tag, "c_oracle", flip_frac=2e-3)
+    _compare(got, want, tag, "c_oracle", flip_frac=1e-4)
 
 
 @pytest.mark.first_hardware_run(order=4)  # after the self-consistency tests of this file
@@ -112,7 +115,7 @@ def test_patch_ncc_vs_reference(tag, device):
     torch.cuda.synchronize()
     got = _ours(sc, device)
     torch.cuda.synchronize()
-    _compare(got, want, tag, "reference", flip_frac=1e-3)
+    _compare(got, want, tag, "reference", flip_frac=0.0)
 
 
 def test_patch_ncc_autograd_surface(device):
