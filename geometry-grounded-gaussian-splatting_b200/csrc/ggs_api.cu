@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <string>
 
+#include <nvtx3/nvToolsExt.h>  // header-only: the calls are no-ops unless a profiler injects its library
+
 #include "../../include/ggs_rasterizer.h"
 #include "ggs_kernels.cuh"
 
@@ -49,7 +51,18 @@ struct Profiler {
 };
 Profiler g_prof;  // process-wide: autograd runs the backward on its own thread
 
+// NVTX ranges around the enqueue of every stage, driven by the same marks as the event timer:
+// a mark closes the range of the stage that ends there and opens the next one's.
+const char* const kStageAfter[EV_COUNT] = {
+    "ggs:preprocess", "ggs:depth_order", "ggs:scan", "ggs:pair_count+workspace", "ggs:duplicate_keys", "ggs:tile_sort",
+    "ggs:tile_ranges", "ggs:render_forward", nullptr, "ggs:render_backward", "ggs:gaussian_backward", nullptr,
+    "ggs:query_binning", "ggs:query_kernel", nullptr};
+thread_local bool g_nvtx_open = false;
+
 void prof_mark(cudaStream_t s, int which) {
+    if (g_nvtx_open) nvtxRangePop();
+    g_nvtx_open = kStageAfter[which] != nullptr;
+    if (g_nvtx_open) nvtxRangePushA(kStageAfter[which]);
     if (!g_prof.on) return;
     if (!g_prof.created) {
         for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&g_prof.ev[i]);
