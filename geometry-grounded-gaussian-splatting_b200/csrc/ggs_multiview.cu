@@ -21,7 +21,13 @@
 
 namespace ggs {
 
-constexpr int MV_THREADS = 128;
+#ifndef GGS_MV_THREADS
+#define GGS_MV_THREADS 128
+#endif
+#ifndef GGS_MV_MIN_BLOCKS
+#define GGS_MV_MIN_BLOCKS 6  // 80 registers: 102 -> 88 us for 8 views of 1 M Gaussians (tools/sh_sum_bench.py); 8 blocks (64 registers) spill
+#endif
+constexpr int MV_THREADS = GGS_MV_THREADS;
 
 __device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* mc) {
     float4 v;
@@ -82,7 +88,7 @@ __device__ __forceinline__ void reduce_slice(const PeerJob& job, int block, int 
     if (i < job.hi4) store_to_ranks(job, i, sum_over_ranks(job, i));
 }
 
-__global__ void __launch_bounds__(MV_THREADS, 5)
+__global__ void __launch_bounds__(MV_THREADS, GGS_MV_MIN_BLOCKS)
     view_sum_kernel(int P, int SHD, int SHM, int V, const float* __restrict__ means3D, const ViewSources src,
                     float* __restrict__ dL_dsh, const PeerJob job) {
     extern __shared__ float s_slab[];  // [warps][32][RS]
@@ -195,8 +201,37 @@ __global__ void __launch_bounds__(MV_THREADS, 5)
     }
 }
 
+// The slice half on its own (no SH rows in the launch) with a multicast mapping: out[i] = multimem.ld_reduce(send[i]),
+// multimem.st(recv[i]).  One round trip through the switch per 16 bytes, so what counts is bytes in flight: four
+// independent columns per thread and a grid that covers a 5-11 MB slice in one sweep (measured at 8 GPUs with the
+// 128-thread, two-column blocks of view_sum_kernel: 114 us for a 5.5 MB slice, 205 us for 11 MB -- 50 GB/s per rank).
+constexpr int SLICE_THREADS = 256;
+constexpr int SLICE_COLUMNS = 4;
+__global__ void __launch_bounds__(SLICE_THREADS) slice_sum_multimem_kernel(const float4* __restrict__ mc_send,
+                                                                          float4* __restrict__ mc_recv, size_t lo4,
+                                                                          size_t hi4) {
+    const size_t stride = (size_t)gridDim.x * SLICE_THREADS;
+    for (size_t i = lo4 + (size_t)blockIdx.x * SLICE_THREADS + threadIdx.x; i < hi4; i += SLICE_COLUMNS * stride) {
+        float4 v[SLICE_COLUMNS];
+#pragma unroll
+        for (int k = 0; k < SLICE_COLUMNS; k++)
+            if (i + k * stride < hi4) v[k] = multimem_ld_reduce_add(mc_send + i + k * stride);
+#pragma unroll
+        for (int k = 0; k < SLICE_COLUMNS; k++)
+            if (i + k * stride < hi4) multimem_st(mc_recv + i + k * stride, v[k]);
+    }
+}
+
 static void launch_view_sum(int P, int SHD, int SHM, int V, const float* means3D, const ViewSources& src,
                             float* dL_dsh, const PeerJob& job, cudaStream_t stream) {
+    if (P == 0 && job.blocks > 0 && job.mc_send && job.mc_recv && job.hi4 > job.lo4) {
+        const size_t n4 = job.hi4 - job.lo4;
+        const size_t per_block = (size_t)SLICE_THREADS * SLICE_COLUMNS;
+        const size_t want = (n4 + per_block - 1) / per_block;
+        const unsigned blocks = (unsigned)(want < (size_t)(148 * 8) ? want : (size_t)(148 * 8));
+        slice_sum_multimem_kernel<<<blocks, SLICE_THREADS, 0, stream>>>(job.mc_send, job.mc_recv, job.lo4, job.hi4);
+        return;
+    }
     // output slab [warps][32][RS] + colour stage [warps][V][96]; RS = 3 SHM | 1 keeps the slab a multiple of 16 bytes
     const size_t smem = (size_t)(MV_THREADS / 32) * (32 * ((SHM * 3) | 1) + (size_t)V * 96) * sizeof(float);
     static SmemOptIn opted;
