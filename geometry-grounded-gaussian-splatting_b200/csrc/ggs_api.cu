@@ -389,6 +389,17 @@ int check_exchange(const GgsPeerExchange* px) {
     for (int r = 0; r < px->world; r++)
         if (!px->peer_buffers[r] || (px->peer_buffers[r] & 15))
             return fail(GGS_ERR_INVALID_ARGUMENT, "bad peer buffer");
+    if (px->chunks > 1) {
+        if (px->chunks > GGS_MAX_CHUNKS || !px->pull_reduce || !px->multicast_base)
+            return fail(GGS_ERR_INVALID_ARGUMENT, "chunked sums need pull_reduce, a multicast mapping and <= 8 chunks");
+        int64_t prev = 0;
+        for (int k = 0; k < px->chunks; k++) {
+            if (!px->chunk_events[k]) return fail(GGS_ERR_INVALID_ARGUMENT, "null chunk event");
+            if (k + 1 < px->chunks && (px->chunk_end[k] <= prev || (px->chunk_end[k] & 127)))
+                return fail(GGS_ERR_INVALID_ARGUMENT, "chunk boundaries must increase in multiples of 128");
+            prev = px->chunk_end[k];
+        }
+    }
     const size_t n4 = (size_t)px->reduce_floats / 4;
     const size_t longest = (n4 + px->world - 1) / px->world;
     if ((size_t)px->reduce_stage_stride / 4 < longest)
@@ -490,7 +501,20 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     gg.dL_dsg_axis = sg ? grads->dL_dsg_axis : nullptr;
     gg.dL_dsg_sharpness = sg ? grads->dL_dsg_sharpness : nullptr;
     gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
-    launch_gaussian_backward(fp, in, bi->radii, at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
+    if (px && px->chunks > 1) {
+        // pieces of the model, an event of the caller behind each: the caller sums piece k over the ranks (node barrier +
+        // ggs_peer_sum_ranges on another stream) while piece k + 1 is computed here
+        int64_t first = 0;
+        for (int k = 0; k < px->chunks; k++) {
+            const int64_t last = k + 1 == px->chunks ? (int64_t)fp.P : std::min<int64_t>(px->chunk_end[k], fp.P);
+            launch_gaussian_backward(fp, in, bi->radii, at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream, first,
+                                     last);
+            GGS_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(px->chunk_events[k]), stream));
+            first = last;
+        }
+    } else {
+        launch_gaussian_backward(fp, in, bi->radii, at<uint8_t>(state->geometry, GL.clamped), acc, gg, stream);
+    }
     GGS_STAGE("gaussian_backward", debug, stream);
     prof_mark(stream, EV_GBWD);
     g_prof.have_bwd = g_prof.on;
@@ -620,6 +644,28 @@ int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const
     launch_view_sum_peer((parts & GGS_VIEW_SUM_SH) ? (int)count : 0, sh_degree, sh_coeffs, means3D, src, dL_dsh, job,
                          stream);
     GGS_STAGE("view_sum_peer", false, stream);
+    return GGS_OK;
+}
+
+int ggs_peer_sum_ranges(const GgsPeerExchange* px, int32_t count, const int64_t* lo4, const int64_t* hi4,
+                        void* stream_) {
+    const int rc = check_exchange(px);
+    if (rc) return rc;
+    if (!px->multicast_base) return fail(GGS_ERR_UNSUPPORTED, "ggs_peer_sum_ranges needs a multicast mapping");
+    if (count < 0 || count > 8 || (count > 0 && (!lo4 || !hi4))) return fail(GGS_ERR_INVALID_ARGUMENT, "bad ranges");
+    SumRanges r = {};
+    r.count = count;
+    const int64_t n4 = px->reduce_floats / 4;
+    for (int k = 0; k < count; k++) {
+        if (lo4[k] < 0 || hi4[k] < lo4[k] || hi4[k] > n4) return fail(GGS_ERR_INVALID_ARGUMENT, "range outside the region");
+        r.lo4[k] = (size_t)lo4[k];
+        r.hi4[k] = (size_t)hi4[k];
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_sum_ranges_multimem(
+        reinterpret_cast<const float4*>(reinterpret_cast<float*>(px->multicast_base) + px->send_offset),
+        reinterpret_cast<float4*>(reinterpret_cast<float*>(px->multicast_base) + px->recv_offset), r, stream);
+    GGS_STAGE("peer_sum_ranges", false, stream);
     return GGS_OK;
 }
 

@@ -40,9 +40,10 @@ constexpr int GB_THREADS = 128;
 __global__ void __launch_bounds__(GB_THREADS)
     gaussian_backward_kernel(const FrameParams fp, const GaussianInputs in, const int* __restrict__ radii,
                              const uint8_t* __restrict__ clamped, const double* __restrict__ grad_acc,
-                             const GaussianGrads g) {
+                             const GaussianGrads g, const uint32_t first_block) {
     extern __shared__ float s_slab[];  // [warps][32][RS]
-    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t block = (size_t)blockIdx.x + first_block;  // a launch may cover a piece of the model (ggs_api.cu)
+    const size_t idx = block * blockDim.x + threadIdx.x;
     const int SHM = fp.SHM, SGM = fp.SGM;
     const bool has_sh = in.shs != nullptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(GB_THREADS)
     const int RS = F | 1;    // odd row stride: conflict-free when every lane walks its own row
     float* const swarp = s_slab + (size_t)warp * 32 * RS;
     float* const srow = swarp + lane * RS;
-    const size_t g0 = (size_t)blockIdx.x * blockDim.x + warp * 32;  // first Gaussian of the warp
+    const size_t g0 = block * blockDim.x + warp * 32;  // first Gaussian of the warp
     const int ng = g0 < (size_t)fp.P ? (int)min((size_t)32, (size_t)fp.P - g0) : 0;
     const uint32_t vm = __ballot_sync(0xffffffffu, vis);
     const bool vec4 = (F & 3) == 0;
@@ -529,13 +530,16 @@ __global__ void __launch_bounds__(GB_THREADS)
 
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
                               const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
-                              cudaStream_t stream) {
-    if (fp.P == 0) return;
+                              cudaStream_t stream, int64_t first, int64_t last) {
+    if (last < 0 || last > fp.P) last = fp.P;
+    if (fp.P == 0 || first >= last) return;
     const size_t smem = (size_t)(GB_THREADS / 32) * 32 * ((fp.SHM * 3) | 1) * sizeof(float);
     static SmemOptIn opted;
     opt_in_shared_memory(gaussian_backward_kernel, smem, opted);
-    gaussian_backward_kernel<<<(fp.P + GB_THREADS - 1) / GB_THREADS, GB_THREADS, smem, stream>>>(fp, in, radii, clamped,
-                                                                                               grad_acc, g);
+    // `first` is a multiple of GB_THREADS; a piece that ends inside a block ends the model (the kernel checks fp.P)
+    const uint32_t first_block = (uint32_t)(first / GB_THREADS);
+    const uint32_t blocks = (uint32_t)((last - first + GB_THREADS - 1) / GB_THREADS);
+    gaussian_backward_kernel<<<blocks, GB_THREADS, smem, stream>>>(fp, in, radii, clamped, grad_acc, g, first_block);
 }
 
 }  // namespace ggs

@@ -138,9 +138,10 @@ struct GaussianGrads {
     float* dL_dsg_color;      // [P,SGM,3] or null
     float* dL_drgb;           // [P,3] or null: dL/d(colour) after the clamp mask (the factor of the SH gradient)
 };
+// [first, last): the Gaussians of this launch (first a multiple of 128; the whole model by default)
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,
                               const uint8_t* clamped, const double* grad_acc, const GaussianGrads& g,
-                              cudaStream_t stream);
+                              cudaStream_t stream, int64_t first = 0, int64_t last = -1);
 
 // ---- point queries (integrate / sample_depth / evaluate_sdf), ggs_query.cu -------------------------------------
 // Queries are sorted by (tile, Morton code of the quarter-pixel cell inside the tile); a CTA owns QUERY_CTA consecutive
@@ -204,6 +205,12 @@ struct PeerJob {
 };
 void launch_view_sum_peer(int P, int SHD, int SHM, const float* means3D, const ViewSources& src, float* dL_dsh,
                           const PeerJob& job, cudaStream_t stream);
+// recv[i] = multimem.ld_reduce(send[i]) for the 16-byte units of up to 8 ranges, stored with multimem.st
+struct SumRanges {
+    int count;
+    size_t lo4[8], hi4[8];
+};
+void launch_sum_ranges_multimem(const float4* mc_send, float4* mc_recv, const SumRanges& r, cudaStream_t stream);
 
 // Push half of the exchange (ggs_peer.cu): every byte crosses the link as a posted store.
 struct PushTargets {  // slot `rank` of every rank's colour stage / camera stage, as this process maps them

@@ -201,37 +201,53 @@ __global__ void __launch_bounds__(MV_THREADS, GGS_MV_MIN_BLOCKS)
     }
 }
 
-// The slice half on its own (no SH rows in the launch) with a multicast mapping: out[i] = multimem.ld_reduce(send[i]),
-// multimem.st(recv[i]).  One round trip through the switch per 16 bytes, so what counts is bytes in flight: four
-// independent columns per thread and a grid that covers a 5-11 MB slice in one sweep (measured at 8 GPUs with the
-// 128-thread, two-column blocks of view_sum_kernel: 114 us for a 5.5 MB slice, 205 us for 11 MB -- 50 GB/s per rank).
-constexpr int SLICE_THREADS = 256;
-constexpr int SLICE_COLUMNS = 4;
-__global__ void __launch_bounds__(SLICE_THREADS) slice_sum_multimem_kernel(const float4* __restrict__ mc_send,
-                                                                          float4* __restrict__ mc_recv, size_t lo4,
-                                                                          size_t hi4) {
-    const size_t stride = (size_t)gridDim.x * SLICE_THREADS;
-    for (size_t i = lo4 + (size_t)blockIdx.x * SLICE_THREADS + threadIdx.x; i < hi4; i += SLICE_COLUMNS * stride) {
-        float4 v[SLICE_COLUMNS];
+// Sum over ranks of up to eight ranges of the gradient region through the switch: out[i] = multimem.ld_reduce(send[i]),
+// multimem.st(recv[i]), 16 bytes per unit.  Used for the pieces of the region a chunk of the per-Gaussian backward has
+// just written (ggs_peer_sum_ranges): the links sum chunk k while the SMs compute chunk k + 1.  The ranges are walked
+// as one concatenated index space, two columns in flight per thread (more in flight did not help: the in-switch
+// reduction sustains ~350 GB/s per GPU whatever the issue pattern -- 5.5 MB per rank in 114 us with this shape, 128 us
+// with four columns and twice the threads).
+constexpr int RANGE_THREADS = 128;
+__global__ void __launch_bounds__(RANGE_THREADS) sum_ranges_multimem_kernel(const float4* __restrict__ mc_send,
+                                                                           float4* __restrict__ mc_recv,
+                                                                           const SumRanges r, const size_t total) {
+    const size_t stride = (size_t)gridDim.x * RANGE_THREADS;
+    auto locate = [&](size_t j) -> size_t {  // unit j of the concatenation -> unit of the region
 #pragma unroll
-        for (int k = 0; k < SLICE_COLUMNS; k++)
-            if (i + k * stride < hi4) v[k] = multimem_ld_reduce_add(mc_send + i + k * stride);
-#pragma unroll
-        for (int k = 0; k < SLICE_COLUMNS; k++)
-            if (i + k * stride < hi4) multimem_st(mc_recv + i + k * stride, v[k]);
+        for (int k = 0; k < 8; k++) {
+            if (k < r.count) {
+                const size_t n = r.hi4[k] - r.lo4[k];
+                if (j < n) return r.lo4[k] + j;
+                j -= n;
+            }
+        }
+        return r.lo4[0];
+    };
+    size_t j = (size_t)blockIdx.x * RANGE_THREADS + threadIdx.x;
+    for (; j + stride < total; j += 2 * stride) {
+        const size_t ia = locate(j), ib = locate(j + stride);
+        const float4 a = multimem_ld_reduce_add(mc_send + ia);
+        const float4 b = multimem_ld_reduce_add(mc_send + ib);
+        multimem_st(mc_recv + ia, a);
+        multimem_st(mc_recv + ib, b);
     }
+    if (j < total) {
+        const size_t ia = locate(j);
+        multimem_st(mc_recv + ia, multimem_ld_reduce_add(mc_send + ia));
+    }
+}
+
+void launch_sum_ranges_multimem(const float4* mc_send, float4* mc_recv, const SumRanges& r, cudaStream_t stream) {
+    size_t total = 0;
+    for (int k = 0; k < r.count; k++) total += r.hi4[k] - r.lo4[k];
+    if (total == 0) return;
+    const size_t want = (total + 2 * RANGE_THREADS - 1) / (2 * RANGE_THREADS);
+    const unsigned blocks = (unsigned)(want < (size_t)(148 * 4) ? want : (size_t)(148 * 4));
+    sum_ranges_multimem_kernel<<<blocks, RANGE_THREADS, 0, stream>>>(mc_send, mc_recv, r, total);
 }
 
 static void launch_view_sum(int P, int SHD, int SHM, int V, const float* means3D, const ViewSources& src,
                             float* dL_dsh, const PeerJob& job, cudaStream_t stream) {
-    if (P == 0 && job.blocks > 0 && job.mc_send && job.mc_recv && job.hi4 > job.lo4) {
-        const size_t n4 = job.hi4 - job.lo4;
-        const size_t per_block = (size_t)SLICE_THREADS * SLICE_COLUMNS;
-        const size_t want = (n4 + per_block - 1) / per_block;
-        const unsigned blocks = (unsigned)(want < (size_t)(148 * 8) ? want : (size_t)(148 * 8));
-        slice_sum_multimem_kernel<<<blocks, SLICE_THREADS, 0, stream>>>(job.mc_send, job.mc_recv, job.lo4, job.hi4);
-        return;
-    }
     // output slab [warps][32][RS] + colour stage [warps][V][96]; RS = 3 SHM | 1 keeps the slab a multiple of 16 bytes
     const size_t smem = (size_t)(MV_THREADS / 32) * (32 * ((SHM * 3) | 1) + (size_t)V * 96) * sizeof(float);
     static SmemOptIn opted;

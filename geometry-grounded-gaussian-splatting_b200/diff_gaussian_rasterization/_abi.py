@@ -76,11 +76,16 @@ class GgsGradients(C.Structure):
                 ("dL_dsg_sharpness", _f32p), ("dL_dsg_color", _f32p), ("dL_drgb", _f32p)]
 
 
+MAX_CHUNKS = 8  # GGS_MAX_CHUNKS
+
+
 class GgsPeerExchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("peer_buffers", C.POINTER(C.c_uint64)),
                 ("multicast_base", C.c_uint64)] + [(n, C.c_int64) for n in (
         "send_offset", "recv_offset", "reduce_floats", "rgb_stage_offset", "rgb_stage_stride",
-        "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")] + [("pull_reduce", C.c_int32)]
+        "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")] + [
+        ("pull_reduce", C.c_int32), ("chunks", C.c_int32), ("chunk_end", C.c_int64 * MAX_CHUNKS),
+        ("chunk_events", C.c_uint64 * MAX_CHUNKS)]
 
 
 class GgsLayout(C.Structure):
@@ -106,7 +111,7 @@ EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_ra
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
            "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_integrate_view_counted", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_count_blend_ops", "ggs_describe_layout", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
-           "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
+           "ggs_peer_sum_ranges", "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
 
 def _load():
@@ -171,6 +176,9 @@ def _load():
                                    C.c_void_p, C.c_void_p]
     lib.ggs_profile_enable.restype = C.c_int
     lib.ggs_profile_enable.argtypes = [C.c_int]
+    lib.ggs_peer_sum_ranges.restype = C.c_int
+    lib.ggs_peer_sum_ranges.argtypes = [C.POINTER(GgsPeerExchange), C.c_int32, C.POINTER(C.c_int64),
+                                        C.POINTER(C.c_int64), C.c_void_p]
     lib.ggs_view_sum_peer.restype = C.c_int
     lib.ggs_view_sum_peer.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(GgsPeerExchange),
                                       C.c_void_p, C.c_int32, C.c_void_p]

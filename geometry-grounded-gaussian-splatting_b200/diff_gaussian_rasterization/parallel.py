@@ -12,6 +12,7 @@ One process per GPU (`torchrun`), `torch.distributed` with the NCCL backend on t
 from __future__ import annotations
 
 import contextlib
+import os
 from typing import Callable, Sequence
 
 import torch
@@ -102,7 +103,7 @@ class PeerGradientExchange:
     Wire bytes received per rank and step: 12 B x P x (world - 1) colour gradients + 2 x 44 B x P x (world - 1) / world."""
 
     def __init__(self, P: int, device, group=None, multicast: bool | None = None, pull_reduce: bool | None = None,
-                 zero_copy: bool = False):
+                 zero_copy: bool = False, chunks: int | None = None):
         """`zero_copy=False` (default): the summed gradients are cloned out of the exchange buffers (236 B per
         Gaussian at SH3), so they may be kept, accumulated into, or outlive the next backward like any gradient.
         `zero_copy=True`: they are views into the buffers, valid until the next backward through this exchange; that
@@ -122,8 +123,9 @@ class PeerGradientExchange:
             raise RuntimeError("at most 16 ranks (one node)")
         self.P, self.device = int(P), torch.device(device)
         self.zero_copy = bool(zero_copy)
+        self.sh_after_backward = os.environ.get("GGS_PEER_SH_LATE", "1") == "1"
         self._lease = ResultLease("PeerGradientExchange(zero_copy=True)")
-        self._args = dict(multicast=multicast, pull_reduce=pull_reduce, zero_copy=zero_copy)
+        self._args = dict(multicast=multicast, pull_reduce=pull_reduce, zero_copy=zero_copy, chunks=chunks)
         L = self.layout = exchange_layout(self.P, self.world)
         self.buf = symm.empty(L["total"], dtype=torch.float32, device=self.device)
         self.buf.zero_()
@@ -149,6 +151,25 @@ class PeerGradientExchange:
         self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
                                        L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
                                        L["reduce_stage"], L["reduce_stride"], int(bool(pull_reduce)))
+        # Pipelining: with the switch-reduced sum the per-Gaussian backward runs in pieces and the links sum piece k
+        # while the SMs compute piece k + 1 (GGS_PEER_CHUNKS).  Default 1 = one piece, summed after the backward: at 8 GPUs two
+        # pieces tie and four lose (C3 2656 / 2648 / 2617 iters/s, C4 6.64x / 6.71x / 6.59x for 1 / 2 / 4 pieces) -- every piece
+        # pays a node barrier of its own and the switch sums 44 MB in ~110 us whatever the pieces
+        if chunks is None:
+            chunks = int(os.environ.get("GGS_PEER_CHUNKS", "1"))
+        self.chunks = max(1, min(int(chunks), _abi.MAX_CHUNKS)) if (self.pull_reduce and mc and self.P >= 128 * 8) else 1
+        self._chunk_events, self._chunk_ranges = [], []
+        if self.chunks > 1:
+            ends, self._chunk_ranges = chunk_ranges(self.P, self.world, self.rank, self.chunks, L)
+            with torch.cuda.device(self.device):
+                for k in range(self.chunks):
+                    ev = torch.cuda.Event()
+                    ev.record()  # creates the underlying cudaEvent_t
+                    self._chunk_events.append(ev)
+                    self.px.chunk_end[k] = ends[k]
+                    self.px.chunk_events[k] = int(ev.cuda_event)
+            self.px.chunks = self.chunks
+            self.sum_stream = torch.cuda.Stream(self.device)
         # the colour push and the SH half of the sum run on this stream, concurrent with the per-Gaussian backward
         self.side = torch.cuda.Stream(self.device)
         self._d_sh = None  # persistent: written on the side stream, so it must not come from the caching allocator
@@ -199,13 +220,33 @@ class PeerGradientExchange:
 
         # side stream, behind the colour push and concurrent with the per-Gaussian backward: once every rank's colour
         # gradients have landed, the SH gradient summed over views (all reads local)
+        backward_done = main.record_event() if self.sh_after_backward else None
         with torch.cuda.stream(self.side):
             self.hdl.barrier(channel=2)
+            if backward_done is not None:
+                # both are HBM-bound: rather than share the memory system with the per-Gaussian backward, the SH sum
+                # runs next to the slice sum, which is bound by the links
+                self.side.wait_event(backward_done)
             launch(2, self.side)  # GGS_VIEW_SUM_SH
             sh_done = self.side.record_event()
-        # main stream, behind the per-Gaussian backward and the slice push
-        self.hdl.barrier(channel=0)  # every rank's slices have landed
-        launch(1, main)  # GGS_VIEW_SUM_SLICE
+        if self.chunks > 1:
+            # the pieces of the per-Gaussian backward are summed as they finish: node barrier (every rank has written
+            # piece k) + this rank's share of piece k through the switch, on a stream of their own
+            with torch.cuda.stream(self.sum_stream):
+                for k in range(self.chunks):
+                    self.sum_stream.wait_event(self._chunk_events[k])
+                    self.hdl.barrier(channel=3)
+                    mine = self._chunk_ranges[k]
+                    lo = (C.c_int64 * len(mine))(*[a for a, _ in mine])
+                    hi = (C.c_int64 * len(mine))(*[b for _, b in mine])
+                    _abi.check(_abi.lib.ggs_peer_sum_ranges(C.byref(self.px), len(mine), lo, hi,
+                                                            C.c_void_p(self.sum_stream.cuda_stream)),
+                               "ggs_peer_sum_ranges")
+                main.wait_event(self.sum_stream.record_event())
+        else:
+            # main stream, behind the per-Gaussian backward and the slice push
+            self.hdl.barrier(channel=0)  # every rank's slices have landed
+            launch(1, main)  # GGS_VIEW_SUM_SLICE
         main.wait_event(sh_done)
         self.hdl.barrier(channel=1)  # result regions complete everywhere; every stage may be overwritten
         r = self.layout["recv"]
@@ -216,6 +257,32 @@ class PeerGradientExchange:
         if self.zero_copy:
             return self._lease.hand_out(out)
         return tuple(t.clone() for t in out)
+
+
+def chunk_ranges(P: int, world: int, rank: int, chunks: int, layout: dict) -> tuple[list, list]:
+    """Pipelined sum (GgsPeerExchange.chunks): the per-Gaussian backward runs in `chunks` pieces of the model; piece k =
+    Gaussians [ends[k-1], ends[k]), every boundary but the last a multiple of 128.  Returns (ends, ranges) where
+    ranges[k] = this rank's share of the 16-byte units of the gradient region that piece k writes -- per parameter array
+    one contiguous run split evenly over the ranks -- as [(lo4, hi4), ...] in units of 4 floats from the region's base.
+    Over the ranks and pieces every unit of the (padded) arrays is covered exactly once."""
+    blocks = (int(P) + 127) // 128
+    ends = [min(int(P), (blocks * (k + 1) // chunks) * 128) for k in range(chunks)]
+    ends[-1] = int(P)
+    ranges, first = [], 0
+    for k, last in enumerate(ends):
+        mine = []
+        for name in ("rotations", "means3D", "scales", "opacities"):
+            o, w = layout[name]
+            lo = (o + w * first) // 4  # first is a multiple of 128 and o of 64: exact
+            # the last piece runs to the end of the array's padded extent (the pad is zero on every rank)
+            hi = (o + w * last + 3) // 4 if k + 1 < chunks else (o + (w * int(P) + 63) // 64 * 64) // 4
+            n = hi - lo
+            a, b = lo + n * rank // world, lo + n * (rank + 1) // world
+            if b > a:
+                mine.append((a, b))
+        ranges.append(mine)
+        first = last
+    return ends, ranges
 
 
 def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:

@@ -297,6 +297,7 @@ GGS_API int ggs_mark_visible(const float* means3D, int64_t count, const float* v
  * every rank's recv region and writes dL_dsh = sum over ranks of the rank-one SH gradients (as
  * ggs_sh_gradient_from_views) -- all reads local; after a second barrier the recv region holds the gradients summed
  * over all views.  The reference has no counterpart (no distributed code). */
+#define GGS_MAX_CHUNKS 8
 typedef struct GgsPeerExchange {
     int32_t world, rank;
     const uint64_t* peer_buffers; /* [world], host array */
@@ -309,6 +310,15 @@ typedef struct GgsPeerExchange {
      * 1: no slice push; the owner of a slice sums it straight out of every rank's send region -- one
      *    multimem.ld_reduce per 16 bytes when multicast_base is set (the switch adds), peer loads otherwise. */
     int32_t pull_reduce;
+    /* Pipelining of the sum with the per-Gaussian backward (pull_reduce with a multicast mapping only; 0 or 1: off).
+     * ggs_rasterize_backward_peer launches the per-Gaussian backward in `chunks` pieces -- chunk k = Gaussians
+     * [chunk_end[k-1], chunk_end[k]), every boundary but the last a multiple of 128 -- and records
+     * chunk_events[k] (a cudaEvent_t of the caller) on `stream` behind piece k.  The caller, on another stream, waits
+     * for event k, holds a node barrier and calls ggs_peer_sum_ranges on the part of the gradient region chunk k wrote:
+     * the links sum chunk k while the SMs compute chunk k + 1. */
+    int32_t chunks;
+    int64_t chunk_end[GGS_MAX_CHUNKS];
+    uint64_t chunk_events[GGS_MAX_CHUNKS];
 } GgsPeerExchange;
 /* side_stream (may be NULL: the library then uses a stream of its own): the stream the colour push is enqueued on.
  * A caller that passes one can chain, on that stream, a barrier and ggs_view_sum_peer(GGS_VIEW_SUM_SH) behind the
@@ -322,6 +332,12 @@ GGS_API int ggs_rasterize_backward_peer(const GgsFrame* frame, const GgsGaussian
                                 void* side_stream);
 GGS_API int ggs_view_sum_peer(int64_t count, int32_t sh_degree, int32_t sh_coeffs, const float* means3D,
                       const GgsPeerExchange* exchange, float* dL_dsh, int32_t parts, void* stream);
+/* recv[i] = sum over ranks of send[i] for every 16-byte unit i of the `count` (<= 8) ranges [lo4[j], hi4[j]) of the
+ * gradient region (units of 4 floats from send_offset / recv_offset), stored into every rank's recv region: one
+ * multimem.ld_reduce + one multimem.st per unit (needs multicast_base).  The ranges a rank passes are ITS share of the
+ * units to sum -- the ranks of the node together cover what they want summed, each unit exactly once. */
+GGS_API int ggs_peer_sum_ranges(const GgsPeerExchange* exchange, int32_t count, const int64_t* lo4, const int64_t* hi4,
+                        void* stream);
 
 /* ---- fused caller-side activations (opt-in, the reference does this in torch) -------------
  * One pass each way over what gaussian_renderer/__init__.py:62-63 obtains from

@@ -284,3 +284,24 @@ def test_alpha_cull_with_prepared_views_matches():
     b = parallel.alpha_cull(pts, views, None, None, None, None, prepare=View, prepared=prepared, chunk_size=170)
     assert len(made) == n_made, "nothing may be prepared again"
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_chunk_ranges_cover_the_region_once():
+    """Pipelined sum of the view-parallel exchange: over ranks and pieces every 16-byte unit of the padded gradient
+    region is summed exactly once, piece boundaries are multiples of 128 Gaussians."""
+    from diff_gaussian_rasterization import parallel
+
+    for P in (1024, 1025, 12800, 99_999):
+        for world in (1, 2, 3, 8):
+            L = parallel.exchange_layout(P, world)
+            for chunks in (1, 2, 4, 8):
+                cover = [0] * (L["reduce"] // 4)
+                for r in range(world):
+                    ends, ranges = parallel.chunk_ranges(P, world, r, chunks, L)
+                    assert ends[-1] == P and ends == sorted(ends) and all(e % 128 == 0 for e in ends[:-1])
+                    assert len(ranges) == chunks and all(len(m) <= 4 for m in ranges)
+                    for mine in ranges:
+                        for a, b in mine:
+                            for i in range(a, b):
+                                cover[i] += 1
+                assert all(c == 1 for c in cover), (P, world, chunks)
