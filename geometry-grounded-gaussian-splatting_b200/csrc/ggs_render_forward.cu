@@ -97,6 +97,10 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     return v;
 }
 constexpr uint32_t REC_STRIDE = REC_QUADS * sizeof(float4);
+#ifndef GGS_CLASSIFY_ITERATIONS
+#define GGS_CLASSIFY_ITERATIONS 2
+#endif
+constexpr int CLASSIFY_ITERATIONS = GGS_CLASSIFY_ITERATIONS;  // bisection iterations that pre-classify a word's entries
 
 // One depth sample of the vacancy-corrected transmittance product (render_forward.cu:603-621).
 __device__ __forceinline__ float sample_factor(float ts, float t_peak, float rsigma, bool ball, float alpha) {
@@ -267,6 +271,7 @@ __global__ void __launch_bounds__(THREADS, 8)
     if constexpr (!GEOMETRY) return;
 
     // ---- passes 2-6: median depth by 8-way bisection ---------------------------------------------------
+    const float rx0 = static_cast<float>(pix0.x), ry0 = static_cast<float>(pix0.y);
     const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
                           (pixf.y - static_cast<float>(H - 1) / 2.f) / rp.focal_y};
     const float rln = rnorm3df(pixnf.x, pixnf.y, 1.f);
@@ -302,6 +307,8 @@ __global__ void __launch_bounds__(THREADS, 8)
         // list positions (1-based) any pixel of this warp still needs: (warp_first, warp_last]
         const uint32_t warp_last = __reduce_max_sync(FULL, in_range ? last_contributor : 0u);
         const uint32_t warp_first = __reduce_min_sync(FULL, pre_pos);
+        // far end of the brackets of the warp's live pixels (depths are >= 0: their bits order like the floats)
+        const float warp_hi = __uint_as_float(__reduce_max_sync(FULL, in_range ? __float_as_uint(depth_hi) : 0u));
         if (lane == 0) {
             s_first[warp] = warp_last ? min(warp_first, warp_last) : NEVER;
             s_last[warp] = warp_last;
@@ -352,6 +359,32 @@ __global__ void __launch_bounds__(THREADS, 8)
                 uint32_t keep = 0;    // positions some pixel of the warp can still need in later iterations
                 uint32_t drop16 = 0;  // positions that leave the backward's list
                 const uint32_t word_addr = buf_addr + w * (32 * REC_STRIDE);
+                if (it < CLASSIFY_ITERATIONS && bits) {
+                    // Most of what pass 1 accepted lies BEHIND the median depth (a pixel blends on until T < 1e-4), far
+                    // behind every bracket of the warp once those are 0.8 or 0.1 wide.  Lane j examines entry j of the
+                    // word: the peak depth is linear in the pixel, so its minimum over the warp's 8x4 rectangle is at
+                    // a corner; if that is more than 6.5 sigma behind the far end of every live bracket the entry is
+                    // quiet behind the bracket for every pixel -- factor exactly 1, now and later -- and is never
+                    // visited (and leaves the backward's list too if even 16 sigma away).  The margins (2 % + 0.1
+                    // sigma here, 6.5 against 6.004 in the rule itself) cover the rounding differences between this
+                    // bound and the per-pixel evaluation for splats at least 4e-6 of the depth thick.
+                    bool behind = false, behind16 = false;
+                    if ((bits >> lane) & 1u) {
+                        const uint32_t rec = word_addr + lane * REC_STRIDE;
+                        const float4 q0 = lds128(rec);
+                        const float4 q1 = lds128(rec + 16);
+                        const float4 q2 = lds128(rec + 32);
+                        const float dx0 = q0.x - rx0, dy0 = q0.y - ry0;  // d = mean - pixel, pixel in [x0, x0+7] x [y0, y0+3]
+                        const float t_min = fminf(q1.z * dx0, q1.z * (dx0 - 7.f)) + fminf(q1.w * dy0, q1.w * (dy0 - 3.f)) + q2.x;
+                        const float rs = q2.y;
+                        const float gap = (t_min - warp_hi) * rs;
+                        const bool thick = rs > 0.f && rs * warp_hi < 2.5e5f;
+                        behind = thick && gap > QUIET_SIGMAS * 1.02f + 0.1f;
+                        behind16 = thick && gap > FAR_SIGMAS * 1.02f + 0.1f && t_min - warp_hi > 2e-5f * warp_hi;
+                    }
+                    bits &= ~__ballot_sync(FULL, behind);
+                    drop16 |= __ballot_sync(FULL, behind16);
+                }
                 WALK_STAT(6, 1);
                 while (bits) {
                     const uint32_t bit = bits & (0u - bits);
