@@ -128,8 +128,6 @@ __global__ void __launch_bounds__(THREADS, 8)
     uint32_t(*const s_mask)[MASK_WORDS] = reinterpret_cast<uint32_t(*)[MASK_WORDS]>(smem_raw + REC_BYTES);
     // (s_near[w] is s_mask[WARPS + w]: one base pointer)
     __shared__ uint32_t s_red[WARPS];
-    __shared__ uint32_t s_first[WARPS];
-    __shared__ uint32_t s_last[WARPS];
 
     const int W = rp.W, H = rp.H;
     const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
@@ -309,56 +307,52 @@ __global__ void __launch_bounds__(THREADS, 8)
         const uint32_t warp_first = __reduce_min_sync(FULL, pre_pos);
         // far end of the brackets of the warp's live pixels (depths are >= 0: their bits order like the floats)
         const float warp_hi = __uint_as_float(__reduce_max_sync(FULL, in_range ? __float_as_uint(depth_hi) : 0u));
-        if (lane == 0) {
-            s_first[warp] = warp_last ? min(warp_first, warp_last) : NEVER;
-            s_last[warp] = warp_last;
-        }
-        __syncthreads();  // also: every warp is done with the staging buffers of the previous iteration
-        uint32_t block_first = NEVER, block_last = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; w++) {
-            block_first = min(block_first, s_first[w]);
-            block_last = max(block_last, s_last[w]);
-        }
-        const int b0 = block_last ? block_first / BATCH : 0;
-        const int b1 = (block_last + BATCH - 1) / BATCH;
         bool pfx = exact_one;  // still extending this pixel's constant prefix
 #ifdef GGS_WALK_STATS
         unsigned int ws[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
-
-        uint32_t id_next = 0;
-        if (b0 < b1) {
-            const uint32_t e = b0 * BATCH + tid;
-            if (e < block_last) stage_record(s_rec, tid, records, __ldg(list + e), 3);
+        // The warp walks ITS list positions on its own: after pass 1 and the thinning of earlier iterations they are a
+        // few dozen out of the tile's hundreds, so only their records are gathered -- lane j copies entry j of a mask
+        // word with cp.async into the warp's private double buffer (a quarter of the staging area pass 1 used; the
+        // block barrier behind pass 1 separates the two uses), the next non-empty word is in flight while this one is
+        // processed, and no block barrier couples the warps of the CTA any more.
+        const uint32_t word_end = (warp_last + 31) / 32;  // words [warp_first / 32, word_end) hold (warp_first, warp_last]
+        auto word_bits = [&](uint32_t gw) -> uint32_t {
+            uint32_t b = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
+            const uint32_t base = gw * 32;
+            if (warp_last - base < 32u) b &= (1u << (warp_last - base)) - 1u;  // nothing lives beyond warp_last
+            if (warp_first > base) b &= FULL << (warp_first - base);           // bits below are folded everywhere
+            return b;
+        };
+        auto next_word = [&](uint32_t gw, uint32_t& b) -> uint32_t {  // first word >= gw with a position to visit
+            b = 0;
+            while (gw < word_end && !(b = word_bits(gw))) gw++;
+            return gw;
+        };
+        auto gather = [&](uint32_t gw, uint32_t b, int slot) {
+            if ((b >> lane) & 1u)
+                stage_record(s_rec + (warp * 2 + slot) * (32 * REC_QUADS), lane, records, __ldg(list + gw * 32 + lane), 3);
             cp_async_commit();
-            if (e + BATCH < block_last) id_next = __ldg(list + e + BATCH);
-        }
-        for (int i = b0; i < b1; i++) {
-            cp_async_wait_all();
-            __syncthreads();
-            const int k = i - b0;
-            if (i + 1 < b1) {
-                const uint32_t e = (i + 1) * BATCH + tid;
-                if (e < block_last) stage_record(s_rec + ((k + 1) & 1) * (BATCH * REC_QUADS), tid, records, id_next, 3);
-                cp_async_commit();
-                if (e + BATCH < block_last) id_next = __ldg(list + e + BATCH);
+        };
+        uint32_t bits = 0;
+        uint32_t gw = warp_last ? next_word(warp_first / 32, bits) : word_end;
+        if (gw < word_end) gather(gw, bits, 0);
+        for (int slot = 0; gw < word_end; slot ^= 1) {
+            uint32_t bits_next = 0;
+            const uint32_t gw_next = next_word(gw + 1, bits_next);
+            if (gw_next < word_end) {
+                gather(gw_next, bits_next, slot ^ 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                cp_async_wait_all();
             }
-            const uint32_t buf_addr = s_rec_addr + (k & 1) * (BATCH * REC_STRIDE);
-            for (int w = 0; w < BATCH / 32; w++) {
-                const uint32_t base = i * BATCH + w * 32;
-                if (base >= warp_last) break;
-                if (base + 32 <= warp_first) continue;
-                const uint32_t gw = i * (BATCH / 32) + w;
-                uint32_t bits = gw < mask_words ? (gw < MASK_WORDS ? s_mask[warp][gw] : FULL) : 0u;
-                // only list positions (1-based: base + jj + 1) in (warp_first, warp_last]: bits below are folded
-                // everywhere, nothing lives beyond
+            __syncwarp();
+            {
+                const uint32_t base = gw * 32;
                 const uint32_t upto = warp_last - base >= 32u ? FULL : (1u << (warp_last - base)) - 1u;
-                bits &= upto;
-                if (warp_first > base) bits &= FULL << (warp_first - base);
+                const uint32_t word_addr = s_rec_addr + (warp * 2 + slot) * (32 * REC_STRIDE);
                 uint32_t keep = 0;    // positions some pixel of the warp can still need in later iterations
                 uint32_t drop16 = 0;  // positions that leave the backward's list
-                const uint32_t word_addr = buf_addr + w * (32 * REC_STRIDE);
                 if (it < CLASSIFY_ITERATIONS && bits) {
                     // Most of what pass 1 accepted lies BEHIND the median depth (a pixel blends on until T < 1e-4), far
                     // behind every bracket of the warp once those are 0.8 or 0.1 wide.  Lane j examines entry j of the
@@ -474,11 +468,15 @@ __global__ void __launch_bounds__(THREADS, 8)
                     }
                 }
                 if (exact_one && lane == 0 && gw < MASK_WORDS && gw < mask_words) {
+                    // (bits below warp_first in this word were skipped, not examined: they are folded everywhere)
                     s_mask[warp][gw] = keep;
                     // the backward's list keeps what was not examined, except positions beyond warp_last
                     s_mask[WARPS + warp][gw] &= ~drop16 & upto;
                 }
             }
+            __syncwarp();  // every lane is done with this slot before the gather after next refills it
+            gw = gw_next;
+            bits = bits_next;
         }
 #ifdef GGS_WALK_STATS
         ws[3] = __reduce_max_sync(FULL, ws[3]);  // constant-path entries (counted by the active lanes only)
