@@ -9,8 +9,10 @@
 // depth profile at the median depth, which is exactly 0 (ex2.approx.ftz underflow) beyond 16 sigma.  The forward's
 // bisection exports the list positions it saw within 16 sigma of some pixel's bracket the last time it examined
 // them (near_mask); what is left of those is tested against the median depth itself before any alpha arithmetic.
-// Adding an exact zero changes nothing, so skipping those entries is exact.  Batches are staged with cp.async
-// into a double buffer (ggs_tile.cuh).
+// Adding an exact zero changes nothing, so skipping those entries is exact.  Both passes are driven by the masks and
+// warp-private: lane l fetches mask word l of a group of 32, the non-empty words are visited in order, lane j copies
+// the record of entry j with cp.async into the warp's own double buffer while the previous word is processed -- only
+// the records a warp needs are gathered and no block barrier couples the eight warps of a tile inside a pass.
 // Each (warp, list entry) produces 17 partial sums.  Instead of 17 five-step shuffle trees and 17
 // scalar atomics from one lane (the reference), the warp runs ONE transposing butterfly (20
 // shuffles) that leaves component c on its own lane, and those 17 lanes issue a single predicated
@@ -26,10 +28,9 @@ struct RenderBwdParams {
     const float* bg;  // device [3]
 };
 
-constexpr int BATCH_B = TILE_BATCH;
+
 constexpr int REC_QUADS_B = REC_QUADS;
 constexpr size_t BWD_REC_BYTES = (size_t)2 * STAGE_QUADS * sizeof(float4);
-constexpr size_t BWD_ID_BYTES = (size_t)2 * BATCH_B * sizeof(uint32_t);
 constexpr uint32_t FULL_B = 0xffffffffu;
 
 // Butterfly reduce-scatter of 17 values (v[17] must be 0).  Returns the warp-wide sum of component
@@ -104,9 +105,6 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                            const float* __restrict__ dL_dpixel_normals, double* __restrict__ grad_acc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* const s_rec = reinterpret_cast<float4*>(smem_raw);                     // [2][STAGE_QUADS]
-    uint32_t* const s_id = reinterpret_cast<uint32_t*>(smem_raw + BWD_REC_BYTES);  // [2][BATCH_B]
-    __shared__ uint32_t s_first[TILE_WARPS];
-    __shared__ uint32_t s_last[TILE_WARPS];
 
     const int W = rp.W, H = rp.H;
     const size_t HW = (size_t)H * W;
@@ -122,7 +120,6 @@ __global__ void __launch_bounds__(TILE_PIXELS)
 
     const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
     const uint2 range = ranges[tile_id];
-    const uint32_t max_contributor = max_contributors[tile_id];
     const uint32_t mask_base = range.x / 32 + tile_id;
     const uint32_t* const list = point_list + range.x;
     const uint32_t mask_words = warp_words[tile_id * (TILE_PIXELS / 32) + warp];
@@ -165,7 +162,6 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     }
 
     float dL_dmt_dT_dtm = 0.f;
-    const int rounds = (max_contributor + BATCH_B - 1) / BATCH_B;
 
     if constexpr (GEOMETRY) {
         // ---- pass A: dT/dt_m at the stored median depth, front to back --------------------------------
@@ -175,50 +171,50 @@ __global__ void __launch_bounds__(TILE_PIXELS)
         // list positions <= nf need no visit: the forward cleared them all in near_mask
         const uint32_t nf = near_first[tile_id * TILE_WARPS + warp];
         const uint32_t* my_near = near_mask + (size_t)mask_base * 8 + warp;
-        if (lane == 0) {
-            s_first[warp] = warp_last_a ? min(nf, warp_last_a) : 0xffffffffu;
-            s_last[warp] = warp_last_a;
-        }
-        __syncthreads();
-        uint32_t block_first = 0xffffffffu, block_last = 0;
-#pragma unroll
-        for (int w = 0; w < TILE_WARPS; w++) {
-            block_first = min(block_first, s_first[w]);
-            block_last = max(block_last, s_last[w]);
-        }
-        const int b0 = block_last ? block_first / BATCH_B : 0;
-        const int b1 = (block_last + BATCH_B - 1) / BATCH_B;
-        uint32_t id_next = 0;
-        if (b0 < b1) {
-            const uint32_t e = b0 * BATCH_B + tid;
-            if (e < block_last) stage_record(s_rec, tid, records, __ldg(list + e), 3);
+        // The warp walks its own list positions (near_mask beyond nf, a few dozen of the tile's hundreds): lane l fetches
+        // mask word wb + l, the non-empty words are visited in order, and for each of them lane j copies the record of
+        // entry j with cp.async into the warp's private double buffer (an eighth of the staging area pass B uses),
+        // the next non-empty word in flight while this one is processed.  No block barrier inside the pass.
+        const uint32_t word_end = min((warp_last_a + 31) / 32, mask_words);
+        float4* const wbuf = s_rec + warp * (2 * 32 * REC_QUADS_B);
+        auto gather = [&](uint32_t gw, uint32_t b, int slot) {
+            if ((b >> lane) & 1u)
+                stage_record(wbuf + slot * (32 * REC_QUADS_B), lane, records, __ldg(list + gw * 32 + lane), 3);
             cp_async_commit();
-            if (e + BATCH_B < block_last) id_next = __ldg(list + e + BATCH_B);
-        }
-        for (int i = b0; i < b1; i++) {
-            cp_async_wait_all();
-            __syncthreads();
-            const int k = i - b0;
-            const float4* const buf = s_rec + (k & 1) * STAGE_QUADS;
-            if (i + 1 < b1) {
-                const uint32_t e = (i + 1) * BATCH_B + tid;
-                if (e < block_last) stage_record(s_rec + ((k + 1) & 1) * STAGE_QUADS, tid, records, id_next, 3);
-                cp_async_commit();
-                if (e + BATCH_B < block_last) id_next = __ldg(list + e + BATCH_B);
+        };
+        for (uint32_t wb = warp_last_a ? nf / 32 : word_end; wb < word_end; wb += 32) {
+            const uint32_t gwl = wb + lane;
+            uint32_t mine = 0;
+            if (gwl < word_end) {
+                mine = __ldg((gwl < MASK_WORDS ? my_near : my_mask) + (size_t)gwl * 8);
+                const uint32_t base = gwl * 32;
+                if (warp_last_a - base < 32u) mine &= (1u << (warp_last_a - base)) - 1u;  // pos <= warp_last_a
+                if (nf > base) mine &= 0xffffffffu << (nf - base);                        // pos > nf
             }
-            for (int w = 0; w < BATCH_B / 32; w++) {
-                const uint32_t base = i * BATCH_B + w * 32;
-                if (base >= warp_last_a) break;
-                if (base + 32 <= nf) continue;
-                const uint32_t gw = i * (BATCH_B / 32) + w;
-                uint32_t bits = gw < mask_words ? __ldg((gw < MASK_WORDS ? my_near : my_mask) + (size_t)gw * 8) : 0u;
+            uint32_t words = __ballot_sync(FULL_B, mine != 0);
+            if (!words) continue;
+            int k = __ffs(words) - 1;
+            words &= words - 1;
+            uint32_t bits = __shfl_sync(FULL_B, mine, k);
+            gather(wb + k, bits, 0);
+            for (int slot = 0; k >= 0; slot ^= 1) {
+                const int k_next = words ? __ffs(words) - 1 : -1;
+                words &= words - 1;
+                const uint32_t bits_next = __shfl_sync(FULL_B, mine, k_next < 0 ? 0 : k_next);
+                if (k_next >= 0) {
+                    gather(wb + k_next, bits_next, slot ^ 1);
+                    asm volatile("cp.async.wait_group 1;" ::: "memory");
+                } else {
+                    cp_async_wait_all();
+                }
+                __syncwarp();
+                const uint32_t base = (wb + k) * 32;
+                const float4* const buf = wbuf + slot * (32 * REC_QUADS_B);
                 while (bits) {
                     const int jj = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const uint32_t pos = base + jj + 1;
-                    if (pos > warp_last_a) break;
-                    if (pos <= nf) continue;
-                    const float4* rec = buf + (w * 32 + jj) * REC_QUADS_B;
+                    const float4* rec = buf + jj * REC_QUADS_B;
                     const float4 q0 = rec[0];
                     const float4 q1 = rec[1];
                     const float4 q2 = rec[2];
@@ -241,6 +237,9 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                         dT_dtm += -0.25f * Gt / (1.f - Gt) * fabsf(t_delta) * rsigma;
                     }
                 }
+                __syncwarp();  // every lane is done with this slot before the gather after next refills it
+                k = k_next;
+                bits = bits_next;
             }
         }
         __syncthreads();  // pass B reuses the staging buffers
@@ -256,42 +255,57 @@ __global__ void __launch_bounds__(TILE_PIXELS)
     const float ddely_dy = 0.5f * H;
     const int my_comp = warp_component(lane);
 
-    // batches are walked back to front; batch i is staged into buffer (rounds - 1 - i) & 1
-    {
-        const uint32_t e = (rounds - 1) * BATCH_B + tid;
-        if (rounds > 0 && e < max_contributor) {
-            const uint32_t id = __ldg(list + e);
-            s_id[tid] = id;
-            stage_record(s_rec, tid, records, id, 4);
+    // The warp walks its own accepted list positions back to front (accept_mask: ~80 of the tile's hundreds), with the
+    // same private gather as pass A: lane l fetches mask word wb + l, the non-empty words are visited from the back,
+    // lane j copies the four quads of entry j's record with cp.async into the warp's double buffer and keeps the
+    // entry's Gaussian index for the atomics; the next word is in flight while this one is processed.
+    const uint32_t word_end_b = min((warp_last + 31) / 32, mask_words);
+    float4* const wbuf_b = s_rec + warp * (2 * 32 * REC_QUADS_B);
+    uint32_t id_slot0 = 0u, id_slot1 = 0u;  // Gaussian index of entry `lane` of the word in slot 0 / 1
+    auto gather_b = [&](uint32_t gw, uint32_t b, int slot) {
+        if ((b >> lane) & 1u) {
+            const uint32_t id = __ldg(list + gw * 32 + lane);
+            if (slot)
+                id_slot1 = id;
+            else
+                id_slot0 = id;
+            stage_record(wbuf_b + slot * (32 * REC_QUADS_B), lane, records, id, 4);
         }
         cp_async_commit();
-    }
-    uint32_t id_prev = 0;
-    if (rounds > 1) id_prev = __ldg(list + (rounds - 2) * BATCH_B + tid);
-    for (int i = rounds - 1; i >= 0; i--) {
-        cp_async_wait_all();
-        __syncthreads();
-        const int k = rounds - 1 - i;
-        const float4* const buf = s_rec + (k & 1) * STAGE_QUADS;
-        const uint32_t* const ids = s_id + (k & 1) * BATCH_B;
-        if (i > 0) {
-            // batch i-1 is full (only the last batch of the list can be partial)
-            s_id[((k + 1) & 1) * BATCH_B + tid] = id_prev;
-            stage_record(s_rec + ((k + 1) & 1) * STAGE_QUADS, tid, records, id_prev, 4);
-            cp_async_commit();
-            if (i > 1) id_prev = __ldg(list + (i - 2) * BATCH_B + tid);
+    };
+    for (int wb = word_end_b ? (int)((word_end_b - 1) / 32 * 32) : -1; wb >= 0; wb -= 32) {
+        const uint32_t gwl = wb + lane;
+        uint32_t mine = 0;
+        if (gwl < word_end_b) {
+            mine = __ldg(my_mask + (size_t)gwl * 8);
+            const uint32_t base = gwl * 32;
+            if (warp_last - base < 32u) mine &= (1u << (warp_last - base)) - 1u;  // idx = base + jj < warp_last
         }
-
-        for (int w = BATCH_B / 32 - 1; w >= 0; w--) {
-            const uint32_t base = i * BATCH_B + w * 32;
-            if (base >= warp_last) continue;
-            const uint32_t gw = i * (BATCH_B / 32) + w;
-            uint32_t bits = gw < mask_words ? __ldg(my_mask + (size_t)gw * 8) : 0u;
+        uint32_t words = __ballot_sync(FULL_B, mine != 0);
+        if (!words) continue;
+        int k = 31 - __clz(words);
+        words ^= 1u << k;
+        uint32_t bits = __shfl_sync(FULL_B, mine, k);
+        gather_b(wb + k, bits, 0);
+        for (int slot = 0; k >= 0; slot ^= 1) {
+            const int k_next = words ? 31 - __clz(words) : -1;
+            if (k_next >= 0) words ^= 1u << k_next;
+            const uint32_t bits_next = __shfl_sync(FULL_B, mine, k_next < 0 ? 0 : k_next);
+            if (k_next >= 0) {
+                gather_b(wb + k_next, bits_next, slot ^ 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                cp_async_wait_all();
+            }
+            __syncwarp();
+            const uint32_t base = (wb + k) * 32;
+            const float4* const buf = wbuf_b + slot * (32 * REC_QUADS_B);
+            const uint32_t ids_mine = slot ? id_slot1 : id_slot0;
             while (bits) {
                 const int jj = 31 - __clz(bits);
                 bits ^= 1u << jj;
                 const uint32_t idx = base + jj;  // 0-based list position == the reference's `contributor`
-                const int j = w * 32 + jj;
+                const int j = jj;
                 const float4* rec = buf + j * REC_QUADS_B;
                 const float4 q0 = rec[0];
                 const float4 q1 = rec[1];
@@ -380,11 +394,15 @@ __global__ void __launch_bounds__(TILE_PIXELS)
                     v[6] = G * dL_dopa;
                 }
                 const float sum = warp_reduce_scatter17(v, lane);
+                const uint32_t id = __shfl_sync(FULL_B, ids_mine, jj);
                 if (my_comp >= 0) {
                     if (GEOMETRY || my_comp < 10)
-                        atomicAdd(grad_acc + (size_t)ids[j] * GRAD_STRIDE + my_comp, static_cast<double>(sum));
+                        atomicAdd(grad_acc + (size_t)id * GRAD_STRIDE + my_comp, static_cast<double>(sum));
                 }
             }
+            __syncwarp();  // every lane is done with this slot before the gather after next refills it
+            k = k_next;
+            bits = bits_next;
         }
     }
 }
@@ -401,7 +419,7 @@ void launch_render_backward(const FrameParams& fp, const uint2* ranges, const ui
     rp.bg = fp.view.bg;
     const dim3 grid(fp.gx, fp.gy, 1);
     const dim3 block(TILE_PIXELS, 1, 1);
-    constexpr size_t SMEM = BWD_REC_BYTES + BWD_ID_BYTES;
+    constexpr size_t SMEM = BWD_REC_BYTES;  // eight warps x two slots x 32 records
     static SmemOptIn opted_geometry, opted_colour;
     opt_in_shared_memory(render_backward_kernel<true>, SMEM, opted_geometry);
     opt_in_shared_memory(render_backward_kernel<false>, SMEM, opted_colour);

@@ -11,7 +11,11 @@ import scenes
 pytestmark = pytest.mark.gpu
 
 
-def test_factored_sh_gradient_single_view_is_bit_identical(device):
+def test_factored_sh_gradient_single_view(device):
+    """One view: the factored path (colour gradient -> ggs_sh_gradient_from_views) against the plain backward.  Every
+    other gradient is the same kernel's output and must be the same bits; the SH gradient comes from two different
+    kernels built with --use_fast_math (the compiler may associate basis * dL/dRGB differently in each), so it is held
+    to a few ulps of the tensor's largest element instead."""
     import diff_gaussian_rasterization as ours
     from diff_gaussian_rasterization import parallel
 
@@ -20,7 +24,11 @@ def test_factored_sh_gradient_single_view_is_bit_identical(device):
     with parallel.factored_sh_gradients():
         _, fact = H.run_module(ours, sc, device)
     for k in H.GRAD_NAMES:
-        assert torch.equal(plain[k], fact[k]), k
+        if k == "shs":
+            err = float((plain[k] - fact[k]).abs().max() / plain[k].abs().max())
+            assert err <= 5e-7, err
+        else:
+            assert torch.equal(plain[k], fact[k]), k
 
 
 @pytest.mark.parametrize("sh_degree", [0, 1, 2, 3])
