@@ -432,7 +432,7 @@ def algorithmic(sc_stats):
         "scan": 8 * P,
         "duplicate": 20 * V + 12 * D,
         "sort": 8 * D + r * 24 * D,
-        "ranges": 8 * D + 8 * Tn,
+        "ranges": 4 * D + 8 * Tn,  # the sorted 32-bit tile keys (the reference reads its 64-bit keys: 8 D)
         "render_forward": 68 * D + 36 * N,
         "render_backward": 68 * D + 56 * N + 136 * V,
         "gaussian_backward": V * (32 + 12 * c + 144) + P * (12 + 12 + 12 + 4 + 12 + 16 + 12 * c),
@@ -893,9 +893,8 @@ def main():
                  "tiles": ((c.W + 15) // 16) * ((c.H + 15) // 16), "npix": npix, "sort_bits": inter["sort_bits"]}
         stats["sort_passes_run"] = sort_passes_run
         # depth pre-sort: histogram read + 4 passes of (8 + 4) B in and out per Gaussian; tile sort: 32-bit keys + values
-        # in and out per pass, the last pass writes the 64-bit keys (and gathers 4 B of depth per pair)
-        stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + (sort_passes_run - 1) * 16 * stats["num_rendered"] \
-            + 24 * stats["num_rendered"]
+        # in and out per pass (the reference's 64-bit keys are not materialised on the hot path)
+        stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + sort_passes_run * 16 * stats["num_rendered"]
         # preprocess, depth pre-sort (histogram, offsets, 4 passes), scan, duplicate (+ tile histograms), tile sort
         # (offsets, passes), ranges, render fwd, render bwd, per-Gaussian bwd
         line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 1 + sort_passes_run + 1 + 1 + 2)

@@ -214,8 +214,9 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
         if (!b) return fail(GGS_ERR_ALLOC, "binning workspace allocation failed");
         *bin = b;
         // The pairs are emitted in depth order, so only the tile bits [32, end_bit) are left to sort (stable), and only
-        // the 32-bit tile halves of the keys move through the passes: two u32[cap] ping-pong arrays inside keys_b; the
-        // last pass writes the reference's 64-bit keys into keys_a.  Sorted values always land in vals_a.
+        // the 32-bit tile halves of the keys move through the passes: two u32[cap] ping-pong arrays inside keys_b.  The
+        // sorted tile keys always land in the first of them and the sorted values in vals_a; the reference's 64-bit keys
+        // (keys_a) are only formed on demand (ggs_materialize_sorted_keys).
         uint32_t* tk_a = at<uint32_t>(b, BL.keys_b);
         uint32_t* tk_b = tk_a + cap;
         uint32_t* v_a = at<uint32_t>(b, BL.vals_a);
@@ -227,12 +228,11 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
                               stream);
         GGS_STAGE("duplicate_keys", debug, stream);
         prof_mark(stream, EV_DUP);
-        launch_tile_sort(tk_a, tk_b, v_a, v_b, (uint32_t)cap, n_dev, tile_bits, at<uint32_t>(geom, GL.depths),
-                         at<uint64_t>(b, BL.keys_a), at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status),
-                         at<uint32_t>(b, BL.counters), stream);
+        launch_tile_sort(tk_a, tk_b, v_a, v_b, (uint32_t)cap, n_dev, tile_bits, nullptr, nullptr,
+                         at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), at<uint32_t>(b, BL.counters), stream);
         GGS_STAGE("radix_sort", debug, stream);
         prof_mark(stream, EV_SORT);
-        launch_tile_ranges(at<uint64_t>(b, BL.keys_a), (uint32_t)cap, n_dev, ranges, tiles, stream);
+        launch_tile_ranges(tk_a, (uint32_t)cap, n_dev, ranges, tiles, stream);  // the sorted tile keys land in tk_a
         GGS_STAGE("tile_ranges", debug, stream);
         prof_mark(stream, EV_RANGES);
         if (counted_yet) break;
@@ -769,6 +769,22 @@ int ggs_count_blend_ops(const GgsFrame* frame, const GgsGaussians* gaussians, co
                            at<SplatRecord>(state->geometry, GL.records),
                            reinterpret_cast<unsigned long long*>(counters), stream);
     GGS_STAGE("count_blend_ops", false, stream);
+    return GGS_OK;
+}
+
+int ggs_materialize_sorted_keys(int64_t P, int32_t width, int32_t height, const GgsForwardState* state, void* stream_) {
+    if (!state || P < 0 || width <= 0 || height <= 0) return fail(GGS_ERR_INVALID_ARGUMENT, "bad arguments");
+    if (state->num_rendered == 0) return GGS_OK;
+    if (!state->geometry || !state->binning) return fail(GGS_ERR_INVALID_ARGUMENT, "forward state is incomplete");
+    const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
+    const int tiles = gx * gy;
+    const GeomLayout GL = geom_layout((size_t)P);
+    const BinLayout BL = bin_layout((size_t)state_capacity(state), sort_passes(32, sort_end_bit(tiles)), tiles);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    launch_emit_keys64(at<uint32_t>(state->binning, BL.keys_b), at<uint32_t>(state->binning, BL.vals_a),
+                       at<uint32_t>(state->geometry, GL.depths), (uint32_t)state->num_rendered,
+                       at<uint64_t>(state->binning, BL.keys_a), stream);
+    GGS_STAGE("materialize_sorted_keys", false, stream);
     return GGS_OK;
 }
 

@@ -235,12 +235,13 @@ void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets
 }
 
 // ------------------------------------------------------------------------------------------------
-// Tile ranges from the sorted keys (rasterizer_impl.cu:142-161); untouched tiles stay (0,0).
+// Tile ranges from the sorted tile keys (rasterizer_impl.cu:142-161); untouched tiles stay (0,0).  The keys are the
+// 32-bit tile halves the sort moved: the reference's 64-bit keys (tile << 32 | depth bits) are not materialised on the
+// hot path -- nothing downstream reads their depth half -- and are formed on demand (emit_keys64_kernel below).
 // ------------------------------------------------------------------------------------------------
-// Four keys per thread (two 16-byte loads + the predecessor): one 8-byte load per thread left the kernel latency-bound
-// at a third of the HBM rate.
-constexpr int RANGE_ITEMS = 4;
-__global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n,
+// Eight keys per thread (two 16-byte loads + the predecessor).
+constexpr int RANGE_ITEMS = 8;
+__global__ void __launch_bounds__(256) tile_ranges_kernel(const uint32_t* __restrict__ keys, uint32_t n,
                                                           const uint32_t* __restrict__ n_dev,
                                                           uint2* __restrict__ ranges) {
     if (n_dev) n = min(n, __ldg(n_dev));  // launched for the capacity, the count lives on the device
@@ -248,17 +249,15 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __rest
     if (base >= n) return;
     uint32_t t[RANGE_ITEMS + 1];
     if (base + RANGE_ITEMS <= n) {
-        const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2*>(keys + base));
-        const ulonglong2 b = __ldg(reinterpret_cast<const ulonglong2*>(keys + base) + 1);
-        t[1] = (uint32_t)(a.x >> 32);
-        t[2] = (uint32_t)(a.y >> 32);
-        t[3] = (uint32_t)(b.x >> 32);
-        t[4] = (uint32_t)(b.y >> 32);
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(keys + base));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(keys + base) + 1);
+        t[1] = a.x; t[2] = a.y; t[3] = a.z; t[4] = a.w;
+        t[5] = b.x; t[6] = b.y; t[7] = b.z; t[8] = b.w;
     } else {
 #pragma unroll
-        for (int i = 0; i < RANGE_ITEMS; i++) t[i + 1] = base + i < n ? (uint32_t)(__ldg(keys + base + i) >> 32) : 0u;
+        for (int i = 0; i < RANGE_ITEMS; i++) t[i + 1] = base + i < n ? __ldg(keys + base + i) : 0u;
     }
-    t[0] = base ? (uint32_t)(__ldg(keys + base - 1) >> 32) : 0u;
+    t[0] = base ? __ldg(keys + base - 1) : 0u;
 #pragma unroll
     for (int i = 0; i < RANGE_ITEMS; i++) {
         const uint32_t idx = base + i;
@@ -274,12 +273,27 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __rest
     }
 }
 
-void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
+void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
                         cudaStream_t stream) {
     cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
     if (n == 0) return;
     const uint32_t per_block = 256 * RANGE_ITEMS;
-    tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_keys, n, n_dev, ranges);
+    tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_tile_keys, n, n_dev, ranges);
+}
+
+// The reference's sorted 64-bit keys, for inspection and the parity tests: (tile << 32) | depth bits of the pair's Gaussian.
+__global__ void __launch_bounds__(256) emit_keys64_kernel(const uint32_t* __restrict__ tile_keys,
+                                                          const uint32_t* __restrict__ vals,
+                                                          const uint32_t* __restrict__ depth_bits, uint32_t n,
+                                                          uint64_t* __restrict__ keys64) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keys64[i] = ((uint64_t)__ldg(tile_keys + i) << 32) | (uint64_t)__ldg(depth_bits + __ldg(vals + i));
+}
+
+void launch_emit_keys64(const uint32_t* tile_keys, const uint32_t* vals, const uint32_t* depth_bits, uint32_t n,
+                        uint64_t* keys64, cudaStream_t stream) {
+    if (n == 0) return;
+    emit_keys64_kernel<<<(n + 255) / 256, 256, 0, stream>>>(tile_keys, vals, depth_bits, n, keys64);
 }
 
 }  // namespace ggs

@@ -72,8 +72,8 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 
 // Stable sort of depth-ordered pairs on their 32-bit tile keys (bits [0, tile_bits)); the histograms are those of
 // launch_duplicate_keys.  Input in (tk_a, vals_a) when tile_sort_passes() is even, in (tk_b, vals_b) when odd; the
-// sorted values land in vals_a and the last pass writes the reference's 64-bit keys (tile << 32 | depth bits of the
-// pair's Gaussian) to keys64_out.
+// sorted keys and values land in (tk_a, vals_a).  With keys64_out the last pass writes the reference's 64-bit keys
+// (tile << 32 | depth bits of the pair's Gaussian) there instead of the 32-bit ones (not used on the hot path).
 // Stable sort of (u32 key, u32 value) pairs on key bits [0, bits).  Returns 0 if the result is in *_a, 1 if in *_b.
 int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
@@ -85,8 +85,11 @@ void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t
                       const uint32_t* n_dev, int tile_bits, const uint32_t* depth_bits, uint64_t* keys64_out,
                       uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream);
 
-void launch_tile_ranges(const uint64_t* sorted_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
+void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
                         cudaStream_t stream);
+// keys64[i] = (tile_keys[i] << 32) | depth_bits[vals[i]]: the reference's sorted keys, on demand (tests, inspection)
+void launch_emit_keys64(const uint32_t* tile_keys, const uint32_t* vals, const uint32_t* depth_bits, uint32_t n,
+                        uint64_t* keys64, cudaStream_t stream);
 
 // ---- stage 3: tile blend --------------------------------------------------------------------
 struct RenderOut {

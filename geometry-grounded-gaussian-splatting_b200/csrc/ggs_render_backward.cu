@@ -93,7 +93,10 @@ __device__ __forceinline__ int warp_component(const int lane) {
 }
 
 template <bool GEOMETRY>
-__global__ void __launch_bounds__(TILE_PIXELS)
+#ifndef GGS_BWD_MIN_BLOCKS
+#define GGS_BWD_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(TILE_PIXELS, GGS_BWD_MIN_BLOCKS)
     render_backward_kernel(const RenderBwdParams rp, const uint2* __restrict__ ranges,
                            const uint32_t* __restrict__ point_list, const SplatRecord* __restrict__ records,
                            const float* __restrict__ alphas, const float* __restrict__ normalmap,

@@ -427,7 +427,7 @@ void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t
         spec.vshift = -1;
         uint32_t* st = status + (size_t)p * tiles * RADIX;
         // tile digits of depth-ordered pairs come in runs: rank with ballots (see onesweep_kernel)
-        if (p + 1 == passes)
+        if (p + 1 == passes && keys64_out)
             onesweep_kernel<false, uint32_t, true><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, spec, hist + p * RADIX, st, counters + p, keys64_out, depth_bits, n_dev);
         else

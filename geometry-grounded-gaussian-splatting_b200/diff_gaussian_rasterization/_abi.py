@@ -109,7 +109,7 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
 EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_rasterize_backward",
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
-           "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_integrate_view_counted", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_count_blend_ops", "ggs_describe_layout", "ggs_sort_scratch_bytes",
+           "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_integrate_view_counted", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_count_blend_ops", "ggs_describe_layout", "ggs_materialize_sorted_keys", "ggs_sort_scratch_bytes",
            "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
            "ggs_peer_sum_ranges", "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
@@ -176,6 +176,8 @@ def _load():
                                    C.c_void_p, C.c_void_p]
     lib.ggs_profile_enable.restype = C.c_int
     lib.ggs_profile_enable.argtypes = [C.c_int]
+    lib.ggs_materialize_sorted_keys.restype = C.c_int
+    lib.ggs_materialize_sorted_keys.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.POINTER(GgsForwardState), C.c_void_p]
     lib.ggs_peer_sum_ranges.restype = C.c_int
     lib.ggs_peer_sum_ranges.argtypes = [C.POINTER(GgsPeerExchange), C.c_int32, C.POINTER(C.c_int64),
                                         C.POINTER(C.c_int64), C.c_void_p]

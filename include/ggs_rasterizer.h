@@ -393,6 +393,13 @@ typedef struct GgsLayout {
                              point_offsets is the inclusive scan of tiles_touched taken in this order */
 } GgsLayout;
 GGS_API int ggs_describe_layout(int64_t P, int32_t width, int32_t height, int64_t num_rendered, GgsLayout* layout);
+/* The forward sorts the (tile, Gaussian) pairs on the 32-bit tile half of the reference's key -- the pairs are emitted
+ * in depth order, so the depth half never has to move -- and nothing downstream reads the 64-bit keys
+ * (rasterizer_impl.cu:406-414: SortPairs, then identifyTileRanges looks at `key >> 32` only).  This writes them,
+ * (tile << 32) | depth bits of the pair's Gaussian in sorted order, into the binning workspace at
+ * GgsLayout.sorted_keys for inspection and for the bit-exactness tests against the reference's point_list_keys. */
+GGS_API int ggs_materialize_sorted_keys(int64_t P, int32_t width, int32_t height, const GgsForwardState* state,
+                                        void* stream);
 
 /* Stand-alone stable radix sort of (u64 key, u32 value) pairs on bits [begin_bit, end_bit) -- the
  * replacement for cub::DeviceRadixSort::SortPairs at rasterizer_impl.cu:406-412.  `scratch` must

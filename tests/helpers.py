@@ -130,6 +130,10 @@ def ours_forward_raw(sc, device, require_depth=True, want_ctx=False, capacity_hi
     torch.cuda.synchronize(device)
     D = int(n)
     assert int(state.num_rendered) == D and int(state.capacity) >= D
+    # the reference's 64-bit keys are not formed on the hot path: write them into the workspace for the comparisons
+    _abi.check(_abi.lib.ggs_materialize_sorted_keys(P, W, H, C.byref(state), _abi.stream_handle(torch.device(device))),
+               "ggs_materialize_sorted_keys")
+    torch.cuda.synchronize(device)
     L = _abi.describe_layout(P, W, H, int(state.capacity))
     geom, binb, img, tile = (arena.buffers[s] for s in (_abi.SLOT_GEOMETRY, _abi.SLOT_BINNING, _abi.SLOT_IMAGE,
                                                        _abi.SLOT_TILE))
