@@ -280,6 +280,14 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
     bool done = !job.valid;
     float T_point = 1.f, T_gaussian = 1.f;
 
+    // rsqrt.approx(1.0): the vacancy factor of a pair whose Gaussian term does not reach 1 - alpha * g (see below)
+    float c1;
+    {
+        const float one = 1.0f;
+        asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(c1) : "f"(one));
+    }
+    const uint32_t s_rec_addr = static_cast<uint32_t>(__cvta_generic_to_shared(s_rec));
+    constexpr uint32_t Q_STRIDE = Q_QUADS * sizeof(float4);
     uint32_t id_next = 0;
     if (tid < n) stage3q(s_rec, tid, records, __ldg(list + tid));
     cp_async_commit();
@@ -287,7 +295,7 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
     for (int i = 0; i < rounds; i++) {
         cp_async_wait_all();
         if (__syncthreads_and(done)) break;
-        const float4* const buf = s_rec + (i & 1) * (Q_BATCH * Q_QUADS);
+        const uint32_t buf_addr = s_rec_addr + (i & 1) * (Q_BATCH * Q_STRIDE);
         if (i + 1 < rounds) {
             const uint32_t e = (i + 1) * Q_BATCH + tid;
             if (e < n) stage3q(s_rec + ((i + 1) & 1) * (Q_BATCH * Q_QUADS), tid, records, id_next);
@@ -299,37 +307,52 @@ __global__ void __launch_bounds__(Q_THREADS, 8)
         for (int w = 0; w * 32 < lim; w++) {
             if (__all_sync(Q_FULL, done)) break;
             const int jl = w * 32 + lane;
+            const uint32_t word_addr = buf_addr + w * (32 * Q_STRIDE);
             bool c = false;
-            if (jl < lim) c = may_touch_box(buf[jl * Q_QUADS], buf[jl * Q_QUADS + 1], box);
+            if (jl < lim) c = may_touch_box(lds128(word_addr + lane * Q_STRIDE), lds128(word_addr + lane * Q_STRIDE + 16), box);
             uint32_t cand = __ballot_sync(Q_FULL, c);
             while (cand) {
                 const int jj = __ffs(cand) - 1;
                 cand &= cand - 1;
-                if (done) continue;
-                if constexpr (COUNT) n_eval++;
-                const float4* rec = buf + (w * 32 + jj) * Q_QUADS;
-                const float4 q0 = rec[0];
-                const float4 q1 = rec[1];
+                // The reference's per-query chain of `continue`s (sample_forward.cu:118-160), predicated: a query takes
+                // part in an entry iff it is not done and passes the power / alpha tests; the entry that would push its
+                // T below 1e-4 ends it without being applied.
+                const uint32_t rec = word_addr + jj * Q_STRIDE;
+                const float4 q0 = lds128(rec);
+                const float4 q1 = lds128(rec + 16);
                 const float2 d = {q0.x - pxy.x, q0.y - pxy.y};
                 const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                if (power > 0.0f) continue;
                 const float alpha = fminf(0.99f, q1.y * expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
+                const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if constexpr (COUNT) n_eval += done ? 0u : 1u;
+                if (!__any_sync(Q_FULL, ok)) continue;
                 const float test_T = T_gaussian * (1.f - alpha);
-                if (test_T < 0.0001f) {
-                    done = true;
-                    continue;
-                }
-                const float2 q2 = *reinterpret_cast<const float2*>(rec + 2);
+                const bool stop = ok && test_T < 0.0001f;
+                done = done || stop;
+                const bool upd = ok && !stop;
+                const float4 q2 = lds128(rec + 32);
                 const float t_peak = q1.z * d.x + q1.w * d.y + q2.x;
                 const float rsigma = q2.y;
                 const float delta = (t_peak - pt) * rsigma;
-                const float g = rsigma > 0 ? expf(-0.5f * delta * delta) : 0.f;
-                const float one_minus_gaussian = 1.f - alpha * g;
-                const float rvacancy = rsqrtf(one_minus_gaussian);
-                T_point *= (pt > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
-                T_gaussian = test_T;
-                if constexpr (COUNT) n_acc++;
+                // From 6.5 sigma on 1 - alpha * exp(-delta^2/2) rounds to exactly 1.0f (ggs_common.cuh), as it does
+                // for a splat without depth extent: the factor is then (1 - alpha | 1) * rsqrt.approx(1) and neither
+                // exp nor rsqrt is issued unless some query of the warp is closer.  A warp's 32 queries are
+                // neighbours in the image, not in depth, but most of a ray's splats are far from any one of them.
+                const bool quiet = !(rsigma > 0) || fabsf(delta) > QUIET_SIGMAS;
+                float factor;
+                if (__any_sync(Q_FULL, upd && !quiet)) {
+                    const float g = rsigma > 0 ? expf(-0.5f * delta * delta) : 0.f;
+                    const float one_minus_gaussian = 1.f - alpha * g;
+                    const float rvacancy = rsqrtf(one_minus_gaussian);
+                    factor = (pt > t_peak ? (1.f - alpha) : one_minus_gaussian) * rvacancy;
+                } else {
+                    factor = (pt > t_peak ? (1.f - alpha) : 1.f) * c1;
+                }
+                if (upd) {
+                    T_point *= factor;
+                    T_gaussian = test_T;
+                    if constexpr (COUNT) n_acc++;
+                }
             }
         }
     }

@@ -89,13 +89,6 @@ __device__ unsigned long long g_walk_stats[SPLIT_ITERATIONS][8];
 #define WALK_STAT(k, v)
 #endif
 
-// Staged records are read through 32-bit shared-memory addresses: one multiply-add per record instead of the 64-bit
-// generic pointer arithmetic the compiler emits for `buf + slot * REC_QUADS`.
-__device__ __forceinline__ float4 lds128(uint32_t addr) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-    return v;
-}
 constexpr uint32_t REC_STRIDE = REC_QUADS * sizeof(float4);
 #ifndef GGS_CLASSIFY_ITERATIONS
 #define GGS_CLASSIFY_ITERATIONS 2

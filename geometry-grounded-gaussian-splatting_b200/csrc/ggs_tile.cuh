@@ -30,4 +30,12 @@ __device__ __forceinline__ void stage_record(float4* buf, int slot, const SplatR
     if (quads > 3) cp_async16(dst + 3, src + 3);
 }
 
+// Staged records are read through 32-bit shared-memory addresses: one multiply-add per record instead of the 64-bit
+// generic pointer arithmetic the compiler emits for `buf + slot * REC_QUADS`.
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
 }  // namespace ggs
