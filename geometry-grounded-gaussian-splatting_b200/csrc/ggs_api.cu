@@ -168,15 +168,15 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
                       at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
                       at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.total) + 1,
-                      at<uint64_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_vals_a), stream);
+                      at<uint32_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_vals_a), stream);
     GGS_STAGE("preprocess", debug, stream);
     prof_mark(stream, EV_PRE);
-    // Depth pre-sort of the P Gaussians (4 passes over 12 B x P) so that the D pairs only need the tile passes.
-    // ORDER_PASSES is even: the order lands back in order_vals_a.
-    launch_radix_sort(at<uint64_t>(geom, GL.order_keys_a), at<uint64_t>(geom, GL.order_keys_b),
-                      at<uint32_t>(geom, GL.order_vals_a), at<uint32_t>(geom, GL.order_vals_b), (uint32_t)fp.P,
-                      plain_sort_plan(0, 32), at<uint32_t>(geom, GL.order_hist), at<uint32_t>(geom, GL.order_status),
-                      GL.order_status_bytes, at<uint32_t>(geom, GL.order_counters), stream);
+    // Depth pre-sort of the P Gaussians (4 passes over 8 B x P: 32-bit keys) so that the D pairs only need the tile
+    // passes.  ORDER_PASSES is even: the order lands back in order_vals_a.
+    launch_radix_sort32(at<uint32_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_keys_b),
+                        at<uint32_t>(geom, GL.order_vals_a), at<uint32_t>(geom, GL.order_vals_b), (uint32_t)fp.P, 32,
+                        at<uint32_t>(geom, GL.order_hist), at<uint32_t>(geom, GL.order_status), GL.order_status_bytes,
+                        at<uint32_t>(geom, GL.order_counters), stream, 3);
     GGS_STAGE("depth_order", debug, stream);
     prof_mark(stream, EV_ORDER);
     const uint32_t* order = at<uint32_t>(geom, GL.order_vals_a);

@@ -119,7 +119,7 @@ struct GeomLayout {
     size_t total;          // u32 D mirror
     // Depth pre-sort of the Gaussians (stable, by the float bits of the depth; culled Gaussians last): the key
     // duplication walks the Gaussians in this order, so that the pair sort only has to order the tile bits.
-    size_t order_keys_a, order_keys_b;  // u64[P]  (depth bits in the low word)
+    size_t order_keys_a, order_keys_b;  // u32[P]  (depth bits; culled Gaussians 0xffffffff)
     size_t order_vals_a, order_vals_b;  // u32[P]  (the sorted order lands in order_vals_a)
     size_t order_hist;                  // u32[MAX_PASSES][RADIX]
     size_t order_status;                // u32[4][sort tiles][RADIX]
@@ -158,8 +158,8 @@ inline GeomLayout geom_layout(size_t P) {
     L.scan_status = take(tiles * 8);
     L.scan_counter = take(256);
     L.total = take(256);
-    L.order_keys_a = take(P * 8);
-    L.order_keys_b = take(P * 8);
+    L.order_keys_a = take(P * 4);
+    L.order_keys_b = take(P * 4);
     L.order_vals_a = take(P * 4);
     L.order_vals_b = take(P * 4);
     L.order_hist = take(MAX_PASSES * RADIX * 4);

@@ -37,7 +37,10 @@ __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
 
 constexpr int GB_THREADS = 128;
 
-__global__ void __launch_bounds__(GB_THREADS)
+#ifndef GGS_GB_MIN_BLOCKS
+#define GGS_GB_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(GB_THREADS, GGS_GB_MIN_BLOCKS)
     gaussian_backward_kernel(const FrameParams fp, const GaussianInputs in, const int* __restrict__ radii,
                              const uint8_t* __restrict__ clamped, const double* __restrict__ grad_acc,
                              const GaussianGrads g, const uint32_t first_block) {

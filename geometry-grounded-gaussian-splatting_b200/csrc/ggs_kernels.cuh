@@ -31,7 +31,7 @@ struct GaussianInputs {
 // (i.e. ~min); zeroed here.  The host uses them to plan the sort (SortPlan).
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       uint32_t* depth_extremes, uint64_t* order_keys, uint32_t* order_vals, cudaStream_t stream);
+                       uint32_t* depth_extremes, uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream);
 
 // order != null: scans in[order[i]] (the tile counts taken in depth order)
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
@@ -77,7 +77,7 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 // Stable sort of (u32 key, u32 value) pairs on key bits [0, bits).  Returns 0 if the result is in *_a, 1 if in *_b.
 int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
-                        cudaStream_t stream);
+                        cudaStream_t stream, int match_passes = 1);
 int tile_sort_passes(int tile_bits);
 // n_dev (may be null): the pair count in device memory; the launch is then sized for n = the capacity and the kernels
 // clamp to min(n, *n_dev).

@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
                                                                  uint2* __restrict__ rects, uint8_t* __restrict__ clamped,
                                                                  int* __restrict__ radii,
                                                                  uint32_t* __restrict__ depth_extremes,
-                                                                 uint64_t* __restrict__ order_keys,
+                                                                 uint32_t* __restrict__ order_keys,
                                                                  uint32_t* __restrict__ order_vals) {
     extern __shared__ float s_slab[];  // [warps][32][RS] SH rows (only when colours come from SH)
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
     }
     if (in_range) {
         // input of the depth pre-sort: culled Gaussians take the largest key and land behind every visible one
-        order_keys[idx] = vis ? (uint64_t)__float_as_uint(pr.tc) : 0xffffffffull;
+        order_keys[idx] = vis ? __float_as_uint(pr.tc) : 0xffffffffu;
         order_vals[idx] = (uint32_t)idx;
     }
     {
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
 
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       uint32_t* depth_extremes, uint64_t* order_keys, uint32_t* order_vals, cudaStream_t stream) {
+                       uint32_t* depth_extremes, uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream) {
     cudaMemsetAsync(depth_extremes, 0, 8, stream);
     if (fp.P == 0) return;
     const int threads = PRE_THREADS;

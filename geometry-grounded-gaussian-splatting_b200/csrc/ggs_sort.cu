@@ -361,7 +361,7 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 // the depth pre-sort of the Gaussians.  8-byte pairs instead of 12: a pass moves a third less.
 int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, int match_passes) {
     if (n == 0 || bits <= 0) return 0;
     const int passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
     PassSpecs specs;
@@ -383,9 +383,10 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; p++) {
-        // low digit: fine-grained and mixed (match.any is cheap there); higher digits come in runs when the input is
-        // spatially coherent: ballots (see onesweep_kernel)
-        if (p == 0)
+        // digits whose values are mixed across a warp rank with match.any (cheap there): the low digit of spatially
+        // coherent keys, the three mantissa digits of depth keys; digits that come in runs rank with ballots (see
+        // onesweep_kernel)
+        if (p < match_passes)
             onesweep_kernel<true, uint32_t, false><<<tiles, SORT_THREADS, 0, stream>>>(
                 kin, kout, vin, vout, n, specs.d[p], hist + p * RADIX, status + (size_t)p * tiles * RADIX, counters + p,
                 nullptr, nullptr, nullptr);
