@@ -182,10 +182,13 @@ def dist_env():
     return rank, world, local
 
 
+SCALE_MULT = 1.0  # --scale-mult: every Gaussian's scales times this (longer tile lists, larger splats)
+
+
 def make_view(workload, rank, world):
     """View `rank` of a `world`-view batch; the Gaussians are identical on every rank."""
     n_views = max(world, 1)
-    return scenes.make_scene(workload, view=rank, n_views=n_views if n_views > 1 else 1)
+    return scenes.make_scene(workload, view=rank, n_views=n_views if n_views > 1 else 1, scale_mult=SCALE_MULT)
 
 
 class Step:
@@ -749,7 +752,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--c5-gaussians", type=int, default=1_000_000)
     ap.add_argument("--c5-views", type=int, default=8)
+    ap.add_argument("--scale-mult", type=float, default=1.0,
+                    help="multiply every Gaussian's scales (scene-statistics sweeps; the headline is 1.0)")
     args = ap.parse_args()
+    global SCALE_MULT
+    SCALE_MULT = args.scale_mult
     args.warmup = max(args.warmup, 3)
 
     rank, world, local = dist_env()
@@ -862,7 +869,8 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "mpix_per_s": value * npix / 1e6,
         "config": {"workload": f"{args.workload}: {sc.P} Gaussians, {c.W}x{c.H}, SH{sc.sh_degree}, "
-                               "require_depth=True, one view per rank",
+                               "require_depth=True, one view per rank" +
+                               (f", scales x{args.scale_mult:g}" if args.scale_mult != 1.0 else ""),
                    "views_per_step": n_ranks,
                    "parallelism": (f"view-parallel x{n_ranks}: one view per rank, parameter gradients summed over views "
                                    f"inside the timed region: {step.exchange_note}") if multi else "single GPU",
