@@ -170,51 +170,104 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
     __syncthreads();
     const uint32_t begin = s_off[0];
     const int last = min(DUP_THREADS, P - g0);
-    const uint32_t end = s_off[last];
-    const uint32_t span = end - begin;
-    // whole warps walk the slice together (the histogram votes below need every lane)
-    for (uint32_t ob = (tid & ~31u); ob < span; ob += DUP_THREADS) {
-        const uint32_t o = begin + ob + (tid & 31u);
-        // `capacity`: slots of the key arrays.  It is the exact pair count unless the workspace was sized from a hint
-        // before the count was known; a count beyond it is detected by the host, which bins again (ggs_api.cu)
-        const bool live = o < end && o < capacity;
-        uint32_t tile = 0;
-        if (live) {
-            // largest j in [0,last) with s_off[j] <= o
-            int lo = 0, hi = last;
+    // `capacity`: slots of the key arrays.  It is the exact pair count unless the workspace was sized from a hint
+    // before the count was known; a count beyond it is detected by the host, which bins again (ggs_api.cu)
+    const uint32_t end = min(s_off[last], capacity);
+    // Each thread owns FOUR consecutive slots, aligned to 16 bytes in the output (a warp covers 128 slots, one 512-byte
+    // run per array): one binary search for the first of them, the others are found by walking on -- the slots of
+    // a Gaussian are consecutive, y-major then x, so the tile coordinates advance without a division.  Quads that
+    // straddle the block's slice are written slot by slot (the rest of them belongs to the neighbouring blocks).
+    const uint32_t q_begin = begin / 4, q_end = (end + 3) / 4;  // quads that touch [begin, end)
+    // (the second tile-key array of the ping-pong starts `capacity` words behind the first: not always 16-byte aligned)
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(tile_keys) | reinterpret_cast<uintptr_t>(vals)) & 15) == 0;
+    for (uint32_t qb = (tid & ~31u); q_begin + qb < q_end; qb += DUP_THREADS) {  // whole warps: the votes need every lane
+        const uint32_t o0 = (q_begin + qb + (tid & 31u)) * 4;
+        uint32_t tile[4], val[4];
+        bool live[4];
+        // largest j in [0,last) with s_off[j] <= o, for the first live slot of the quad
+        const uint32_t of = max(o0, begin);
+        int lo = 0;
+        uint32_t tx = 0, ty = 0, minx = 0, maxx = 1, next_off = 0;
+        const bool any_live = of < end && of < o0 + 4;
+        if (any_live) {
+            int hi = last;
 #pragma unroll
-            for (int s = 0; s < 9; s++) {
+            for (int st = 0; st < 9; st++) {
                 const int mid = (lo + hi) >> 1;
                 if (lo + 1 < hi) {
-                    if (s_off[mid] <= o)
+                    if (s_off[mid] <= of)
                         lo = mid;
                     else
                         hi = mid;
                 }
             }
-            const uint32_t local = o - s_off[lo];
+            // Gaussians without slots share their offset with the next one: s_off[j] <= of < s_off[j + 1] holds for
+            // the LAST j with s_off[j] <= of, which the search returns
             const uint2 rc = s_rect[lo];
-            const uint32_t minx = rc.x & 0xffffu, miny = rc.x >> 16;
-            const uint32_t w = (rc.y & 0xffffu) - minx;
-            const uint32_t ty = miny + local / w;
-            const uint32_t tx = minx + local % w;
-            tile = ty * (uint32_t)gx + tx;
-            tile_keys[o] = tile;
-            vals[o] = s_g[lo];
+            minx = rc.x & 0xffffu;
+            maxx = rc.y & 0xffffu;
+            const uint32_t w = maxx - minx;
+            const uint32_t local = of - s_off[lo];
+            const uint32_t row = local / w;
+            ty = (rc.x >> 16) + row;
+            tx = minx + (local - row * w);
+            next_off = s_off[lo + 1];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t o = o0 + k;
+            live[k] = o >= begin && o < end;
+            tile[k] = 0;
+            val[k] = 0;
+            if (live[k]) {
+                if (o >= next_off) {
+                    // on to the next Gaussian that owns slots (those in between own none)
+                    do {
+                        lo++;
+                    } while (s_off[lo + 1] <= o);
+                    const uint2 rc = s_rect[lo];
+                    minx = rc.x & 0xffffu;
+                    maxx = rc.y & 0xffffu;
+                    ty = rc.x >> 16;
+                    tx = minx;
+                    next_off = s_off[lo + 1];
+                }
+                tile[k] = ty * (uint32_t)gx + tx;
+                val[k] = s_g[lo];
+                if (++tx == maxx) {
+                    tx = minx;
+                    ty++;
+                }
+            }
+        }
+        if (live[0] && live[3] && vec_ok) {
+            *reinterpret_cast<uint4*>(tile_keys + o0) = uint4{tile[0], tile[1], tile[2], tile[3]};
+            *reinterpret_cast<uint4*>(vals + o0) = uint4{val[0], val[1], val[2], val[3]};
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (live[k]) {
+                    tile_keys[o0 + k] = tile[k];
+                    vals[o0 + k] = val[k];
+                }
+            }
         }
         // digit histograms: the low digit of neighbouring slots differs (consecutive tiles), the higher ones are
         // mostly warp-uniform -- one add for the warp then, per-lane atomics otherwise
-        if (live) atomicAdd(&s_hist[0][tile & (RADIX - 1)], 1u);
-        for (int p = 1; p < passes; p++) {
-            const uint32_t d = (tile >> (RADIX_BITS * p)) & (RADIX - 1);
-            const uint32_t lives = __ballot_sync(0xffffffffu, live);
-            if (lives == 0) break;
-            const int leader = __ffs(lives) - 1;
-            const uint32_t d0 = __shfl_sync(0xffffffffu, d, leader);
-            if (__all_sync(0xffffffffu, !live || d == d0)) {
-                if ((tid & 31) == leader) atomicAdd(&s_hist[p][d0], (uint32_t)__popc(lives));
-            } else if (live) {
-                atomicAdd(&s_hist[p][d], 1u);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (live[k]) atomicAdd(&s_hist[0][tile[k] & (RADIX - 1)], 1u);
+            for (int p = 1; p < passes; p++) {
+                const uint32_t d = (tile[k] >> (RADIX_BITS * p)) & (RADIX - 1);
+                const uint32_t lives = __ballot_sync(0xffffffffu, live[k]);
+                if (lives == 0) break;
+                const int leader = __ffs(lives) - 1;
+                const uint32_t d0 = __shfl_sync(0xffffffffu, d, leader);
+                if (__all_sync(0xffffffffu, !live[k] || d == d0)) {
+                    if ((tid & 31) == leader) atomicAdd(&s_hist[p][d0], (uint32_t)__popc(lives));
+                } else if (live[k]) {
+                    atomicAdd(&s_hist[p][d], 1u);
+                }
             }
         }
     }
