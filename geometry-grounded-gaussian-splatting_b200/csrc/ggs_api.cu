@@ -465,8 +465,11 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     GGS_STAGE("render_backward", debug, stream);
     prof_mark(stream, EV_RBWD);
 
+    // fuse_rgb_push: the per-Gaussian backward stores dL/dRGB into every rank's colour stage itself (multicast); no
+    // separate pass over the accumulators on a side stream
+    const bool fused_push = px && px->fuse_rgb_push && px->multicast_base && in.shs;
     PushLane* lane = nullptr;
-    if (px) {
+    if (px && !fused_push) {
         // the colour gradient of this view is final here: push it to every rank while the per-Gaussian backward runs
         lane = push_lane();
         if (!lane) return fail(GGS_ERR_CUDA, "could not create the push stream");
@@ -497,10 +500,16 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     gg.dL_drotations = grads->dL_drotations;
     gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
     gg.dL_drgb = in.shs ? grads->dL_drgb : nullptr;
+    gg.mc_rgb = gg.mc_campos = nullptr;
     const bool sg = in.shs && fp.SGM;
     gg.dL_dsg_axis = sg ? grads->dL_dsg_axis : nullptr;
     gg.dL_dsg_sharpness = sg ? grads->dL_dsg_sharpness : nullptr;
     gg.dL_dsg_color = sg ? grads->dL_dsg_color : nullptr;
+    if (fused_push) {
+        float* const mc = reinterpret_cast<float*>(px->multicast_base);
+        gg.mc_rgb = mc + px->rgb_stage_offset + (int64_t)px->rank * px->rgb_stage_stride;
+        gg.mc_campos = mc + px->campos_stage_offset + (int64_t)px->rank * 4;
+    }
     if (px && px->chunks > 1) {
         // pieces of the model, an event of the caller behind each: the caller sums piece k over the ranks (node barrier +
         // ggs_peer_sum_ranges on another stream) while piece k + 1 is computed here
@@ -519,7 +528,7 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     prof_mark(stream, EV_GBWD);
     g_prof.have_bwd = g_prof.on;
     if (px && px->pull_reduce) {
-        GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
+        if (lane) GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
     } else if (px) {
         // reduce-scatter by stores: slice s of this rank's gradient region -> slot `rank` of rank s's reduce stage
         PushSlices ps = {};
@@ -529,7 +538,7 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
             ps.dest[s] = reinterpret_cast<float4*>(
                 peer_ptr(px, s, px->reduce_stage_offset + (int64_t)px->rank * px->reduce_stage_stride));
         launch_push_slices(reinterpret_cast<const float4*>(peer_ptr(px, px->rank, px->send_offset)), ps, stream);
-        GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
+        if (lane) GGS_CUDA(cudaStreamWaitEvent(stream, lane->done, 0));
         GGS_STAGE("peer_push", debug, stream);
     }
     return GGS_OK;
@@ -580,6 +589,7 @@ int ggs_backward_from_accumulators(const GgsFrame* frame, const GgsGaussians* ga
     gg.dL_drotations = grads->dL_drotations;
     gg.dL_dsh = in.shs ? grads->dL_dsh : nullptr;
     gg.dL_drgb = in.shs ? grads->dL_drgb : nullptr;
+    gg.mc_rgb = gg.mc_campos = nullptr;
     const bool sg = in.shs && fp.SGM;
     if (sg && (!grads->dL_dsg_axis || !grads->dL_dsg_sharpness || !grads->dL_dsg_color))
         return fail(GGS_ERR_INVALID_ARGUMENT, "spherical-Gaussian gradient tensors required");

@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(GB_THREADS, GGS_GB_MIN_BLOCKS)
     }
     __syncwarp();
 
+    float3 rgb_push = {0.f, 0.f, 0.f};  // dL/dRGB of this Gaussian after the clamp mask (0 when culled)
     if (!vis) {
         if (idx < (size_t)fp.P) {
             st3(g.dL_dmeans3D, idx, 0.f, 0.f, 0.f);
@@ -435,6 +436,7 @@ __global__ void __launch_bounds__(GB_THREADS, GGS_GB_MIN_BLOCKS)
             }
         }
         if (g.dL_drgb) st3(g.dL_drgb, idx, dL_dRGB.x, dL_dRGB.y, dL_dRGB.z);
+        rgb_push = dL_dRGB;
         // ---- d colour / d SH coefficient: overwrite the row with the gradient (render_backward.cu:76-160) ----
         // (skipped when the caller forms the SH gradient from dL_drgb itself: view-parallel training)
         if (g.dL_dsh) {
@@ -511,6 +513,35 @@ __global__ void __launch_bounds__(GB_THREADS, GGS_GB_MIN_BLOCKS)
     st3(g.dL_dscales, idx, dL_dscale.x, dL_dscale.y, dL_dscale.z);
     reinterpret_cast<float4*>(g.dL_drotations)[idx] = dL_dq;
     }  // vis
+
+    // ---- view-parallel exchange: this view's dL/dRGB straight into slot `rank` of EVERY rank's colour stage ------
+    // (ggs_rasterize_backward_peer with GgsPeerExchange.fuse_rgb_push: the warp's 32 rows are one 384-byte segment,
+    // staged in the slab -- free here, the SH gradient is formed elsewhere in this mode -- and stored as 24 x 16 bytes
+    // through the NVSwitch multicast mapping; the camera position goes with block 0)
+    if (g.mc_rgb) {
+        __syncwarp();  // every lane is done reading its SH row
+        swarp[3 * lane] = rgb_push.x;
+        swarp[3 * lane + 1] = rgb_push.y;
+        swarp[3 * lane + 2] = rgb_push.z;
+        __syncwarp();
+        if (ng == 32) {
+            if (lane < 24) {
+                const float4 v = {swarp[4 * lane], swarp[4 * lane + 1], swarp[4 * lane + 2], swarp[4 * lane + 3]};
+                float4* dst = reinterpret_cast<float4*>(g.mc_rgb) + g0 * 3 / 4 + lane;  // g0 % 32 == 0: aligned
+                asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v.x),
+                             "f"(v.y), "f"(v.z), "f"(v.w)
+                             : "memory");
+            }
+        } else {
+            for (int e = lane; e < ng * 3; e += 32)
+                asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(g.mc_rgb + g0 * 3 + e), "f"(swarp[e])
+                             : "memory");
+        }
+        if (block == 0 && threadIdx.x < 3)
+            asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(g.mc_campos + threadIdx.x),
+                         "f"(fp.view.campos[threadIdx.x])
+                         : "memory");
+    }
 
     // ---- gradient slab of the warp's 32 Gaussians: shared memory -> global, coalesced ---------------
     if (g.dL_dsh) {

@@ -140,6 +140,8 @@ struct GaussianGrads {
     float* dL_dsg_sharpness;  // [P,SGM] or null
     float* dL_dsg_color;      // [P,SGM,3] or null
     float* dL_drgb;           // [P,3] or null: dL/d(colour) after the clamp mask (the factor of the SH gradient)
+    float* mc_rgb;            // or null: NVSwitch multicast address of this view's [P,3] slot in every rank's colour
+    float* mc_campos;         //          stage, and of its camera-position slot (view-parallel exchange, fused push)
 };
 // [first, last): the Gaussians of this launch (first a multiple of 128; the whole model by default)
 void launch_gaussian_backward(const FrameParams& fp, const GaussianInputs& in, const int* radii,

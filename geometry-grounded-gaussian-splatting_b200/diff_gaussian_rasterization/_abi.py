@@ -85,7 +85,7 @@ class GgsPeerExchange(C.Structure):
         "send_offset", "recv_offset", "reduce_floats", "rgb_stage_offset", "rgb_stage_stride",
         "campos_stage_offset", "reduce_stage_offset", "reduce_stage_stride")] + [
         ("pull_reduce", C.c_int32), ("chunks", C.c_int32), ("chunk_end", C.c_int64 * MAX_CHUNKS),
-        ("chunk_events", C.c_uint64 * MAX_CHUNKS)]
+        ("chunk_events", C.c_uint64 * MAX_CHUNKS), ("fuse_rgb_push", C.c_int32)]
 
 
 class GgsLayout(C.Structure):

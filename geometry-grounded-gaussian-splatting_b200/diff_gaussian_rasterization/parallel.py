@@ -124,6 +124,7 @@ class PeerGradientExchange:
         self.P, self.device = int(P), torch.device(device)
         self.zero_copy = bool(zero_copy)
         self.sh_after_backward = os.environ.get("GGS_PEER_SH_LATE", "1") == "1"
+        self._want_fused_push = os.environ.get("GGS_PEER_FUSE_RGB", "1") == "1"
         self._lease = ResultLease("PeerGradientExchange(zero_copy=True)")
         self._args = dict(multicast=multicast, pull_reduce=pull_reduce, zero_copy=zero_copy, chunks=chunks)
         L = self.layout = exchange_layout(self.P, self.world)
@@ -151,6 +152,10 @@ class PeerGradientExchange:
         self.px = _abi.GgsPeerExchange(self.world, self.rank, C.cast(self._ptrs, C.POINTER(C.c_uint64)), mc, L["send"],
                                        L["recv"], L["reduce"], L["rgb_stage"], L["rgb_stride"], L["campos_stage"],
                                        L["reduce_stage"], L["reduce_stride"], int(bool(pull_reduce)))
+        # the per-Gaussian backward pushes the colour gradient itself (no second pass over the accumulators next to
+        # it) where the SH sum waits for that kernel anyway and the switch can replicate the stores
+        self.fused_push = bool(self._want_fused_push and self.sh_after_backward and mc)
+        self.px.fuse_rgb_push = int(self.fused_push)
         # Pipelining: with the switch-reduced sum the per-Gaussian backward runs in pieces and the links sum piece k
         # while the SMs compute piece k + 1 (GGS_PEER_CHUNKS).  Default 1 = one piece, summed after the backward: at 8 GPUs two
         # pieces tie and four lose (C3 2656 / 2648 / 2617 iters/s, C4 6.64x / 6.71x / 6.59x for 1 / 2 / 4 pieces) -- every piece
@@ -222,11 +227,15 @@ class PeerGradientExchange:
         # gradients have landed, the SH gradient summed over views (all reads local)
         backward_done = main.record_event() if self.sh_after_backward else None
         with torch.cuda.stream(self.side):
-            self.hdl.barrier(channel=2)
-            if backward_done is not None:
-                # both are HBM-bound: rather than share the memory system with the per-Gaussian backward, the SH sum
-                # runs next to the slice sum, which is bound by the links
-                self.side.wait_event(backward_done)
+            if self.fused_push:
+                self.side.wait_event(backward_done)  # the backward kernel itself pushed this view's colour gradient
+                self.hdl.barrier(channel=2)          # ... and so did every other rank's
+            else:
+                self.hdl.barrier(channel=2)
+                if backward_done is not None:
+                    # both are HBM-bound: rather than share the memory system with the per-Gaussian backward, the SH
+                    # sum runs next to the slice sum, which is bound by the links
+                    self.side.wait_event(backward_done)
             launch(2, self.side)  # GGS_VIEW_SUM_SH
             sh_done = self.side.record_event()
         if self.chunks > 1:

@@ -319,6 +319,12 @@ typedef struct GgsPeerExchange {
     int32_t chunks;
     int64_t chunk_end[GGS_MAX_CHUNKS];
     uint64_t chunk_events[GGS_MAX_CHUNKS];
+    /* 1 (needs multicast_base): the per-Gaussian backward itself stores this view's dL/dRGB and camera position into
+     * every rank's stage (multimem.st from the kernel that computes them) instead of a separate pass over the gradient
+     * accumulators on the side stream.  The colour gradients are then complete when `stream` has finished the
+     * backward: hold the node barrier and launch ggs_view_sum_peer(GGS_VIEW_SUM_SH) behind it, not behind the side
+     * stream. */
+    int32_t fuse_rgb_push;
 } GgsPeerExchange;
 /* side_stream (may be NULL: the library then uses a stream of its own): the stream the colour push is enqueued on.
  * A caller that passes one can chain, on that stream, a barrier and ggs_view_sum_peer(GGS_VIEW_SUM_SH) behind the
