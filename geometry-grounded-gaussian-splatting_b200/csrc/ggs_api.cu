@@ -868,6 +868,91 @@ int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
 
 }  // extern "C"
 
+// ---- ggs_sort_pairs_static: the stand-alone sort without any allocation ----------------------------------------
+// No counterpart in the reference: for callers that cannot call
+// cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses that forbid it.  The scratch that
+// ggs_sort_pairs takes from its caller lives here in a file-scope device array sized for GGS_SORT_STATIC_MAX_PAIRS
+// pairs over the full 64 key bits; every GPU that loads the library holds it (about 3.7 MiB) until the process exits.
+namespace {
+
+constexpr size_t static_up(size_t x) { return (x + 255) / 256 * 256; }
+constexpr size_t STATIC_SORT_PAIRS = GGS_SORT_STATIC_MAX_PAIRS;
+constexpr size_t STATIC_SORT_TILES = (STATIC_SORT_PAIRS + SORT_TILE - 1) / SORT_TILE;
+// the second buffer of the key / value ping-pong, the digit histograms, the look-back descriptors of every pass, and
+// the tile tickets -- bin_layout's fields without its first buffers (the caller's outputs play that part)
+constexpr size_t STATIC_SORT_KEYS = 0;
+constexpr size_t STATIC_SORT_VALS = STATIC_SORT_KEYS + static_up(STATIC_SORT_PAIRS * 8);
+constexpr size_t STATIC_SORT_HIST = STATIC_SORT_VALS + static_up(STATIC_SORT_PAIRS * 4);
+constexpr size_t STATIC_SORT_STATUS = STATIC_SORT_HIST + static_up((size_t)MAX_PASSES * RADIX * 4);
+constexpr size_t STATIC_SORT_COUNTERS = STATIC_SORT_STATUS + static_up((size_t)MAX_PASSES * STATIC_SORT_TILES * RADIX * 4);
+constexpr size_t STATIC_SORT_BYTES = STATIC_SORT_COUNTERS + static_up((size_t)MAX_PASSES * 4);
+
+static __device__ __align__(256) unsigned char g_static_sort_scratch[STATIC_SORT_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address: the device address is asked for once
+// per device, with that device current, and kept.  Only written under the lock; a device's slot never changes again.
+void* g_static_sort_ptr[MAX_DEVICES] = {};
+volatile int g_static_sort_lock = 0;
+
+int static_sort_scratch(unsigned char** out) {
+    int dev = -1;
+    GGS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return fail(GGS_ERR_INVALID_ARGUMENT, "device index out of range");
+    while (__sync_lock_test_and_set(&g_static_sort_lock, 1)) {
+    }
+    void* p = g_static_sort_ptr[dev];
+    cudaError_t e = cudaSuccess;
+    if (!p) {
+        e = cudaGetSymbolAddress(&p, g_static_sort_scratch);
+        if (e == cudaSuccess) g_static_sort_ptr[dev] = p;
+    }
+    __sync_lock_release(&g_static_sort_lock);
+    if (e != cudaSuccess || !p)
+        return fail(GGS_ERR_CUDA, std::string("cudaGetSymbolAddress(static sort scratch): ") + cudaGetErrorString(e));
+    *out = static_cast<unsigned char*>(p);
+    return GGS_OK;
+}
+
+}  // namespace
+
+extern "C" int ggs_sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                                     uint32_t* vals_out, int64_t n, int32_t begin_bit, int32_t end_bit,
+                                     void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n < 0) return fail(GGS_ERR_INVALID_ARGUMENT, "n out of range");
+    if (n > (int64_t)STATIC_SORT_PAIRS)
+        return fail(GGS_ERR_INVALID_ARGUMENT,
+                    "ggs_sort_pairs_static: n = " + std::to_string(n) + " exceeds GGS_SORT_STATIC_MAX_PAIRS = " +
+                        std::to_string(STATIC_SORT_PAIRS) + " (use ggs_sort_pairs with caller scratch)");
+    if (begin_bit < 0 || end_bit > 64 || end_bit <= begin_bit || sort_passes(begin_bit, end_bit) > MAX_PASSES)
+        return fail(GGS_ERR_INVALID_ARGUMENT, "bad bit range");
+    if (n == 0) return GGS_OK;
+    if (!keys_in || !vals_in || !keys_out || !vals_out) return fail(GGS_ERR_INVALID_ARGUMENT, "null argument");
+    unsigned char* scratch = nullptr;
+    const int rc = static_sort_scratch(&scratch);
+    if (rc) return rc;
+    const int passes = sort_passes(begin_bit, end_bit);
+    const size_t tiles = ((size_t)n + SORT_TILE - 1) / SORT_TILE;
+    const size_t status_bytes = (size_t)passes * tiles * RADIX * 4;  // <= the array's share: n and passes are bounded
+    uint64_t* keys_b = reinterpret_cast<uint64_t*>(scratch + STATIC_SORT_KEYS);
+    uint32_t* vals_b = reinterpret_cast<uint32_t*>(scratch + STATIC_SORT_VALS);
+    GGS_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
+    GGS_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    // the array keeps the last call's contents: launch_radix_sort clears the histograms, the descriptors and the
+    // tickets on `stream` before its first kernel; the ping-pong buffers are fully written before they are read
+    const int where = launch_radix_sort(keys_out, keys_b, vals_out, vals_b, (uint32_t)n,
+                                        plain_sort_plan(begin_bit, end_bit),
+                                        reinterpret_cast<uint32_t*>(scratch + STATIC_SORT_HIST),
+                                        reinterpret_cast<uint32_t*>(scratch + STATIC_SORT_STATUS), status_bytes,
+                                        reinterpret_cast<uint32_t*>(scratch + STATIC_SORT_COUNTERS), stream);
+    if (where) {
+        GGS_CUDA(cudaMemcpyAsync(keys_out, keys_b, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
+        GGS_CUDA(cudaMemcpyAsync(vals_out, vals_b, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    }
+    GGS_STAGE("sort_pairs_static", false, stream);
+    return GGS_OK;
+}
+
 // ---- point queries: integrate / sample_depth / evaluate_sdf ----------------------------------------------------
 // The reference bins the Gaussians of the view inside every call (rasterizer_impl.cu:637-714, :861-936, :1084-1160),
 // i.e. once per (chunk of points, view) in mesh_extract_tetrahedra.py:70-82.  Here that half is its own entry point

@@ -77,6 +77,7 @@ class GgsGradients(C.Structure):
 
 
 MAX_CHUNKS = 8  # GGS_MAX_CHUNKS
+SORT_STATIC_MAX_PAIRS = 1 << 18  # GGS_SORT_STATIC_MAX_PAIRS
 
 
 class GgsPeerExchange(C.Structure):
@@ -110,7 +111,7 @@ EXPORTS = ("ggs_abi_version", "ggs_last_error", "ggs_rasterize_forward", "ggs_ra
            "ggs_backward_from_accumulators", "ggs_sh_gradient_from_views", "ggs_sample_depth_forward",
            "ggs_sample_depth_backward", "ggs_evaluate_sdf",
            "ggs_integrate_points", "ggs_view_prepare", "ggs_integrate_view", "ggs_integrate_view_counted", "ggs_evaluate_sdf_view", "ggs_mark_visible", "ggs_count_blend_ops", "ggs_describe_layout", "ggs_materialize_sorted_keys", "ggs_sort_scratch_bytes",
-           "ggs_sort_pairs", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
+           "ggs_sort_pairs", "ggs_sort_pairs_static", "ggs_profile_enable", "ggs_profile_read", "ggs_view_sum_peer",
            "ggs_peer_sum_ranges", "ggs_rasterize_backward_peer", "ggs_activate_forward", "ggs_activate_backward")
 
 
@@ -174,6 +175,10 @@ def _load():
     lib.ggs_sort_pairs.restype = C.c_int
     lib.ggs_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                    C.c_void_p, C.c_void_p]
+    # no allocation anywhere: the scratch is a static device array inside the library (include/ggs_rasterizer.h)
+    lib.ggs_sort_pairs_static.restype = C.c_int
+    lib.ggs_sort_pairs_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                          C.c_int32, C.c_void_p]
     lib.ggs_profile_enable.restype = C.c_int
     lib.ggs_profile_enable.argtypes = [C.c_int]
     lib.ggs_materialize_sorted_keys.restype = C.c_int

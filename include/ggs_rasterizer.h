@@ -414,6 +414,20 @@ GGS_API size_t ggs_sort_scratch_bytes(int64_t n, int32_t begin_bit, int32_t end_
 GGS_API int ggs_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                    int64_t n, int32_t begin_bit, int32_t end_bit, void* scratch, void* stream);
 
+/* ggs_sort_pairs without an allocation anywhere -- NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results as ggs_sort_pairs minus `scratch`: the scratch is a file-scope
+ * `static __device__` array inside the library, sized for GGS_SORT_STATIC_MAX_PAIRS pairs over all 64 key bits
+ * (about 3.7 MiB, held by every GPU that loads the library until the process exits).  n beyond the maximum is refused
+ * with GGS_ERR_INVALID_ARGUMENT and a message naming the limit.  The call makes no cudaMalloc / cudaFree / allocating
+ * library call; it enqueues copies, memsets and kernels on `stream` and returns.  Every call on a device shares the
+ * one array, which keeps the previous call's contents (the histograms, look-back descriptors and tile tickets are
+ * cleared on `stream` at the start of each call): calls that OVERLAP on the GPU -- two streams, two host threads, or
+ * this call beside another still running -- race on it; serialise them on one stream or with events. */
+#define GGS_SORT_STATIC_MAX_PAIRS (1 << 18)
+GGS_API int ggs_sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                                  uint32_t* vals_out, int64_t n, int32_t begin_bit, int32_t end_bit, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,8 @@ def pytest_configure(config):
 
 def pytest_collection_modifyitems(config, items):
     def rank(item):  # stable sort: unmarked tests keep their order and run first; marked ones by their `order`
+        if os.path.basename(str(item.fspath)).startswith("test_zz_"):
+            return 1 << 30  # tests/test_zz_no_alloc.py stays the very last file, behind the marked ones too
         m = item.get_closest_marker("first_hardware_run")
         return 0 if m is None else 1 + int(m.kwargs.get("order", 0))
 
