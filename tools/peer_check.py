@@ -24,7 +24,10 @@ def main():
     sc = bench.make_view(workload, rank, world)
     names = ("means3D", "opacities", "scales", "rotations", "shs")
 
-    def run(peer, multicast=None, reps=1, pull=False):
+    def run(peer, multicast=None, reps=1, pull=False, extra=None):
+        for k in ("GGS_PEER_FUSE_RGB", "GGS_PEER_SH_LATE", "GGS_PEER_CHUNKS"):
+            os.environ.pop(k, None)
+        os.environ.update(extra or {})
         os.environ["GGS_PEER"] = "1" if peer else "0"
         os.environ["GGS_PEER_PULL"] = "1" if pull else "0"
         os.environ["GGS_MULTICAST"] = "" if multicast is None else ("1" if multicast else "0")
@@ -39,9 +42,13 @@ def main():
     if rank == 0:
         print(f"nccl reference done ({workload}, P={sc.P}, world={world})", flush=True)
     rc = 0
-    for mc, pull in ((False, False), (True, False), (True, True)):
+    # the last four are the switch-reduced default (colour gradients pushed by the per-Gaussian backward itself, SH sum
+    # behind the backward) and each of its parts switched off / the pipelined sum switched on
+    variants = ((False, False, {}), (True, False, {}), (True, True, {}), (True, True, {"GGS_PEER_FUSE_RGB": "0"}),
+                (True, True, {"GGS_PEER_SH_LATE": "0"}), (True, True, {"GGS_PEER_CHUNKS": "2"}))
+    for mc, pull, extra in variants:
         try:
-            step, got = run(True, mc, reps=3, pull=pull)
+            step, got = run(True, mc, reps=3, pull=pull, extra=extra)
         except Exception as e:  # noqa: BLE001
             print(f"rank {rank}: exchange(multicast={mc}) failed: {type(e).__name__}: {e}", flush=True)
             if mc:
@@ -56,7 +63,9 @@ def main():
         errs = {k: float((got[k] - ref[k]).abs().max() / ref[k].abs().max().clamp_min(1e-30)) for k in names}
         ok = max(errs.values()) < 1e-5
         msg = "  ".join(f"{k} {v:.1e}" for k, v in errs.items())
-        print(f"rank {rank}: {step.exchange_note}: {'OK' if ok else 'MISMATCH'}  {msg}", flush=True)
+        ex = step.exchange
+        flags = f"fused_push={int(ex.fused_push)} sh_late={int(ex.sh_after_backward)} chunks={ex.chunks}"
+        print(f"rank {rank}: {step.exchange_note} [{flags}]: {'OK' if ok else 'MISMATCH'}  {msg}", flush=True)
         if not ok:
             rc = 1
         # the exchange alone: barrier + view-sum launch + barrier, on static data
