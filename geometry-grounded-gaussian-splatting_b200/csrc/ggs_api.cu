@@ -87,6 +87,12 @@ uint32_t* pinned_word() {
     return g_pinned;
 }
 
+// render CTAs take the tiles longest list first (TileLayout::order); -DGGS_TILE_ORDER=0 keeps row-major order
+#ifndef GGS_TILE_ORDER
+#define GGS_TILE_ORDER 1
+#endif
+constexpr bool kTileOrder = GGS_TILE_ORDER != 0;
+
 int sort_end_bit(int tiles) { return 32 + (int)higher_msb((uint32_t)tiles); }
 int sort_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS; }
 
@@ -349,6 +355,11 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     ro.warp_words = at<uint32_t>(tile, TL.warp_words);
     ro.near_mask = near_mask(bin, cap, tiles);
     ro.near_first = at<uint32_t>(tile, TL.near_first);
+    ro.tile_order = nullptr;
+    if (kTileOrder) {
+        launch_tile_order(at<uint2>(tile, TL.ranges), nullptr, tiles, at<uint32_t>(tile, TL.order), stream);
+        ro.tile_order = at<uint32_t>(tile, TL.order);
+    }
     launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, cap, tiles),
                           at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
     GGS_STAGE("render_forward", debug, stream);
@@ -456,6 +467,7 @@ int backward_impl(const GgsFrame* frame, const GgsGaussians* gaussians, const Gg
     ri.warp_words = at<uint32_t>(state->tile, TL.warp_words);
     ri.near_mask = near_mask(state->binning, state_capacity(state), tiles);
     ri.near_first = at<uint32_t>(state->tile, TL.near_first);
+    ri.tile_order = kTileOrder ? at<uint32_t>(state->tile, TL.order) : nullptr;
     ri.dL_dcolor = bi->dL_dcolor;
     ri.dL_dmdepth = bi->dL_dmdepth;
     ri.dL_dalpha = bi->dL_dalpha;

@@ -334,6 +334,69 @@ void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint
     tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_tile_keys, n, n_dev, ranges);
 }
 
+// Longest-processing-time-first order of the tiles for the render kernels.  A tile's cost follows its list length; the
+// hardware hands CTAs out in grid order, so with row-major tiles whichever long lists happen to sit in the last rows
+// run alone at the end.  One block: maximum length, 1024 length classes (descending), counting sort.  The order inside
+// a class is whatever the shared-memory atomics give -- no result depends on it.
+constexpr int ORDER_THREADS = 1024;
+__global__ void __launch_bounds__(ORDER_THREADS) tile_order_kernel(const uint2* __restrict__ ranges,
+                                                                   const uint32_t* __restrict__ lengths, int tiles,
+                                                                   uint32_t* __restrict__ order) {
+    // cost of tile t: its list length, or lengths[t] where the caller knows better (the backward: the last list
+    // position any pixel of the tile reached in the forward)
+    auto cost = [&](int t) {
+        if (lengths) return __ldg(lengths + t);
+        const uint2 r = __ldg(ranges + t);
+        return r.y - r.x;
+    };
+    __shared__ uint32_t s_count[ORDER_THREADS];
+    __shared__ uint32_t s_warp[ORDER_THREADS / 32];
+    __shared__ uint32_t s_max;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    s_count[tid] = 0;
+    if (tid == 0) s_max = 0;
+    __syncthreads();
+    uint32_t longest = 0;
+    for (int t = tid; t < tiles; t += ORDER_THREADS) longest = max(longest, cost(t));
+    longest = __reduce_max_sync(0xffffffffu, longest);
+    if (lane == 0 && longest) atomicMax(&s_max, longest);
+    __syncthreads();
+    const uint32_t top = s_max;
+    const int shift = top >= (uint32_t)ORDER_THREADS ? 32 - __clz(top) - 10 : 0;  // (top >> shift) < 1024
+    for (int t = tid; t < tiles; t += ORDER_THREADS) atomicAdd(&s_count[ORDER_THREADS - 1 - (cost(t) >> shift)], 1u);
+    __syncthreads();
+    // exclusive scan of the class counts: thread t owns class t
+    const uint32_t mine = s_count[tid];
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_warp[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, wi, d);
+            if (lane >= d) wi += up;
+        }
+        s_warp[lane] = wi - w;
+    }
+    __syncthreads();
+    s_count[tid] = s_warp[warp] + incl - mine;
+    __syncthreads();
+    for (int t = tid; t < tiles; t += ORDER_THREADS)
+        order[atomicAdd(&s_count[ORDER_THREADS - 1 - (cost(t) >> shift)], 1u)] = (uint32_t)t;
+}
+
+void launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order, cudaStream_t stream) {
+    if (tiles <= 0) return;
+    tile_order_kernel<<<1, ORDER_THREADS, 0, stream>>>(ranges, lengths, tiles, order);
+}
+
 // The reference's sorted 64-bit keys, for inspection and the parity tests: (tile << 32) | depth bits of the pair's Gaussian.
 __global__ void __launch_bounds__(256) emit_keys64_kernel(const uint32_t* __restrict__ tile_keys,
                                                           const uint32_t* __restrict__ vals,

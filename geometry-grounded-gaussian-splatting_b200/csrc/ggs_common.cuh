@@ -211,6 +211,8 @@ struct TileLayout {
     size_t max_contributor;  // u32[tiles]
     size_t warp_words;       // u32[tiles][8]: words of accept_mask each warp of the tile produced
     size_t near_first;       // u32[tiles][8]: list positions <= this are exactly zero in the warp's dT/dt pass
+    size_t order;            // u32[tiles]: tile ids by descending list length -- the order the render kernels' CTAs take
+                             // them in (longest first, so that the grid's tail is made of short tiles)
     size_t bytes;
 };
 inline TileLayout tile_layout(size_t tiles) {
@@ -219,7 +221,8 @@ inline TileLayout tile_layout(size_t tiles) {
     L.max_contributor = align_up(tiles * 8, 256);
     L.warp_words = L.max_contributor + align_up(tiles * 4, 256);
     L.near_first = L.warp_words + align_up(tiles * 32, 256);
-    L.bytes = L.near_first + align_up(tiles * 32, 256);
+    L.order = L.near_first + align_up(tiles * 32, 256);
+    L.bytes = L.order + align_up(tiles * 4, 256);
     return L;
 }
 

@@ -103,7 +103,13 @@ struct RenderOut {
     uint32_t* warp_words;   // see TileLayout::warp_words
     uint32_t* near_mask;    // see BinLayout::near_mask
     uint32_t* near_first;   // see TileLayout::near_first
+    const uint32_t* tile_order;  // see TileLayout::order; nullptr = CTAs take the tiles in row-major order
 };
+// Tile ids by descending list length (counting sort on 1024 length classes, one block): the render kernels hand their
+// CTAs out in this order, longest lists first, so that the last wave of the grid is made of the shortest tiles.
+// Cost of a tile = its list length, or lengths[t] when `lengths` is given.
+void launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order, cudaStream_t stream);
+
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
                            const SplatRecord* records, const RenderOut& out, bool require_depth,
                            cudaStream_t stream);
@@ -119,6 +125,7 @@ struct RenderBwdIn {
     const uint32_t* warp_words;
     const uint32_t* near_mask;
     const uint32_t* near_first;
+    const uint32_t* tile_order;  // see TileLayout::order; nullptr = row-major
     const float* dL_dcolor;
     const float* dL_dmdepth;
     const float* dL_dalpha;

@@ -26,6 +26,7 @@ struct RenderBwdParams {
     int W, H, gx;
     float focal_x, focal_y;
     const float* bg;  // device [3]
+    const uint32_t* tile_order;  // TileLayout::order or nullptr
 };
 
 
@@ -111,11 +112,17 @@ __global__ void __launch_bounds__(TILE_PIXELS, GGS_BWD_MIN_BLOCKS)
 
     const int W = rp.W, H = rp.H;
     const size_t HW = (size_t)H * W;
-    const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
+    uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y;
+    if (rp.tile_order) {  // in grid order the CTAs walk TileLayout::order: longest lists first
+        const uint32_t t = __ldg(rp.tile_order + blockIdx.y * gridDim.x + blockIdx.x);
+        tile_y = t / (uint32_t)rp.gx;
+        tile_x = t - tile_y * (uint32_t)rp.gx;
+    }
+    const uint32_t tile_id = tile_y * rp.gx + tile_x;
     const uint32_t tid = threadIdx.x;
     const uint32_t warp = tid >> 5;
     const int lane = tid & 31;
-    const uint2 pix = {blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7), blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3)};
+    const uint2 pix = {tile_x * TILE_X + (warp & 1) * 8 + (lane & 7), tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
     const float2 pixnf = {(pixf.x - static_cast<float>(W - 1) / 2.f) / rp.focal_x,
@@ -420,6 +427,7 @@ void launch_render_backward(const FrameParams& fp, const uint2* ranges, const ui
     rp.focal_x = fp.focal_x;
     rp.focal_y = fp.focal_y;
     rp.bg = fp.view.bg;
+    rp.tile_order = in.tile_order;
     const dim3 grid(fp.gx, fp.gy, 1);
     const dim3 block(TILE_PIXELS, 1, 1);
     constexpr size_t SMEM = BWD_REC_BYTES;  // eight warps x two slots x 32 records

@@ -34,6 +34,7 @@ struct RenderParams {
     int W, H, gx;
     float focal_x, focal_y;
     const float* bg;  // device [3]
+    const uint32_t* tile_order;  // TileLayout::order or nullptr
 };
 
 // A CTA renders HALF a tile (16x8 pixels, 4 warps; blockIdx.z = half): the barrier that hands over a staged batch
@@ -123,12 +124,22 @@ __global__ void __launch_bounds__(THREADS, 8)
     __shared__ uint32_t s_red[WARPS];
 
     const int W = rp.W, H = rp.H;
-    const uint32_t tile_id = blockIdx.y * rp.gx + blockIdx.x;
+    // which half of which tile: in grid order the CTAs walk TileLayout::order (longest lists first), the halves of a
+    // tile next to each other
+    uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y, half = blockIdx.z;
+    if (rp.tile_order) {
+        const uint32_t lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        const uint32_t t = __ldg(rp.tile_order + lin / (TILE_WARPS / WARPS));
+        half = lin % (TILE_WARPS / WARPS);
+        tile_y = t / (uint32_t)rp.gx;
+        tile_x = t - tile_y * (uint32_t)rp.gx;
+    }
+    const uint32_t tile_id = tile_y * rp.gx + tile_x;
     const uint32_t tid = threadIdx.x;
     const uint32_t warp = tid >> 5, lane = tid & 31;  // warp: within this CTA (staging, shared arrays)
-    const uint32_t twarp = blockIdx.z * WARPS + warp;  // within the tile (pixels, masks)
+    const uint32_t twarp = half * WARPS + warp;  // within the tile (pixels, masks)
     // warp w of the tile owns its 8x4 pixel block (w & 1, w >> 1)
-    const uint2 pix0 = {blockIdx.x * TILE_X + (twarp & 1) * 8, blockIdx.y * TILE_Y + (twarp >> 1) * 4};
+    const uint2 pix0 = {tile_x * TILE_X + (twarp & 1) * 8, tile_y * TILE_Y + (twarp >> 1) * 4};
     const uint2 pix = {pix0.x + (lane & 7), pix0.y + (lane >> 3)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {static_cast<float>(pix.x), static_cast<float>(pix.y)};
@@ -525,6 +536,7 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     rp.focal_x = fp.focal_x;
     rp.focal_y = fp.focal_y;
     rp.bg = fp.view.bg;
+    rp.tile_order = out.tile_order;
     const dim3 grid(fp.gx, fp.gy, TILE_WARPS / WARPS);
     const dim3 block(THREADS, 1, 1);
     cudaMemsetAsync(out.max_contributor, 0, (size_t)fp.gx * fp.gy * sizeof(uint32_t), stream);
