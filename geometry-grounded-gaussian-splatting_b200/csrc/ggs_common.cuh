@@ -280,6 +280,61 @@ __device__ __forceinline__ void load_rows_to_shared(const float4* __restrict__ s
         load_rows_to_shared_impl<0>(src, Q, ng, rows, swarp, RS, lane);
 }
 
+// The same copy without registers in between and without waiting: 4-byte cp.async (the odd row stride leaves the rows
+// 4-byte aligned only), every warp instruction one 128-byte line of the slab.  The caller overlaps whatever does not
+// need the rows and then waits -- cp.async.wait_all + __syncwarp at a convergent point, or, where the consumers have
+// diverged from the lanes that issued part of their row, an mbarrier every lane's copies arrive on (below).
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+template <int FC>
+__device__ __forceinline__ void copy_rows_to_shared_async_impl(const float* __restrict__ src, int Fr, int ng,
+                                                               uint32_t rows, float* __restrict__ swarp, int RS,
+                                                               int lane) {
+    const int F = FC > 0 ? FC : Fr;
+    const int total = ng * F;
+#pragma unroll 4
+    for (int e = lane; e < total; e += 32) {
+        const int gi = e / F, rem = e - gi * F;
+        if ((rows >> gi) & 1u) cp_async4(swarp + gi * RS + rem, src + e);
+    }
+}
+// src: the warp's [ng][F] floats; rows: bit gi set = row gi wanted
+__device__ __forceinline__ void copy_rows_to_shared_async(const float* __restrict__ src, int F, int ng, uint32_t rows,
+                                                          float* __restrict__ swarp, int RS, int lane) {
+    if (F == 48)
+        copy_rows_to_shared_async_impl<48>(src, F, ng, rows, swarp, RS, lane);
+    else
+        copy_rows_to_shared_async_impl<0>(src, F, ng, rows, swarp, RS, lane);
+}
+__device__ __forceinline__ void cp_async_wait_everything() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// A warp's mbarrier for such copies: init for 32 arrivals (one lane, then __syncwarp), every lane lets its copies
+// arrive on it (also a lane that issued none), consumers wait for phase 0 -- they may have diverged by then.
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t arrivals) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(a), "r"(arrivals) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_on(uint64_t* bar) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared.b64 [%0];" ::"r"(a) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(a),
+        "r"(parity)
+        : "memory");
+}
+
 // The way back: shared-memory rows of stride RS -> [ng][4 Q] floats contiguous in global memory, 16-byte stores.
 template <int QC>
 __device__ __forceinline__ void store_rows_from_shared_impl(float4* __restrict__ dst, int Qr, int ng,
