@@ -168,13 +168,26 @@ T* at(void* base, size_t off) {
 // again on an exact-size workspace (nothing downstream has consumed the short one).
 int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_color, int* radii, void* geom,
                   uint2* ranges, GgsAllocFn alloc, void* user, void** bin, int64_t* D_out, int64_t capacity_hint,
-                  int64_t* capacity_out, bool debug, cudaStream_t stream) {
+                  int64_t* capacity_out, bool debug, cudaStream_t stream, void* also_clear = nullptr,
+                  size_t also_clear_bytes = 0) {
     const GeomLayout GL = geom_layout(fp.P);
+    const int tiles = fp.gx * fp.gy;
     prof_mark(stream, EV_F0);
+    ClearList cl;
+    {
+        // everything the stages up to the tile ranges expect zeroed, cleared by the preprocess grid on its way (they
+        // used to issue ten small memsets between their kernels): the scan's descriptors, ticket and total, the depth
+        // pre-sort's histograms / look-back descriptors / tickets, the tile ranges, and whatever the caller adds
+        // (the forward: max_contributor)
+        cl.add(at<char>(geom, GL.scan_status), GL.order_keys_a - GL.scan_status);
+        cl.add(at<char>(geom, GL.order_hist), GL.bytes - GL.order_hist);
+        cl.add(ranges, (size_t)tiles * sizeof(uint2));
+        if (also_clear) cl.add(also_clear, also_clear_bytes);
+    }
     launch_preprocess(fp, in, want_color, at<SplatRecord>(geom, GL.records), at<float>(geom, GL.depths),
                       at<uint32_t>(geom, GL.tiles_touched), at<uint2>(geom, GL.rects),
-                      at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.total) + 1,
-                      at<uint32_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_vals_a), stream);
+                      at<uint8_t>(geom, GL.clamped), radii, at<uint32_t>(geom, GL.order_keys_a),
+                      at<uint32_t>(geom, GL.order_vals_a), stream, &cl);
     GGS_STAGE("preprocess", debug, stream);
     prof_mark(stream, EV_PRE);
     // Depth pre-sort of the P Gaussians (4 passes over 8 B x P: 32-bit keys) so that the D pairs only need the tile
@@ -182,13 +195,13 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     launch_radix_sort32(at<uint32_t>(geom, GL.order_keys_a), at<uint32_t>(geom, GL.order_keys_b),
                         at<uint32_t>(geom, GL.order_vals_a), at<uint32_t>(geom, GL.order_vals_b), (uint32_t)fp.P, 32,
                         at<uint32_t>(geom, GL.order_hist), at<uint32_t>(geom, GL.order_status), GL.order_status_bytes,
-                        at<uint32_t>(geom, GL.order_counters), stream, 3);
+                        at<uint32_t>(geom, GL.order_counters), stream, 3, true);
     GGS_STAGE("depth_order", debug, stream);
     prof_mark(stream, EV_ORDER);
     const uint32_t* order = at<uint32_t>(geom, GL.order_vals_a);
     uint32_t* const total = at<uint32_t>(geom, GL.total);
     launch_scan(at<uint32_t>(geom, GL.tiles_touched), at<uint32_t>(geom, GL.point_offsets), fp.P,
-                at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter), total, stream, order);
+                at<uint64_t>(geom, GL.scan_status), at<uint32_t>(geom, GL.scan_counter), total, stream, order, true);
     GGS_STAGE("scan", debug, stream);
     prof_mark(stream, EV_SCAN);
     uint32_t* host = pinned_word();
@@ -197,7 +210,6 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     GGS_CUDA(cudaMemcpyAsync(host, total, 4, cudaMemcpyDeviceToHost, stream));
     GGS_CUDA(cudaEventRecord(counted, stream));
 
-    const int tiles = fp.gx * fp.gy;
     const int end_bit = sort_end_bit(tiles);
     const int tile_bits = end_bit - 32;
     const int passes = tile_sort_passes(tile_bits);
@@ -206,7 +218,7 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
     uint64_t cap = capacity_hint > 0 ? (uint64_t)std::min<int64_t>(capacity_hint, (1 << 30) - 1) : 0;
     bool counted_yet = false;
     uint32_t D = 0;
-    for (;;) {
+    for (bool first_round = true;; first_round = false) {
         if (cap == 0) {
             // no hint (or the hint was too small): the host waits where the reference does
             GGS_CUDA(cudaEventSynchronize(counted));
@@ -228,17 +240,24 @@ int bin_gaussians(const FrameParams& fp, const GaussianInputs& in, bool want_col
         uint32_t* v_a = at<uint32_t>(b, BL.vals_a);
         uint32_t* v_b = at<uint32_t>(b, BL.vals_b);
         const uint32_t* n_dev = counted_yet ? nullptr : total;
+        {
+            ClearList cl;  // digit histograms, look-back descriptors and tickets of the tile sort: adjacent
+            cl.add(at<char>(b, BL.hist), BL.accept_mask - BL.hist);
+            launch_clear(cl, stream);
+        }
         prof_mark(stream, EV_DUP0);
         launch_duplicate_keys(fp.P, order, at<uint32_t>(geom, GL.point_offsets), at<uint2>(geom, GL.rects), fp.gx,
                               odd ? tk_b : tk_a, odd ? v_b : v_a, (uint32_t)cap, passes, at<uint32_t>(b, BL.hist),
-                              stream);
+                              stream, true);
         GGS_STAGE("duplicate_keys", debug, stream);
         prof_mark(stream, EV_DUP);
         launch_tile_sort(tk_a, tk_b, v_a, v_b, (uint32_t)cap, n_dev, tile_bits, nullptr, nullptr,
-                         at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), at<uint32_t>(b, BL.counters), stream);
+                         at<uint32_t>(b, BL.hist), at<uint32_t>(b, BL.status), at<uint32_t>(b, BL.counters), stream,
+                         true);
         GGS_STAGE("radix_sort", debug, stream);
         prof_mark(stream, EV_SORT);
-        launch_tile_ranges(tk_a, (uint32_t)cap, n_dev, ranges, tiles, stream);  // the sorted tile keys land in tk_a
+        // (the sorted tile keys land in tk_a; the ranges of a first, too short round are cleared again)
+        launch_tile_ranges(tk_a, (uint32_t)cap, n_dev, ranges, tiles, stream, first_round);
         GGS_STAGE("tile_ranges", debug, stream);
         prof_mark(stream, EV_RANGES);
         if (counted_yet) break;
@@ -334,7 +353,8 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
     int64_t D = 0, cap = 0;
     void* bin = nullptr;
     rc = bin_gaussians(fp, in, true, out->radii, geom, at<uint2>(tile, TL.ranges), alloc, user, &bin, &D,
-                       capacity_hint, &cap, debug, stream);
+                       capacity_hint, &cap, debug, stream, at<char>(tile, TL.max_contributor),
+                       (size_t)tiles * sizeof(uint32_t));
     if (rc) return rc;
     state->binning = bin;
     state->num_rendered = D;
@@ -361,7 +381,8 @@ int64_t ggs_rasterize_forward(const GgsFrame* frame, const GgsGaussians* gaussia
         ro.tile_order = at<uint32_t>(tile, TL.order);
     }
     launch_render_forward(fp, at<uint2>(tile, TL.ranges), sorted_list(bin, cap, tiles),
-                          at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream);
+                          at<SplatRecord>(geom, GL.records), ro, frame->require_depth != 0, stream,
+                          /*cleared=*/true);
     GGS_STAGE("render_forward", debug, stream);
     prof_mark(stream, EV_RENDER);
     g_prof.have_fwd = g_prof.on;

@@ -120,11 +120,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __re
 }
 
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
-                 cudaStream_t stream, const uint32_t* order) {
+                 cudaStream_t stream, const uint32_t* order, bool cleared) {
     const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    cudaMemsetAsync(status, 0, (size_t)(tiles + 1) * 8, stream);
-    cudaMemsetAsync(counter, 0, 4, stream);
-    cudaMemsetAsync(total, 0, 4, stream);
+    if (!cleared) {
+        cudaMemsetAsync(status, 0, (size_t)(tiles + 1) * 8, stream);
+        cudaMemsetAsync(counter, 0, 4, stream);
+        cudaMemsetAsync(total, 0, 4, stream);
+    }
     if (n == 0) return;
     if (order)
         scan_kernel<true><<<tiles, SCAN_THREADS, 0, stream>>>(in, order, out, n, status, counter, total);
@@ -280,8 +282,8 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_keys_kernel(int P, cons
 
 void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
                            uint32_t* tile_keys, uint32_t* vals, uint32_t capacity, int passes, uint32_t* hist,
-                           cudaStream_t stream) {
-    cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
+                           cudaStream_t stream, bool cleared) {
+    if (!cleared) cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
     if (P == 0 || capacity == 0) return;
     duplicate_keys_kernel<<<(P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, stream>>>(
         P, order, offsets, rects, gx, tile_keys, vals, capacity, passes > 4 ? 4 : passes, hist);
@@ -327,8 +329,8 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint32_t* __rest
 }
 
 void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
-                        cudaStream_t stream) {
-    cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
+                        cudaStream_t stream, bool cleared) {
+    if (!cleared) cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream);
     if (n == 0) return;
     const uint32_t per_block = 256 * RANGE_ITEMS;
     tile_ranges_kernel<<<(n + per_block - 1) / per_block, 256, 0, stream>>>(sorted_tile_keys, n, n_dev, ranges);
@@ -390,6 +392,23 @@ __global__ void __launch_bounds__(ORDER_THREADS) tile_order_kernel(const uint2* 
     __syncthreads();
     for (int t = tid; t < tiles; t += ORDER_THREADS)
         order[atomicAdd(&s_count[ORDER_THREADS - 1 - (cost(t) >> shift)], 1u)] = (uint32_t)t;
+}
+
+// One launch instead of a handful of small memsets (ggs_kernels.cuh: ClearList).
+__global__ void __launch_bounds__(256) clear_kernel(const ClearList list) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (int s = 0; s < list.count; s++) {
+        uint4* const p = static_cast<uint4*>(list.p[s]);
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < list.n16[s]; i += stride) p[i] = uint4{0, 0, 0, 0};
+    }
+}
+
+void launch_clear(const ClearList& list, cudaStream_t stream) {
+    uint32_t most = 0;
+    for (int s = 0; s < list.count; s++) most = max(most, list.n16[s]);
+    if (most == 0) return;
+    const int blocks = (int)min((most + 255u) / 256u, 148u * 8u);
+    clear_kernel<<<blocks, 256, 0, stream>>>(list);
 }
 
 void launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, uint32_t* order, cudaStream_t stream) {

@@ -27,15 +27,30 @@ struct GaussianInputs {
 };
 
 // ---- stage 1: per-Gaussian preprocess + scan -------------------------------------------------
-// depth_extremes[0] = max over visible Gaussians of the depth's float bits, [1] = max of their complement
-// (i.e. ~min); zeroed here.  The host uses them to plan the sort (SortPlan).
+// The stages of the binning clear their own counters / histograms / look-back descriptors with small memsets, each of
+// which costs the stream a drain and a refill.  A caller that knows the whole sequence lists the spans (16-byte
+// aligned, up to six) and has them cleared in one go -- by the preprocess grid on its way (nothing in that kernel
+// touches them), or by launch_clear -- and passes cleared = true to the stages.
+struct ClearList {
+    void* p[6];
+    uint32_t n16[6];  // 16-byte units
+    int count = 0;
+    void add(void* ptr, size_t bytes) {
+        p[count] = ptr;
+        n16[count] = (uint32_t)((bytes + 15) / 16);
+        count++;
+    }
+};
+void launch_clear(const ClearList& list, cudaStream_t stream);
+
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       uint32_t* depth_extremes, uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream);
+                       uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream,
+                       const ClearList* clear = nullptr);
 
 // order != null: scans in[order[i]] (the tile counts taken in depth order)
 void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uint32_t* counter, uint32_t* total,
-                 cudaStream_t stream, const uint32_t* order = nullptr);
+                 cudaStream_t stream, const uint32_t* order = nullptr, bool cleared = false);
 
 // ---- stage 2: key duplication, radix sort, tile ranges ----------------------------------------
 // order[i] = Gaussian at depth rank i; offsets = inclusive scan of the tile counts in that order.  Emits 32-bit TILE
@@ -45,7 +60,7 @@ void launch_scan(const uint32_t* in, uint32_t* out, int n, uint64_t* status, uin
 // count was known (slots beyond the count stay unwritten; pairs beyond the capacity are dropped, see bin_gaussians).
 void launch_duplicate_keys(int P, const uint32_t* order, const uint32_t* offsets, const uint2* rects, int gx,
                            uint32_t* tile_keys, uint32_t* vals, uint32_t capacity, int passes, uint32_t* hist,
-                           cudaStream_t stream);
+                           cudaStream_t stream, bool cleared = false);
 
 // Digit plan of the radix sort.  Plain: 8-bit digits of bits [begin_bit, end_bit).  Compact (rasterizer keys
 // tile<<32 | depth bits only): the top byte of a positive float depth takes very few distinct values (sign + 7
@@ -77,16 +92,17 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 // Stable sort of (u32 key, u32 value) pairs on key bits [0, bits).  Returns 0 if the result is in *_a, 1 if in *_b.
 int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
-                        cudaStream_t stream, int match_passes = 1);
+                        cudaStream_t stream, int match_passes = 1, bool cleared = false);
 int tile_sort_passes(int tile_bits);
 // n_dev (may be null): the pair count in device memory; the launch is then sized for n = the capacity and the kernels
 // clamp to min(n, *n_dev).
 void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
                       const uint32_t* n_dev, int tile_bits, const uint32_t* depth_bits, uint64_t* keys64_out,
-                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream);
+                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream,
+                      bool cleared = false);
 
 void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint32_t* n_dev, uint2* ranges, int tiles,
-                        cudaStream_t stream);
+                        cudaStream_t stream, bool cleared = false);
 // keys64[i] = (tile_keys[i] << 32) | depth_bits[vals[i]]: the reference's sorted keys, on demand (tests, inspection)
 void launch_emit_keys64(const uint32_t* tile_keys, const uint32_t* vals, const uint32_t* depth_bits, uint32_t n,
                         uint64_t* keys64, cudaStream_t stream);
@@ -112,7 +128,7 @@ void launch_tile_order(const uint2* ranges, const uint32_t* lengths, int tiles, 
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
                            const SplatRecord* records, const RenderOut& out, bool require_depth,
-                           cudaStream_t stream);
+                           cudaStream_t stream, bool cleared = false);
 
 // ---- backward --------------------------------------------------------------------------------
 struct RenderBwdIn {

@@ -235,19 +235,29 @@ __device__ __forceinline__ bool project_gaussian(const size_t idx, const FramePa
 
 constexpr int PRE_THREADS = 128;
 
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FrameParams fp, const GaussianInputs in,
+#ifndef GGS_PRE_MIN_BLOCKS
+#define GGS_PRE_MIN_BLOCKS 7  // 72 registers: 89 us instead of 94 at 80 registers / 6 blocks (8 blocks: spills, no gain)
+#endif
+__global__ void __launch_bounds__(PRE_THREADS, GGS_PRE_MIN_BLOCKS) preprocess_kernel(const FrameParams fp, const GaussianInputs in,
                                                                  const bool want_color, SplatRecord* __restrict__ records,
                                                                  float* __restrict__ depths,
                                                                  uint32_t* __restrict__ tiles_touched,
                                                                  uint2* __restrict__ rects, uint8_t* __restrict__ clamped,
                                                                  int* __restrict__ radii,
-                                                                 uint32_t* __restrict__ depth_extremes,
                                                                  uint32_t* __restrict__ order_keys,
-                                                                 uint32_t* __restrict__ order_vals) {
+                                                                 uint32_t* __restrict__ order_vals,
+                                                                 const ClearList clear) {
     extern __shared__ float s_slab[];  // [warps][32][RS] SH rows (only when colours come from SH)
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool in_range = idx < (size_t)fp.P;
+
+    // what the later stages of the binning expect zeroed (ClearList in ggs_kernels.cuh): nothing in this kernel
+    // touches those spans, so the grid clears them on its way instead of a launch of its own
+    for (int s = 0; s < clear.count; s++) {
+        uint4* const p = static_cast<uint4*>(clear.p[s]);
+        for (uint32_t i = (uint32_t)idx; i < clear.n16[s]; i += gridDim.x * blockDim.x) p[i] = uint4{0, 0, 0, 0};
+    }
 
     Projected pr;
     const bool vis = in_range && project_gaussian(idx, fp, in, pr);
@@ -259,16 +269,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
         // input of the depth pre-sort: culled Gaussians take the largest key and land behind every visible one
         order_keys[idx] = vis ? __float_as_uint(pr.tc) : 0xffffffffu;
         order_vals[idx] = (uint32_t)idx;
-    }
-    {
-        // range of the depth keys (positive floats order like their bits), for the sort's digit plan
-        const uint32_t bits = vis ? __float_as_uint(pr.tc) : 0u;
-        const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
-        const uint32_t wnmax = __reduce_max_sync(0xffffffffu, vis ? ~bits : 0u);
-        if (lane == 0 && wnmax) {
-            atomicMax(depth_extremes, wmax);
-            atomicMax(depth_extremes + 1, wnmax);
-        }
     }
 
     // ---- SH slab of the warp's visible Gaussians -> shared memory -------------------------------------
@@ -327,9 +327,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(const FramePara
 
 void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool want_color, SplatRecord* records,
                        float* depths, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped, int* radii,
-                       uint32_t* depth_extremes, uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream) {
-    cudaMemsetAsync(depth_extremes, 0, 8, stream);
-    if (fp.P == 0) return;
+                       uint32_t* order_keys, uint32_t* order_vals, cudaStream_t stream, const ClearList* clear) {
+    if (fp.P == 0) {
+        if (clear) launch_clear(*clear, stream);
+        return;
+    }
     const int threads = PRE_THREADS;
     const int blocks = (fp.P + threads - 1) / threads;
     const bool use_sh = want_color && in.colors_precomp == nullptr;
@@ -337,7 +339,8 @@ void launch_preprocess(const FrameParams& fp, const GaussianInputs& in, bool wan
     static SmemOptIn opted;
     opt_in_shared_memory(preprocess_kernel, smem, opted);
     preprocess_kernel<<<blocks, threads, smem, stream>>>(fp, in, want_color, records, depths, tiles_touched, rects,
-                                                         clamped, radii, depth_extremes, order_keys, order_vals);
+                                                         clamped, radii, order_keys, order_vals,
+                                                         clear ? *clear : ClearList{});
 }
 
 // Frustum visibility only (reference checkFrustum, rasterizer_impl.cu:54-66).

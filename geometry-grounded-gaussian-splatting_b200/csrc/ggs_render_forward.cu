@@ -528,7 +528,7 @@ __global__ void __launch_bounds__(THREADS, 8)
 
 void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uint32_t* point_list,
                            const SplatRecord* records, const RenderOut& out, bool require_depth,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, bool cleared) {
     RenderParams rp;
     rp.W = fp.W;
     rp.H = fp.H;
@@ -539,7 +539,7 @@ void launch_render_forward(const FrameParams& fp, const uint2* ranges, const uin
     rp.tile_order = out.tile_order;
     const dim3 grid(fp.gx, fp.gy, TILE_WARPS / WARPS);
     const dim3 block(THREADS, 1, 1);
-    cudaMemsetAsync(out.max_contributor, 0, (size_t)fp.gx * fp.gy * sizeof(uint32_t), stream);
+    if (!cleared) cudaMemsetAsync(out.max_contributor, 0, (size_t)fp.gx * fp.gy * sizeof(uint32_t), stream);
     static SmemOptIn opted_geometry, opted_colour;
     opt_in_shared_memory(render_forward_kernel<true>, REC_BYTES + MASK_BYTES, opted_geometry);
     opt_in_shared_memory(render_forward_kernel<false>, REC_BYTES, opted_colour);

@@ -361,7 +361,7 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint
 // the depth pre-sort of the Gaussians.  8-byte pairs instead of 12: a pass moves a third less.
 int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n, int bits,
                         uint32_t* hist, uint32_t* status, size_t status_bytes, uint32_t* counters,
-                        cudaStream_t stream, int match_passes) {
+                        cudaStream_t stream, int match_passes, bool cleared) {
     if (n == 0 || bits <= 0) return 0;
     const int passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
     PassSpecs specs;
@@ -375,9 +375,11 @@ int launch_radix_sort32(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, ui
         specs.d[p] = d;
     }
     const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
-    cudaMemsetAsync(status, 0, status_bytes, stream);
-    cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
+    if (!cleared) {
+        cudaMemsetAsync(hist, 0, MAX_PASSES * RADIX * 4, stream);
+        cudaMemsetAsync(status, 0, status_bytes, stream);
+        cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
+    }
     const int hist_blocks = (int)min((uint32_t)GGS_HIST_BLOCKS, (n + 255) / 256);
     histogram_kernel<uint32_t><<<hist_blocks, 256, 0, stream>>>(keys_a, n, specs, passes, hist);
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);
@@ -408,12 +410,14 @@ int tile_sort_passes(int tile_bits) { return (tile_bits + RADIX_BITS - 1) / RADI
 
 void launch_tile_sort(uint32_t* tk_a, uint32_t* tk_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t n,
                       const uint32_t* n_dev, int tile_bits, const uint32_t* depth_bits, uint64_t* keys64_out,
-                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream) {
+                      uint32_t* hist, uint32_t* status, uint32_t* counters, cudaStream_t stream, bool cleared) {
     if (n == 0) return;
     const int passes = tile_sort_passes(tile_bits);
     const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    cudaMemsetAsync(status, 0, (size_t)passes * tiles * RADIX * 4, stream);
-    cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
+    if (!cleared) {
+        cudaMemsetAsync(status, 0, (size_t)passes * tiles * RADIX * 4, stream);
+        cudaMemsetAsync(counters, 0, MAX_PASSES * 4, stream);
+    }
     offsets_kernel<<<1, RADIX, 0, stream>>>(hist, passes);  // the histograms come from the key duplication
     // final values must land in vals_a: an even number of passes starts in *_a, an odd one in *_b
     uint32_t* kin = (passes & 1) ? tk_b : tk_a;
