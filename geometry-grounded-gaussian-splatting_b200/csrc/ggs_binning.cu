@@ -338,34 +338,40 @@ void launch_tile_ranges(const uint32_t* sorted_tile_keys, uint32_t n, const uint
 
 // Longest-processing-time-first order of the tiles for the render kernels.  A tile's cost follows its list length; the
 // hardware hands CTAs out in grid order, so with row-major tiles whichever long lists happen to sit in the last rows
-// run alone at the end.  One block: maximum length, 1024 length classes (descending), counting sort.  The order inside
-// a class is whatever the shared-memory atomics give -- no result depends on it.
+// run alone at the end.  One block, one read of the lengths (kept in registers): 1024 cost classes on a log scale
+// (exponent and five bits below the leading one, i.e. 3 % steps), descending, counting sort.  The order inside a
+// class is whatever the shared-memory atomics give -- no result depends on it.
 constexpr int ORDER_THREADS = 1024;
+constexpr int ORDER_KEEP = 8;  // costs per thread kept in registers: tiles beyond 8192 are read again
+__device__ __forceinline__ uint32_t cost_class(uint32_t c) {
+    const int e = 31 - __clz(c | 1u);
+    const uint32_t m = e >= 5 ? (c >> (e - 5)) & 31u : (c << (5 - e)) & 31u;
+    return (uint32_t)(ORDER_THREADS - 1) - (((uint32_t)e << 5) | m);
+}
 __global__ void __launch_bounds__(ORDER_THREADS) tile_order_kernel(const uint2* __restrict__ ranges,
                                                                    const uint32_t* __restrict__ lengths, int tiles,
                                                                    uint32_t* __restrict__ order) {
-    // cost of tile t: its list length, or lengths[t] where the caller knows better (the backward: the last list
-    // position any pixel of the tile reached in the forward)
+    __shared__ uint32_t s_count[ORDER_THREADS];
+    __shared__ uint32_t s_warp[ORDER_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // cost of tile t: its list length, or lengths[t] where the caller knows better
     auto cost = [&](int t) {
         if (lengths) return __ldg(lengths + t);
         const uint2 r = __ldg(ranges + t);
         return r.y - r.x;
     };
-    __shared__ uint32_t s_count[ORDER_THREADS];
-    __shared__ uint32_t s_warp[ORDER_THREADS / 32];
-    __shared__ uint32_t s_max;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     s_count[tid] = 0;
-    if (tid == 0) s_max = 0;
+    uint32_t klass[ORDER_KEEP];
+#pragma unroll
+    for (int k = 0; k < ORDER_KEEP; k++) {
+        const int t = tid + k * ORDER_THREADS;
+        klass[k] = t < tiles ? cost_class(cost(t)) : 0u;
+    }
     __syncthreads();
-    uint32_t longest = 0;
-    for (int t = tid; t < tiles; t += ORDER_THREADS) longest = max(longest, cost(t));
-    longest = __reduce_max_sync(0xffffffffu, longest);
-    if (lane == 0 && longest) atomicMax(&s_max, longest);
-    __syncthreads();
-    const uint32_t top = s_max;
-    const int shift = top >= (uint32_t)ORDER_THREADS ? 32 - __clz(top) - 10 : 0;  // (top >> shift) < 1024
-    for (int t = tid; t < tiles; t += ORDER_THREADS) atomicAdd(&s_count[ORDER_THREADS - 1 - (cost(t) >> shift)], 1u);
+#pragma unroll
+    for (int k = 0; k < ORDER_KEEP; k++)
+        if (tid + k * ORDER_THREADS < tiles) atomicAdd(&s_count[klass[k]], 1u);
+    for (int t = tid + ORDER_KEEP * ORDER_THREADS; t < tiles; t += ORDER_THREADS) atomicAdd(&s_count[cost_class(cost(t))], 1u);
     __syncthreads();
     // exclusive scan of the class counts: thread t owns class t
     const uint32_t mine = s_count[tid];
@@ -390,11 +396,17 @@ __global__ void __launch_bounds__(ORDER_THREADS) tile_order_kernel(const uint2* 
     __syncthreads();
     s_count[tid] = s_warp[warp] + incl - mine;
     __syncthreads();
-    for (int t = tid; t < tiles; t += ORDER_THREADS)
-        order[atomicAdd(&s_count[ORDER_THREADS - 1 - (cost(t) >> shift)], 1u)] = (uint32_t)t;
+#pragma unroll
+    for (int k = 0; k < ORDER_KEEP; k++) {
+        const int t = tid + k * ORDER_THREADS;
+        if (t < tiles) order[atomicAdd(&s_count[klass[k]], 1u)] = (uint32_t)t;
+    }
+    for (int t = tid + ORDER_KEEP * ORDER_THREADS; t < tiles; t += ORDER_THREADS)
+        order[atomicAdd(&s_count[cost_class(cost(t))], 1u)] = (uint32_t)t;
 }
 
-// One launch instead of a handful of small memsets (ggs_kernels.cuh: ClearList).
+// One launch instead of a handful of small memsets (ggs_kernels.cuh: ClearList), for callers without a grid of
+// their own to do it on the way.
 __global__ void __launch_bounds__(256) clear_kernel(const ClearList list) {
     const uint32_t stride = gridDim.x * blockDim.x;
     for (int s = 0; s < list.count; s++) {
