@@ -903,9 +903,10 @@ def main():
         # depth pre-sort: histogram read + 4 passes of (8 + 4) B in and out per Gaussian; tile sort: 32-bit keys + values
         # in and out per pass (the reference's 64-bit keys are not materialised on the hot path)
         stats["sort_bytes_moved"] = 8 * sc.P + 4 * 24 * sc.P + sort_passes_run * 16 * stats["num_rendered"]
-        # preprocess, depth pre-sort (histogram, offsets, 4 passes), scan, duplicate (+ tile histograms), tile sort
-        # (offsets, passes), ranges, render fwd, render bwd, per-Gaussian bwd
-        line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 1 + sort_passes_run + 1 + 1 + 2)
+        # preprocess (clears the binning scratch on its way), depth pre-sort (histogram, offsets, 4 passes), scan, clear
+        # of the tile sort's scratch, duplicate (+ tile histograms), tile sort (offsets, passes), ranges, tile order,
+        # render fwd, render bwd, per-Gaussian bwd
+        line["gpu_launches"] = args.steps * (1 + 6 + 1 + 1 + 1 + 1 + sort_passes_run + 1 + 1 + 1 + 2)
         alg = algorithmic(stats)
         per_stage = {}
         for k, b in alg.items():
@@ -913,7 +914,7 @@ def main():
             if t:
                 per_stage[k] = {"ms": t, "alg_bytes": b, "gbs": b / t / 1e6, "frac_hbm": b / t / 1e6 / hbm}
         # measured DRAM traffic per launch (ncu --set full of this same command, summarised under profiles/)
-        traffic, traffic_src = {}, None
+        traffic, traffic_src, executed = {}, None, {}
         cands = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic_*.json")))
         if cands and args.workload == "c3":
             with open(cands[-1]) as fh:
@@ -922,9 +923,11 @@ def main():
             kmap = {"preprocess": "preprocess_kernel", "scan": "scan_kernel", "duplicate": "duplicate_keys_kernel",
                     "ranges": "tile_ranges_kernel", "render_forward": "render_forward_kernel",
                     "render_backward": "render_backward_kernel", "gaussian_backward": "gaussian_backward_kernel"}
+            executed = {}
             for st, kn in kmap.items():
                 if kn in tj["kernels"]:
                     traffic[st] = tj["kernels"][kn]["dram_bytes"]
+                    executed[st] = {k: v for k, v in tj["kernels"][kn].items() if k.endswith("_pct")}
                     if st in per_stage:
                         per_stage[st]["dram_bytes_ncu"] = traffic[st]
         dom = max(per_stage, key=lambda k: per_stage[k]["ms"])
@@ -945,6 +948,13 @@ def main():
                                 "peak_source": f"{sms} SMs x 16 (XU) / 128 (FP32) lanes per clock at the SM clock sampled "
                                                "during the run",
                                 "ops": "algorithmic, SURVEY.md 8(d): counts from ggs_count_blend_ops x per-pair constants",
+                                # what the reference's algorithm would issue, not what this kernel issues: the exact
+                                # shortcuts (entries behind every bracket never visited, the 6.5 sigma rule) skip part
+                                # of it, so `frac` can exceed 1; `executed` is the utilisation ncu measured
+                                "note": "ops are the reference algorithm's; this kernel skips part of them exactly, so "
+                                        "frac may exceed 1. executed = pipe / issue utilisation under ncu "
+                                        "(traffic_source)",
+                                "executed": (executed.get(dom) if traffic_src else None),
                                 "hbm": {"achieved": per_stage[dom]["gbs"], "peak": hbm, "unit": "GB/s",
                                         "frac": per_stage[dom]["frac_hbm"], "peak_source": how}}
         else:
