@@ -68,6 +68,24 @@ def test_argument_errors_without_gpu():
     assert rc == -1
 
 
+def test_static_sort_rejects_bad_sizes_without_gpu():
+    """ggs_sort_pairs_static (no allocation; static device scratch): every refusal happens before any CUDA call."""
+    from diff_gaussian_rasterization import _abi
+
+    f = _abi.lib.ggs_sort_pairs_static
+    one = C.c_void_p(256)  # never dereferenced: the size check comes first
+    assert f(one, one, one, one, _abi.SORT_STATIC_MAX_PAIRS + 1, 0, 44, None) == -1
+    msg = _abi.last_error()
+    assert "GGS_SORT_STATIC_MAX_PAIRS" in msg and str(_abi.SORT_STATIC_MAX_PAIRS) in msg
+    assert f(one, one, one, one, -1, 0, 44, None) == -1
+    assert f(one, one, one, one, 10, 44, 44, None) == -1
+    assert f(one, one, one, one, 10, 0, 65, None) == -1
+    assert f(None, None, None, None, 10, 0, 8, None) == -1
+    assert f(None, None, None, None, 0, 0, 8, None) == 0  # nothing to sort, nothing touched
+    hdr = open(os.path.join(H.ROOT, "include", "ggs_rasterizer.h")).read()
+    assert f"#define GGS_SORT_STATIC_MAX_PAIRS (1 << {_abi.SORT_STATIC_MAX_PAIRS.bit_length() - 1})" in hdr
+
+
 def test_python_surface_matches_reference_names():
     import diff_gaussian_rasterization as dgr
 
