@@ -29,6 +29,12 @@
  *     opacities [P], shs [P,sh_coeffs,3], sg_axis [P,sg_lobes,3], sg_sharpness [P,sg_lobes],
  *     sg_color [P,sg_lobes,3], images channel-major [C,H,W]; viewmatrix / projmatrix are the
  *     transposed 4x4 matrices the reference's cameras hold (scene/cameras.py:70-72).
+ *   - threads and devices: a call works on the CURRENT device and enqueues on the stream it is given; several host
+ *     threads may call at once, each on its own stream, and one process may drive several devices.  What the library
+ *     keeps is keyed accordingly: the last error, the pinned word and the event behind the pair-count read-back per
+ *     host thread (and device); shared-memory opt-ins and the side stream of the peer exchange per device; the
+ *     optional stage timer (ggs_profile_enable) is process-wide and meant for one stream at a time.  The one
+ *     exception is ggs_sort_pairs_static, whose scratch is one array per device (see its comment);
  *   - precomputed 3D covariances are not supported: the reference's own kernel cannot consume them
  *     (render_forward.cu:344-345 dereferences scales+idx unconditionally).
  */
